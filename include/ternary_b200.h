@@ -1,0 +1,188 @@
+/* ternary_b200.h — C ABI of libternary_b200.so (B200 / sm_100a only).
+ *
+ * This is the drop-in boundary for the quantised-Linear hot path of
+ * BenCrulis/ternary-vllm.  Each entry point names the reference interface it
+ * replaces (paths relative to the reference tree).  Conventions:
+ *
+ *   - every pointer is a DEVICE pointer unless the name ends in `_host`;
+ *   - weights are [N, K] = [out_features, in_features] row-major, as in the
+ *     reference (binary/modules.py:96);
+ *   - packed weights are "format C" of the reference
+ *     (impl/tf/moondream/ternary.py:374-398): row n, byte j, bits [2i, 2i+1]
+ *     hold code(W[n, 4j+i]) with code = value + 1 in {0,1,2}; padding code is 1
+ *     (value 0).  `ld_packed` is the row pitch in bytes (>= ceil(K/4));
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*),
+ *     allocates nothing unless stated, and returns 0 on success or a negative
+ *     TB200_E* code; tb200_last_error() gives the message of the calling
+ *     thread's last failure;
+ *   - there is no CPU fallback: on a machine without an sm_100 GPU every
+ *     compute entry returns TB200_ENODEV.
+ */
+#ifndef TERNARY_B200_H
+#define TERNARY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TB200_ABI_VERSION 1
+
+/* error codes */
+#define TB200_OK        0
+#define TB200_EINVAL   -1 /* bad argument (shape, alignment, enum)            */
+#define TB200_ECUDA    -2 /* CUDA runtime/driver error, see tb200_last_error  */
+#define TB200_ENODEV   -3 /* no sm_100 device                                 */
+#define TB200_ENOTSUP  -4 /* combination not implemented                      */
+
+/* element types of float-like buffers */
+#define TB200_F32  0
+#define TB200_BF16 1
+#define TB200_F16  2
+
+/* quantiser decision rules (binary/modules.py:5-26) */
+#define TB200_Q_TERNARY  0 /* tri_step_ste: +1 if w>=0.5, -1 if w<=-0.5, else 0 */
+#define TB200_Q_SIGN     1 /* sign_ste:     +1 if w>=0 (incl. -0.0), else -1     */
+#define TB200_Q_STEP     2 /* step_ste:     +1 if w>=0, else 0                   */
+
+/* reference pack layouts (impl/tf/moondream/ternary.py) */
+#define TB200_FMT_A 0 /* pack_ternary   :57-78   planar, bit0=(t==+1), bit1=(t==-1) */
+#define TB200_FMT_B 1 /* pack_ternary2  :114-133 planar, code = t+1                 */
+#define TB200_FMT_C 2 /* ScaledTernaryPackedMM.pack_fn :374-398 row-interleaved     */
+
+int         tb200_abi_version(void);
+const char* tb200_last_error(void);
+/* number of kernels this library has launched in the calling process (for bench.py's gpu_launches) */
+uint64_t    tb200_launch_count(void);
+
+/* ---- weight preparation ------------------------------------------------ */
+
+/* Replaces tri_step_ste / sign_ste / step_ste (binary/modules.py:5-26) followed by the
+ * int8 cast + pack of utils/conversion.py:52-53,71-72 (ops.pack_fn).  One pass:
+ * w [N,K] (dtype, row pitch ldw elements) -> packed [N, ld_packed] format C.
+ * Bytes in [ceil(K/4), ld_packed) are written with the padding code 0x55.
+ * `codes_out` (optional, int8 [N,K] dense) receives the unpacked codes {-1,0,1}. */
+int tb200_quantize_pack(const void* w, int dtype, int64_t N, int64_t K, int64_t ldw,
+                        int mode, uint8_t* packed, int64_t ld_packed,
+                        int8_t* codes_out, void* stream);
+
+/* Replaces ops.unpack_ternary(pw, orig_dim) (impl/tf/moondream/ternary.py:334):
+ * packed format C -> int8 [N,K] values in {-1,0,1,(2)}. */
+int tb200_unpack(const uint8_t* packed, int64_t ld_packed, int64_t N, int64_t K,
+                 int8_t* out, void* stream);
+
+/* int8 codes [T] (flattened) -> reference format A or B (planar, 1-D), or [N,K] -> C.
+ * Replaces pack_ternary / pack_ternary2 / pack_fn.  out has ceil(T/4) bytes (A,B) or
+ * N*ceil(K/4) bytes (C, tight pitch). For A/B pass N=1, K=T. */
+int tb200_pack_format(const int8_t* codes, int64_t N, int64_t K, int fmt,
+                      uint8_t* out, void* stream);
+/* inverse: unpack_ternary_iterative / unpack_ternary_iterative2 / unpack (C). `out` has
+ * 4*ceil(T/4) entries for A/B (the reference returns the padded length) and N*K for C. */
+int tb200_unpack_format(const uint8_t* packed, int64_t N, int64_t K, int fmt,
+                        int8_t* out, void* stream);
+
+/* Replaces clip_binary_weights (binary/utils.py:74-77): in-place clip(w, -1, 1). */
+int tb200_clip_latent(void* w, int dtype, int64_t numel, void* stream);
+
+/* Replaces the ternary branch of linear_to_quantized (binary/modules.py:275-298):
+ * thresholded-mean ("k-means") scale, `iters` refinements, then latent = clip(W/m, +-1).
+ * per_row=0: one scale for the tensor ("uniform"), broadcast into scale[N];
+ * per_row=1: one scale per output row.  W: [N,K] dtype (dense); latent [N,K] and scale [N]
+ * are fp32, like the parameters of the freshly built reference module (modules.py:277).
+ * `workspace` must hold tb200_ternary_init_workspace(N) bytes. */
+size_t tb200_ternary_init_workspace(int64_t N);
+int tb200_ternary_init(const void* W, int dtype, int64_t N, int64_t K, int per_row, int iters,
+                       float* latent, float* scale, void* workspace, void* stream);
+
+/* Replaces the binary / binary01 branches (binary/modules.py:193-266) with
+ * scale = (sum_{w>0} w - sum_{w<0} w)/count (binary01, positive_only=1: positive part
+ * only), latent = clip(W * prescale, +-1).  prescale is a host float (1.0 for scaling
+ * "none", 1/std for "std"); natural=1 uses 1/scale[row] instead (scaling "natural").
+ * latent, scale: fp32.  workspace: tb200_ternary_init_workspace(N) bytes. */
+int tb200_binary_init(const void* W, int dtype, int64_t N, int64_t K, int per_row, int positive_only,
+                      float prescale, int natural, float* latent, float* scale,
+                      void* workspace, void* stream);
+
+/* ---- activations --------------------------------------------------------- */
+
+/* Per-token symmetric int8 quantisation: s_x[m] = max|x[m,:]|/127 (1.0 if the row is all
+ * zero), q = clamp(rint(x / s_x), -127, 127) with round-to-nearest-even.
+ * x [M,K] dtype (pitch ldx elements) -> q_x int8 [M, ldq] ; s_x f32 [M] ; sum_qx i32 [M].
+ * kperm=0: natural K order.  kperm=1: the K order the tcgen05 GEMM consumes (within every
+ * group of 16, position 4i+b holds element 4b+i).  Columns [K, ldq) are zero-filled. */
+int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K, int64_t ldx,
+                       int8_t* q_x, int64_t ldq, float* s_x, int32_t* sum_qx, int kperm,
+                       void* stream);
+
+/* ---- the fused op: ops.ternary_matmul(x, pw, scale, bias, clip_val) ------ */
+/* (impl/tf/moondream/ternary.py:279-281; same maths as ScaledTernaryLinear.forward,
+ *  binary/modules.py:101-109):  out = clip((x @ unpack(pw)^T) * scale + bias, +-clip_val)
+ *
+ * x      [M,K]  x_dtype, pitch ldx elements
+ * packed [N, ld_packed] format C; scale [N] f32 or NULL (=1); bias [N] f32 or NULL (=0)
+ * out    [M,N]  out_dtype, pitch ldo elements
+ * acc_out (optional, i32 [M,N] dense): the exact integer accumulators sum_k q_x*q_w
+ * sx_out  (optional, f32 [M]) / qx_out (optional, int8 [M,K] dense): the activation
+ *         quantisation the kernel used, for parity tests.                             */
+
+/* Decode shape, M <= TB200_GEMV_MAX_M.  HBM-bound: int8 activation quantisation in the
+ * prologue, 128-bit loads of packed rows, dp4a, warp-shuffle reduction, fused epilogue. */
+#define TB200_GEMV_MAX_M 32
+/* flags bit 0: programmatic dependent launch.  The kernel prefetches its packed weights
+ * before waiting for the previous kernel in the stream (which normally produces x); the
+ * caller asserts that the previous kernel does NOT write `packed`. */
+#define TB200_FLAG_PDL 1
+int tb200_gemv(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+               const uint8_t* packed, int64_t ld_packed, int64_t N,
+               const float* scale, const float* bias, float clip_val,
+               void* out, int out_dtype, int64_t ldo,
+               int32_t* acc_out, float* sx_out, int8_t* qx_out, int flags, void* stream);
+
+/* Same contract with float activations and fp32 accumulation (no activation
+ * quantisation): the reference's exact semantics, for M <= TB200_GEMV_MAX_M. */
+int tb200_gemv_f32(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+                   const uint8_t* packed, int64_t ld_packed, int64_t N,
+                   const float* scale, const float* bias, float clip_val,
+                   void* out, int out_dtype, int64_t ldo, void* stream);
+
+/* Grouped decode: `count` independent layers of identical shape in ONE launch (weights of
+ * layer l at packed + l*stride_packed, activations at x + l*stride_x elements, ...). */
+int tb200_gemv_grouped(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                       const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                       const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                       void* out, int out_dtype, int64_t ldo, int64_t stride_out,
+                       int count, int flags, void* stream);
+
+/* Prefill shape: tcgen05.mma kind::i8, TMEM accumulators.  Takes PRE-QUANTISED activations
+ * from tb200_quant_act_i8(kperm=1): q_x int8 [M, ldq], s_x [M], sum_qx [M].
+ * Requires ldq % 16 == 0, ld_packed % 16 == 0, 16-byte aligned base pointers. */
+int tb200_gemm_i8(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx,
+                  int64_t M, int64_t K,
+                  const uint8_t* packed, int64_t ld_packed, int64_t N,
+                  const float* scale, const float* bias, float clip_val,
+                  void* out, int out_dtype, int64_t ldo,
+                  int32_t* acc_out, void* stream);
+
+/* Convenience: quantise (kperm=1) + tb200_gemm_i8.  workspace: tb200_linear_workspace(M,K) bytes. */
+size_t tb200_linear_workspace(int64_t M, int64_t K);
+int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+                         const uint8_t* packed, int64_t ld_packed, int64_t N,
+                         const float* scale, const float* bias, float clip_val,
+                         void* out, int out_dtype, int64_t ldo,
+                         void* workspace, void* stream);
+
+/* End-to-end with HOST activations/outputs (weights stay resident on the device):
+ * H2D x, forward (GEMV or GEMM by M), D2H out, all on `stream`; x_host/out_host should be
+ * pinned.  dev_x / dev_out are caller-provided device staging buffers ([M,K] / [M,N]).    */
+int tb200_linear_forward_host(const void* x_host, int x_dtype, int64_t M, int64_t K,
+                              const uint8_t* packed, int64_t ld_packed, int64_t N,
+                              const float* scale, const float* bias, float clip_val,
+                              void* out_host, int out_dtype,
+                              void* dev_x, void* dev_out, void* workspace, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TERNARY_B200_H */

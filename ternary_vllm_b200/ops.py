@@ -1,0 +1,272 @@
+"""Thin tensor-level wrappers over the C ABI (``include/ternary_b200.h``).
+
+PyTorch is plumbing here: it owns device memory and the current stream; every function
+passes raw device pointers to ``libternary_b200.so``.  Nothing in this module computes on
+the CPU and nothing falls back: non-CUDA tensors raise ``TernaryB200Error``.
+
+The op set mirrors the reference's operator boundary:
+``ternary_matmul`` = ``larq_compute_engine.ops.ternary_matmul`` (impl/tf/moondream/ternary.py:281),
+``unpack`` = ``ops.unpack_ternary`` (:334), ``quantize_pack`` = ternarise + ``ops.pack_fn``
+(utils/conversion.py:52-53,71-72).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib as L
+from ._lib import TernaryB200Error
+
+_DT = {torch.float32: L.TB200_F32, torch.bfloat16: L.TB200_BF16, torch.float16: L.TB200_F16}
+_MODES = {"ternary": L.Q_TERNARY, "binary": L.Q_SIGN, "sign": L.Q_SIGN, "binary01": L.Q_STEP, "step": L.Q_STEP}
+_FMTS = {"A": L.FMT_A, "B": L.FMT_B, "C": L.FMT_C}
+
+
+def _dt(t: torch.Tensor) -> int:
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TernaryB200Error(f"unsupported dtype {t.dtype}; use float32, bfloat16 or float16") from None
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise TernaryB200Error("ternary_vllm_b200 runs on CUDA (sm_100a) tensors only; there is no CPU fallback")
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def packed_pitch(K: int) -> int:
+    """Row pitch (bytes) of the internal packed layout: ceil(K/4) rounded up to 16 so that every
+    row starts on a 128-bit boundary (padding bytes hold code 1 = weight 0)."""
+    return ((K + 3) // 4 + 15) // 16 * 16
+
+
+# ------------------------------------------------------------------ weight preparation
+def quantize_pack(w: torch.Tensor, mode: str = "ternary", ld_packed: int | None = None,
+                  return_codes: bool = False):
+    """latent [N,K] -> packed uint8 [N, ld_packed] (format C).  One kernel, one pass."""
+    _cuda(w)
+    assert w.dim() == 2
+    w = w if w.stride(1) == 1 else w.contiguous()
+    N, K = w.shape
+    ld = packed_pitch(K) if ld_packed is None else int(ld_packed)
+    packed = torch.empty((N, ld), dtype=torch.uint8, device=w.device)
+    codes = torch.empty((N, K), dtype=torch.int8, device=w.device) if return_codes else None
+    with torch.cuda.device(w.device):
+        L.check(L.lib().tb200_quantize_pack(w.data_ptr(), _dt(w), N, K, w.stride(0), _MODES[mode],
+                                            packed.data_ptr(), ld, _ptr(codes), _stream(w)), "quantize_pack")
+    return (packed, codes) if return_codes else packed
+
+
+def unpack(packed: torch.Tensor, K: int) -> torch.Tensor:
+    """ops.unpack_ternary(pw, orig_dim): packed [N, ld] -> int8 [N, K]."""
+    _cuda(packed)
+    assert packed.dtype == torch.uint8 and packed.dim() == 2 and packed.stride(1) == 1
+    N = packed.shape[0]
+    out = torch.empty((N, K), dtype=torch.int8, device=packed.device)
+    with torch.cuda.device(packed.device):
+        L.check(L.lib().tb200_unpack(packed.data_ptr(), packed.stride(0), N, K, out.data_ptr(), _stream(packed)), "unpack")
+    return out
+
+
+def pack_format(codes: torch.Tensor, fmt: str) -> torch.Tensor:
+    """int8 values in {-1,0,1} -> the reference's byte layout A, B (flattened, planar) or C ([N,K])."""
+    _cuda(codes)
+    codes = codes.to(torch.int8).contiguous()
+    if fmt == "C":
+        assert codes.dim() == 2
+        N, K = codes.shape
+        out = torch.empty((N, (K + 3) // 4), dtype=torch.uint8, device=codes.device)
+    else:
+        N, K = 1, codes.numel()
+        out = torch.empty(((K + 3) // 4,), dtype=torch.uint8, device=codes.device)
+    with torch.cuda.device(codes.device):
+        L.check(L.lib().tb200_pack_format(codes.data_ptr(), N, K, _FMTS[fmt], out.data_ptr(), _stream(codes)), "pack_format")
+    return out
+
+
+def unpack_format(packed: torch.Tensor, fmt: str, N: int = 1, K: int | None = None) -> torch.Tensor:
+    """Inverse of :func:`pack_format`.  A/B return the padded length 4*len(packed) like the reference."""
+    _cuda(packed)
+    packed = packed.contiguous()
+    if fmt == "C":
+        assert K is not None
+        out = torch.empty((N, K), dtype=torch.int8, device=packed.device)
+    else:
+        N, K = 1, 4 * packed.numel()
+        out = torch.empty((K,), dtype=torch.int8, device=packed.device)
+    with torch.cuda.device(packed.device):
+        L.check(L.lib().tb200_unpack_format(packed.data_ptr(), N, K, _FMTS[fmt], out.data_ptr(), _stream(packed)), "unpack_format")
+    return out
+
+
+def clip_latent_(w: torch.Tensor) -> torch.Tensor:
+    """In-place clip(w, -1, 1): clip_binary_weights per tensor (binary/utils.py:74-77)."""
+    _cuda(w)
+    assert w.is_contiguous()
+    with torch.cuda.device(w.device):
+        L.check(L.lib().tb200_clip_latent(w.data_ptr(), _dt(w), w.numel(), _stream(w)), "clip_latent")
+    return w
+
+
+def ternary_init(weight: torch.Tensor, per_row: bool, iters: int = 10):
+    """Ternary branch of linear_to_quantized (binary/modules.py:275-298) -> (latent f32, scale f32)."""
+    _cuda(weight)
+    w = weight.detach().contiguous()
+    N, K = w.shape
+    latent = torch.empty((N, K), dtype=torch.float32, device=w.device)
+    scale = torch.empty((N,), dtype=torch.float32, device=w.device)
+    ws = torch.empty((L.lib().tb200_ternary_init_workspace(N),), dtype=torch.uint8, device=w.device)
+    with torch.cuda.device(w.device):
+        L.check(L.lib().tb200_ternary_init(w.data_ptr(), _dt(w), N, K, int(per_row), int(iters),
+                                           latent.data_ptr(), scale.data_ptr(), ws.data_ptr(), _stream(w)), "ternary_init")
+    return latent, scale
+
+
+def binary_init(weight: torch.Tensor, per_row: bool, positive_only: bool = False,
+                prescale: float = 1.0, natural: bool = False):
+    """Binary / binary01 branches of linear_to_quantized (binary/modules.py:193-266)."""
+    _cuda(weight)
+    w = weight.detach().contiguous()
+    N, K = w.shape
+    latent = torch.empty((N, K), dtype=torch.float32, device=w.device)
+    scale = torch.empty((N,), dtype=torch.float32, device=w.device)
+    ws = torch.empty((L.lib().tb200_ternary_init_workspace(N),), dtype=torch.uint8, device=w.device)
+    with torch.cuda.device(w.device):
+        L.check(L.lib().tb200_binary_init(w.data_ptr(), _dt(w), N, K, int(per_row), int(positive_only),
+                                          float(prescale), int(natural), latent.data_ptr(), scale.data_ptr(),
+                                          ws.data_ptr(), _stream(w)), "binary_init")
+    return latent, scale
+
+
+# ------------------------------------------------------------------ activations
+def quant_act_i8(x: torch.Tensor, kperm: bool = False):
+    """x [M,K] -> (q_x int8 [M, ldq], s_x f32 [M], sum_qx i32 [M]); ldq = K rounded up to 16."""
+    _cuda(x)
+    assert x.dim() == 2 and x.stride(1) == 1
+    M, K = x.shape
+    ldq = (K + 15) // 16 * 16
+    q = torch.empty((M, ldq), dtype=torch.int8, device=x.device)
+    s = torch.empty((M,), dtype=torch.float32, device=x.device)
+    sq = torch.empty((M,), dtype=torch.int32, device=x.device)
+    with torch.cuda.device(x.device):
+        L.check(L.lib().tb200_quant_act_i8(x.data_ptr(), _dt(x), M, K, x.stride(0), q.data_ptr(), ldq,
+                                           s.data_ptr(), sq.data_ptr(), int(kperm), _stream(x)), "quant_act_i8")
+    return q, s, sq
+
+
+# ------------------------------------------------------------------ the fused op
+def _f32_or_none(t, n, device):
+    if t is None:
+        return None
+    t = t.detach()
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        t = t.to(torch.float32).contiguous()
+    assert t.numel() == n and t.device == device
+    return t
+
+
+def gemv(x, packed, scale, bias, clip_val, out_dtype=None, debug=False, pdl=False, out=None):
+    """Decode GEMV (M <= 32).  With ``debug`` also returns (acc i32 [M,N], s_x [M], q_x int8 [M,K])."""
+    _cuda(x, packed, scale, bias)
+    assert x.dim() == 2 and x.stride(1) == 1 and packed.dtype == torch.uint8
+    M, K = x.shape
+    N = packed.shape[0]
+    out_dtype = out_dtype or x.dtype
+    scale = _f32_or_none(scale, N, x.device)
+    bias = _f32_or_none(bias, N, x.device)
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    acc = sx = qx = None
+    if debug:
+        acc = torch.empty((M, N), dtype=torch.int32, device=x.device)
+        sx = torch.empty((M,), dtype=torch.float32, device=x.device)
+        qx = torch.empty((M, K), dtype=torch.int8, device=x.device)
+    with torch.cuda.device(x.device):
+        L.check(L.lib().tb200_gemv(x.data_ptr(), _dt(x), M, K, x.stride(0), packed.data_ptr(), packed.stride(0), N,
+                                   _ptr(scale), _ptr(bias), float(clip_val), out.data_ptr(), _DT[out.dtype],
+                                   out.stride(0), _ptr(acc), _ptr(sx), _ptr(qx), L.FLAG_PDL if pdl else 0,
+                                   _stream(x)), "gemv")
+    return (out, acc, sx, qx) if debug else out
+
+
+def gemv_f32(x, packed, scale, bias, clip_val):
+    """Float-activation GEMV (no activation quantisation): the reference's exact semantics."""
+    _cuda(x, packed, scale, bias)
+    assert x.dim() == 2 and x.stride(1) == 1
+    M, K = x.shape
+    N = packed.shape[0]
+    scale = _f32_or_none(scale, N, x.device)
+    bias = _f32_or_none(bias, N, x.device)
+    out = torch.empty((M, N), dtype=x.dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        L.check(L.lib().tb200_gemv_f32(x.data_ptr(), _dt(x), M, K, x.stride(0), packed.data_ptr(), packed.stride(0), N,
+                                       _ptr(scale), _ptr(bias), float(clip_val), out.data_ptr(), _dt(out),
+                                       out.stride(0), _stream(x)), "gemv_f32")
+    return out
+
+
+def gemm_i8(q_x, s_x, sum_qx, K, packed, scale, bias, clip_val, out_dtype=torch.bfloat16, debug=False):
+    """tcgen05 GEMM on pre-quantised (kperm=1) activations.  ``debug`` also returns acc i32 [M,N]."""
+    _cuda(q_x, s_x, sum_qx, packed, scale, bias)
+    M = q_x.shape[0]
+    N = packed.shape[0]
+    scale = _f32_or_none(scale, N, q_x.device)
+    bias = _f32_or_none(bias, N, q_x.device)
+    out = torch.empty((M, N), dtype=out_dtype, device=q_x.device)
+    acc = torch.empty((M, N), dtype=torch.int32, device=q_x.device) if debug else None
+    with torch.cuda.device(q_x.device):
+        L.check(L.lib().tb200_gemm_i8(q_x.data_ptr(), q_x.stride(0), s_x.data_ptr(), sum_qx.data_ptr(), M, K,
+                                      packed.data_ptr(), packed.stride(0), N, _ptr(scale), _ptr(bias),
+                                      float(clip_val), out.data_ptr(), _DT[out_dtype], out.stride(0), _ptr(acc),
+                                      _stream(q_x)), "gemm_i8")
+    return (out, acc) if debug else out
+
+
+_ws_cache: dict = {}
+
+
+def _workspace(M: int, K: int, device) -> torch.Tensor:
+    need = L.lib().tb200_linear_workspace(M, K)
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _ws_cache.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty((max(need, 1 << 20),), dtype=torch.uint8, device=device)
+        _ws_cache[key] = ws
+    return ws
+
+
+def ternary_matmul(x: torch.Tensor, pw: torch.Tensor, scale, bias, clip_val: float, out_dtype=None) -> torch.Tensor:
+    """``ops.ternary_matmul(x, pw, scale, bias, clip_val)`` (impl/tf/moondream/ternary.py:279-281):
+    ``clip((x @ unpack(pw)^T) * scale + bias, +-clip_val)`` for ``x [..., K]`` and ``pw [N, ld]``.
+    M <= 32 tokens run the HBM-bound GEMV, larger M the tcgen05 kind::i8 GEMM."""
+    _cuda(x, pw, scale, bias)
+    K = x.shape[-1]
+    N = pw.shape[0]
+    x2 = x.reshape(-1, K)
+    if x2.stride(-1) != 1:
+        x2 = x2.contiguous()
+    M = x2.shape[0]
+    out_dtype = out_dtype or x.dtype
+    scale = _f32_or_none(scale, N, x.device)
+    bias = _f32_or_none(bias, N, x.device)
+    out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    if M > 0:
+        ws = _workspace(M, K, x.device)
+        with torch.cuda.device(x.device):
+            L.check(L.lib().tb200_linear_forward(x2.data_ptr(), _dt(x2), M, K, x2.stride(0), pw.data_ptr(),
+                                                 pw.stride(0), N, _ptr(scale), _ptr(bias), float(clip_val),
+                                                 out.data_ptr(), _DT[out_dtype], out.stride(0), ws.data_ptr(),
+                                                 _stream(x)), "linear_forward")
+    return out.reshape(*x.shape[:-1], N)
+
+
+def launch_count() -> int:
+    return int(L.lib().tb200_launch_count())
