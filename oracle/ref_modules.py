@@ -120,9 +120,11 @@ def ternary_init(weight: torch.Tensor, neuron_scale="uniform", kmeans_iter=10):
         mask = (a - m[:, None]) > -m[:, None] / 2.0
         m = (a * mask).float().sum(dim=1) / mask.sum(dim=1)
     latent = (weight * (1.0 / m)[:, None]).clip(-1.0, 1.0).detach()
-    scale = torch.empty(weight.shape[0], dtype=weight.dtype)
+    # the freshly built ScaledTernaryLinear holds fp32 parameters (modules.py:277): the
+    # assignments st.weights.data[:] = ..., st.scale.data[:] = m cast into fp32
+    scale = torch.empty(weight.shape[0], dtype=torch.float32)
     scale[:] = m
-    return latent, scale
+    return latent.to(torch.float32), scale
 
 
 def _prescale(weight, scaling, scale_vec):
@@ -154,7 +156,7 @@ def binary_init(weight: torch.Tensor, neuron_scale="uniform", scaling="none", ki
         denom = K
     else:
         raise ValueError(f"Unknown neuron scaling method: {neuron_scale}")
-    scale = torch.empty(N, dtype=weight.dtype)
+    scale = torch.empty(N, dtype=torch.float32)      # sb.scale is an fp32 parameter (modules.py:194)
     if kind == "binary":
         scale[:] = (m_pos - m_neg) / denom
     elif kind == "binary01":
@@ -163,7 +165,7 @@ def binary_init(weight: torch.Tensor, neuron_scale="uniform", scaling="none", ki
         raise ValueError(kind)
     s = _prescale(weight, scaling, scale)
     latent = (weight * s).clip(-1.0, 1.0).detach()
-    return latent, scale
+    return latent.to(torch.float32), scale
 
 
 def clip_latent(w: torch.Tensor) -> torch.Tensor:

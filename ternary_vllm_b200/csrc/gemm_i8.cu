@@ -391,6 +391,7 @@ extern "C" int tb200_gemm_i8(const int8_t* q_x, int64_t ldq, const float* s_x, c
                              void* out, int out_dtype, int64_t ldo,
                              int32_t* acc_out, void* stream) {
     TB_DEVICE_OR_RETURN();
+    if (M == 0 || N == 0) return TB200_OK;
     TB_REQUIRE(q_x && s_x && sum_qx && packed && out, "gemm_i8: null pointer");
     TB_REQUIRE(M >= 0 && N >= 0 && K > 0 && ldo >= N, "gemm_i8: bad shape M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
     TB_REQUIRE(ldq >= K && ldq % 16 == 0, "gemm_i8: ldq=%lld must be >= K and a multiple of 16", (long long)ldq);

@@ -362,6 +362,7 @@ static int gemv_common(const void* x, int x_dtype, int64_t M, int64_t K, int64_t
                        void* out, int out_dtype, int64_t ldo, int64_t stride_out,
                        int32_t* acc_out, float* sx_out, int8_t* qx_out, int layers, int flags, void* stream) {
     TB_DEVICE_OR_RETURN();
+    if (M == 0 || N == 0) return TB200_OK;
     TB_REQUIRE(x && packed && out, "gemv: null pointer");
     TB_REQUIRE(M >= 0 && M <= TB200_GEMV_MAX_M, "gemv: M=%lld out of range [0,%d]", (long long)M, TB200_GEMV_MAX_M);
     TB_REQUIRE(K > 0 && N >= 0 && ldx >= K && ldo >= N, "gemv: bad shape M=%lld K=%lld N=%lld", (long long)M, (long long)K, (long long)N);
@@ -421,6 +422,7 @@ extern "C" int tb200_gemv_f32(const void* x, int x_dtype, int64_t M, int64_t K, 
                               const float* scale, const float* bias, float clip_val,
                               void* out, int out_dtype, int64_t ldo, void* stream) {
     TB_DEVICE_OR_RETURN();
+    if (M == 0 || N == 0) return TB200_OK;
     TB_REQUIRE(x && packed && out, "gemv_f32: null pointer");
     TB_REQUIRE(M >= 0 && M <= TB200_GEMV_MAX_M, "gemv_f32: M=%lld out of range", (long long)M);
     TB_REQUIRE(K > 0 && N >= 0 && ldx >= K && ldo >= N && ld_packed >= (K + 3) / 4, "gemv_f32: bad shape");

@@ -175,6 +175,7 @@ extern "C" int tb200_quantize_pack(const void* w, int dtype, int64_t N, int64_t 
                                    int mode, uint8_t* packed, int64_t ld_packed,
                                    int8_t* codes_out, void* stream) {
     TB_DEVICE_OR_RETURN();
+    if (N == 0) return TB200_OK;
     TB_REQUIRE(w && packed, "quantize_pack: null pointer");
     TB_REQUIRE(N >= 0 && K >= 0 && ldw >= K, "quantize_pack: bad shape N=%lld K=%lld ldw=%lld",
                (long long)N, (long long)K, (long long)ldw);

@@ -103,6 +103,7 @@ extern "C" int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K
                                   int8_t* q_x, int64_t ldq, float* s_x, int32_t* sum_qx, int kperm,
                                   void* stream) {
     TB_DEVICE_OR_RETURN();
+    if (M == 0) return TB200_OK;
     TB_REQUIRE(x && q_x && s_x, "quant_act_i8: null pointer");
     TB_REQUIRE(M >= 0 && K > 0 && ldx >= K, "quant_act_i8: bad shape");
     TB_REQUIRE(ldq >= K && ldq % 16 == 0, "quant_act_i8: ldq=%lld must be >= K and a multiple of 16", (long long)ldq);

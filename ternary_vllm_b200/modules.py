@@ -59,6 +59,11 @@ class SignSTESat(nn.Module):
         return sign_ste_sat(x)
 
 
+def _require_cuda(x):
+    if not x.is_cuda:
+        raise TernaryB200Error("ternary_vllm_b200 layers run on CUDA (sm_100a) only; there is no CPU fallback")
+
+
 # --------------------------------------------------------------------------- layers
 class _PackedQuantLinear(nn.Module):
     """Shared machinery: latent fp weights + cached 2-bit packed form + fused kernels."""
@@ -145,6 +150,7 @@ class _PackedQuantLinear(nn.Module):
         return ops.ternary_matmul(x, pw, scale, self.bias, self.maxval)
 
     def forward(self, x):
+        _require_cuda(x)
         if self._needs_autograd(x) and not self._frozen:
             return self._forward_ste(x)
         return self._forward_packed(x)
@@ -196,6 +202,7 @@ class SmoothlyBinarizedLinear(_PackedQuantLinear):
         self.weights.grad = (ng + nbg) * (g_norm + bg_norm) * 0.5
 
     def forward(self, x):
+        _require_cuda(x)
         if self.training:
             w = self.weights.clip(-1.0, 1.0).to(x.dtype)
             y = nn.functional.linear(x, w, bias=None if self.bias is None else self.bias.to(x.dtype))

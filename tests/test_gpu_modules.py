@@ -1,0 +1,174 @@
+"""GPU parity of the drop-in layer classes and model surgery (mirrors how train.py / convert.py use them)."""
+import numpy as np
+import pytest
+import torch
+from torch import nn
+
+import ternary_vllm_b200 as tb
+from oracle import ref_int8, ref_modules as om
+
+pytestmark = pytest.mark.gpu
+
+
+def oracle_layer(layer, x, mode):
+    q, s, _ = ref_int8.quant_act(x.float().cpu().numpy())
+    codes = ref_int8.codes_of(layer.weights.detach().cpu().numpy(), mode)
+    scale = layer.scale.detach().cpu().numpy() if hasattr(layer, "scale") else None
+    bias = None if layer.bias is None else layer.bias.detach().cpu().numpy()
+    return ref_int8.fused_out(ref_int8.int_acc(q, codes), s, scale, bias, layer.maxval)
+
+
+@pytest.mark.parametrize("cls,mode", [(tb.ScaledTernaryLinear, "ternary"), (tb.ScaledBinaryLinear, "binary"),
+                                      (tb.ScaledBinary01Linear, "binary01"), (tb.SmoothlyBinarizedLinear, "binary")])
+@pytest.mark.parametrize("shape", [(1, 320), (2, 5, 320), (3, 40, 320)])
+def test_layer_forward(cuda, cls, mode, shape):
+    torch.manual_seed(1)
+    layer = cls(320, 200).to(cuda).eval()
+    if hasattr(layer, "scale"):
+        layer.scale.data.fill_(0.05)
+    x = torch.randn(*shape, device=cuda, dtype=torch.bfloat16)
+    with torch.no_grad():
+        y = layer(x)
+    assert y.shape == (*shape[:-1], 200) and y.dtype == torch.bfloat16
+    want = oracle_layer(layer, x.reshape(-1, 320), mode)
+    got = y.float().cpu().numpy().reshape(-1, 200)
+    assert np.all(np.abs(got - want) <= 2.0 ** -7 * np.abs(want) + 1e-5)
+
+
+def test_layer_matches_reference_golden(cuda, golden):
+    W, x = torch.from_numpy(golden["small_W"]), torch.from_numpy(golden["small_x"])
+    layer = tb.ScaledTernaryLinear(W.shape[1], W.shape[0]).to(cuda)
+    layer.load_state_dict({"weights": W, "scale": torch.from_numpy(golden["small_scale"]), "bias": torch.from_numpy(golden["small_bias"])})
+    ref = golden["small_y_ternary"]
+    rms = np.sqrt((ref ** 2).mean())
+    layer.act_quant = False                                  # float activations: the reference's exact semantics
+    with torch.no_grad():
+        y = layer(x.to(cuda)).cpu().numpy()
+    assert np.all(np.abs(y - ref) <= 1e-4 * np.maximum(np.abs(ref), rms))
+    layer.act_quant = True                                   # int8 activations: error is bounded by the quantisation step
+    with torch.no_grad():
+        y8 = layer(x.to(cuda)).cpu().numpy()
+    assert np.abs(y8 - ref).max() / rms < 0.05
+    # training formulation (autograd on) reproduces the reference bit-for-bit up to fp32 rounding
+    y_t = layer(x.to(cuda))
+    assert np.allclose(y_t.detach().cpu().numpy(), ref, rtol=1e-5, atol=1e-5)
+    y_t.sum().backward()
+    assert layer.weights.grad is not None and layer.scale.grad is not None and layer.bias.grad is not None
+    s = tb.SmoothlyBinarizedLinear(W.shape[1], W.shape[0]).to(cuda)
+    s.load_state_dict({"weights": W, "bias": torch.from_numpy(golden["small_bias"])})
+    s.train()
+    assert np.allclose(s(x.to(cuda)).detach().cpu().numpy(), golden["small_y_smooth_train"], rtol=1e-5, atol=1e-5)
+
+
+def test_repack_on_weight_update_and_frozen(cuda):
+    torch.manual_seed(2)
+    layer = tb.ScaledTernaryLinear(128, 64).to(cuda)
+    x = torch.randn(2, 128, device=cuda)
+    with torch.no_grad():
+        y0 = layer(x).clone()
+        layer.weights.mul_(-1.0)                 # in-place op bumps the version -> repack
+        y1 = layer(x)
+    assert not torch.equal(y0, y1)
+    assert np.array_equal(layer.codes().cpu().numpy(), ref_int8.codes_of(layer.weights.detach().cpu().numpy()))
+    layer.weights.requires_grad_(False)          # frozen weights are fine here
+    with torch.no_grad():
+        assert torch.equal(layer(x), y1)
+    layer.freeze()
+    assert torch.equal(layer(x), y1)             # frozen: packed path even with autograd enabled
+    # input must not be mutated
+    x2 = x.clone()
+    layer(x2)
+    assert torch.equal(x, x2)
+
+
+CASES = [("ternary", "none", "uniform"), ("ternary", "none", "none"), ("binary", "none", "uniform"),
+         ("binary", "std", "independent"), ("binary", "natural", "independent"), ("binary01", "none", "independent"),
+         ("smoothBinary", "none", "uniform")]
+
+
+@pytest.mark.parametrize("qn,sc,ns", CASES)
+def test_linear_to_quantized_golden(cuda, golden, qn, sc, ns):
+    holder = nn.Sequential(nn.Linear(40, 24)).to(cuda)
+    holder[0].weight.data = torch.from_numpy(golden["l2q_W"]).to(cuda)
+    holder[0].bias.data = torch.from_numpy(golden["l2q_b"]).to(cuda)
+    assert tb.linear_to_quantized(holder, quantization=qn, scaling=sc, neuron_scale=ns) is True
+    new = holder[0]
+    cls = {"ternary": tb.ScaledTernaryLinear, "binary": tb.ScaledBinaryLinear, "binary01": tb.ScaledBinary01Linear,
+           "smoothBinary": tb.SmoothlyBinarizedLinear}[qn]
+    assert type(new) is cls and new.weights.device.type == "cuda"
+    key = f"l2q_{qn}_{sc}_{ns}"
+    assert np.allclose(new.weights.detach().cpu().numpy(), golden[key + "_latent"], rtol=2e-6, atol=1e-7)
+    if hasattr(new, "scale"):
+        assert np.allclose(new.scale.detach().cpu().numpy(), golden[key + "_scale"], rtol=2e-6)
+    assert np.array_equal(new.bias.detach().cpu().numpy(), golden[key + "_bias"])
+    with torch.no_grad():
+        new(torch.randn(3, 40, device=cuda))
+
+
+def test_linear_to_quantized_bf16_source(cuda, golden):
+    holder = nn.Sequential(nn.Linear(40, 24)).to(cuda).to(torch.bfloat16)
+    holder[0].weight.data = torch.from_numpy(golden["l2q_W"]).to(cuda).to(torch.bfloat16)
+    tb.linear_to_quantized(holder, quantization="ternary", scaling="none", neuron_scale="none")
+    assert np.allclose(holder[0].scale.detach().float().cpu().numpy(), golden["l2q_bf16_ternary_scale"], rtol=1e-5)
+    assert np.allclose(holder[0].weights.detach().float().cpu().numpy(), golden["l2q_bf16_ternary_latent"], rtol=1e-5, atol=1e-6)
+
+
+def test_clip_binary_weights_golden(cuda, golden):
+    m = nn.Sequential(tb.ScaledTernaryLinear(20, 10), tb.SmoothlyBinarizedLinear(10, 6)).to(cuda)
+    m[0].weights.data = torch.from_numpy(golden["clip_in0"]).to(cuda)
+    m[1].weights.data = torch.from_numpy(golden["clip_in1"]).to(cuda)
+    with torch.no_grad():
+        m[0](torch.randn(1, 20, device=cuda))          # builds the packed cache, which the clip must invalidate
+    tb.clip_binary_weights(m)
+    assert np.array_equal(m[0].weights.detach().cpu().numpy(), golden["clip_out0"])
+    assert np.array_equal(m[1].weights.detach().cpu().numpy(), golden["clip_out1"])
+    assert np.array_equal(m[0].codes().cpu().numpy(), ref_int8.codes_of(golden["clip_out0"]))
+
+
+class _Mixer(nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.Wqkv, self.out_proj, self.layer_idx = nn.Linear(d, 3 * d), nn.Linear(d, d), -1
+
+
+class _MLP(nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.fc1, self.fc2 = nn.Linear(d, 4 * d), nn.Linear(4 * d, d)
+
+
+class _Block(nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.ln, self.mixer, self.mlp = nn.LayerNorm(d), _Mixer(d), _MLP(d)
+
+
+class _FakeMoondream(nn.Module):
+    """Module tree with the names quantize_moondream walks (binary/utils.py:8-33, conversion.py:133-136)."""
+
+    def __init__(self, d=64, n=4):
+        super().__init__()
+        self.text_model = nn.Module()
+        self.text_model.transformer = nn.Module()
+        self.text_model.transformer.embd = nn.Embedding(100, d)
+        self.text_model.transformer.h = nn.ModuleList([_Block(d) for _ in range(n)])
+        self.text_model.lm_head = nn.Module()
+        self.text_model.lm_head.ln = nn.LayerNorm(d)
+        self.text_model.lm_head.linear = nn.Linear(d, 100)
+
+
+def test_quantize_moondream(cuda, capsys):
+    torch.manual_seed(3)
+    model = _FakeMoondream().to(cuda)
+    acc = tb.quantize_moondream(model, start_skip=1, last_skip=1, quantization="ternary", scaling="none",
+                                neuron_scale="none", remove_blocks=[2])
+    h = model.text_model.transformer.h
+    assert len(h) == 3 and [b.mixer.layer_idx for b in h] == [0, 1, 2]
+    assert isinstance(h[0].mlp.fc1, nn.Linear)                       # first block skipped
+    assert isinstance(h[1].mlp.fc1, tb.ScaledTernaryLinear) and isinstance(h[1].mixer.Wqkv, tb.ScaledTernaryLinear)
+    assert isinstance(h[2].mlp.fc1, nn.Linear)                       # last block skipped (was index 3)
+    assert isinstance(model.text_model.lm_head.linear, nn.Linear)    # lm_head never converted
+    assert acc["n_ternary_modules"] == 4 and "estimated quantized size" in capsys.readouterr().out
+    with torch.no_grad():
+        y = h[1].mlp.fc2(torch.nn.functional.gelu(h[1].mlp.fc1(torch.randn(5, 64, device=cuda))))
+    assert y.shape == (5, 64) and torch.isfinite(y).all()
