@@ -91,6 +91,21 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------ reference arm
+_CPU_DATA = {}
+
+
+def _cpu_case(K, N, M):
+    """Synthetic layer for the CPU arm, built once (outside every timed region)."""
+    import torch
+    key = (K, N, M)
+    if key not in _CPU_DATA:
+        g = torch.Generator().manual_seed(1234)
+        W = torch.randn(N, K, generator=g).clip(-1, 1)
+        x = torch.randn(M, K, generator=g)
+        _CPU_DATA[key] = (W, x, torch.full((N,), 1.0 / K ** 0.5), torch.randn(N, generator=g))
+    return _CPU_DATA[key]
+
+
 def cpu_forward_sample(cases, iters, warm):
     """Times the oracle's restatement of ScaledTernaryLinear.forward (binary/modules.py:101-109,
     including the per-call re-ternarisation the reference performs) on the host cores.
@@ -100,10 +115,7 @@ def cpu_forward_sample(cases, iters, warm):
     torch.set_num_threads(os.cpu_count() or 1)
     total_b, total_t, per = 0.0, 0.0, []
     for (K, N, M) in cases:
-        g = torch.Generator().manual_seed(1234)
-        W = torch.randn(N, K, generator=g).clip(-1, 1)
-        x = torch.randn(M, K, generator=g)
-        scale, bias = torch.full((N,), 1.0 / K ** 0.5), torch.randn(N, generator=g)
+        W, x, scale, bias = _cpu_case(K, N, M)
         for _ in range(warm):
             om.scaled_linear_forward(x.clone(), W, scale, bias, 100.0, "ternary")
         t0 = time.perf_counter()
@@ -123,6 +135,8 @@ def run_reference(args):
         return
     import torch
     cases = [(K, N, M) for (K, N) in SHAPES for M in BATCHES]
+    for c in cases:
+        _cpu_case(*c)
     # every step = one forward of one layer per case (bounded sample of the sweep)
     for _ in range(args.warmup):
         cpu_forward_sample(cases, 1, 0)
@@ -139,9 +153,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": val, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak" if args.gpus == 1 else "strong", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": CONFIG_N1,
+        "dtype": "f32", "data": "synthetic", "config": CONFIG_N1 if args.gpus == 1 else CONFIG_TP,
         "cpu_baseline": {"value": val, "unit": "GB/s", "cores": cores, "kind": "port",
-                         "sample": "one layer per sweep case per step (6 forwards), oracle port of "
+                         "sample": "one layer per sweep case per step (6 forwards of configs[1]), oracle port of "
                                    "ScaledTernaryLinear.forward incl. per-call re-ternarisation, torch CPU fp32"},
         "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "cases": per, "gpu_launches": 0,
@@ -153,6 +167,9 @@ METRIC = "packed-ternary decode GEMV sweep, algorithmic HBM bytes / time"
 CONFIG_N1 = {"workload": "configs[1] decode GEMV sweep: ternary Linear 4096x4096 and 4096x11008, batch 1/8/32, "
                          "bf16 activations, ring of distinct layers per case",
              "l2_policy": "inputs larger than L2 (ring of 64 x 4.2 MB / 32 x 11.3 MB packed layers per case)"}
+CONFIG_TP = {"workload": "configs[4] 7B-class decoder projections 4096x11008, 11008x4096, 4096x32000 (lm_head), "
+                         "N-sharded across ranks, decode batch 1/8/32, all-gather of the output shards",
+             "l2_policy": "inputs larger than L2 (ring of distinct layers per shape)"}
 
 
 # ------------------------------------------------------------------------------------ B200 arm
@@ -203,7 +220,10 @@ def run_b200(args):
         ring = rings[(K, N)]
         x, out = xs[c], outs[c]
         for r in range(ring.R):
-            ops.gemv(x, ring.packed[r], ring.scale[r], ring.bias[r], 100.0, pdl=pdl, out=out[r])
+            if M <= 2:     # fused activation quantisation, programmatic dependent launch between layers
+                ops.gemv(x, ring.packed[r], ring.scale[r], ring.bias[r], 100.0, pdl=pdl, out=out[r])
+            else:          # tb200_linear_forward: quantise once + GEMV on int8 activations
+                ops.ternary_matmul(x, ring.packed[r], ring.scale[r], ring.bias[r], 100.0, out=out[r])
 
     def launch_step():
         for c in cases:
@@ -258,13 +278,13 @@ def run_b200(args):
             e1.record(stream)
             stream.synchronize()
             t = e0.elapsed_time(e1) * 1e-3 / (reps * R)          # seconds per layer
-            nl = (M + 7) // 8
+            nl = 1 if M <= 2 else 1 + (M + 15) // 16
             per_case.append({"K": K, "N": N, "M": M, "us_per_layer": t * 1e6, "launches_per_layer": nl,
                              "gbs": algorithmic_bytes(K, N, M) / t / 1e9,
                              "frac_hbm_measured": algorithmic_bytes(K, N, M) / t / 1e9 / pk["hbm_gbs"],
                              "tokens_per_s": M / t})
     dom = [p for p in per_case if p["N"] == 11008 and p["M"] == 1][0]
-    roofline = {"bound": "hbm", "kernel": "gemv_dp4a_kernel<bf16,bf16,MT=1,R=4> on 4096x11008, M=1",
+    roofline = {"bound": "hbm", "kernel": "gemv_mma_kernel<bf16,bf16,NT=1,FUSED> on 4096x11008, M=1 (PDL chain of distinct layers)",
                 "achieved": dom["gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": dom["gbs"] / pk["hbm_gbs"],
                 "peak_source": pk["source"], "frac_of_spec_8TBs": dom["gbs"] / 8000.0,
                 "algorithmic_bytes_per_launch": algorithmic_bytes(4096, 11008, 1),

@@ -57,6 +57,9 @@ const char* tb200_last_error(void);
 /* number of kernels this library has launched in the calling process (for bench.py's gpu_launches) */
 uint64_t    tb200_launch_count(void);
 
+/* debug: when non-null, the decode GEMV writes 16 clock64() stamps per CTA (16*#CTAs int64) */
+void        tb200_debug_set_trace(long long* dev_buf);
+
 /* ---- weight preparation ------------------------------------------------ */
 
 /* Replaces tri_step_ste / sign_ste / step_ste (binary/modules.py:5-26) followed by the
@@ -107,13 +110,18 @@ int tb200_binary_init(const void* W, int dtype, int64_t N, int64_t K, int per_ro
 
 /* ---- activations --------------------------------------------------------- */
 
-/* Per-token symmetric int8 quantisation: s_x[m] = max|x[m,:]|/127 (1.0 if the row is all
- * zero), q = clamp(rint(x / s_x), -127, 127) with round-to-nearest-even.
+/* Per-token symmetric int8 quantisation: s_x[m] = max|x[m,:]|/127, inv = 127/max|x[m,:]|
+ * (both 1.0 if the row is all zero), q = clamp(rint(x * inv), -127, 127), fp32 multiply,
+ * round-to-nearest-even.
  * x [M,K] dtype (pitch ldx elements) -> q_x int8 [M, ldq] ; s_x f32 [M] ; sum_qx i32 [M].
- * kperm=0: natural K order.  kperm=1: the K order the tcgen05 GEMM consumes (within every
- * group of 16, position 4i+b holds element 4b+i).  Columns [K, ldq) are zero-filled. */
+ * layout 0: natural K order.  layout 1: the K order the tcgen05 GEMM consumes (within every
+ * group of 16, position 4i+b holds element 4b+i).  layout 2: the decode GEMV's shared-memory
+ * image (ldq must be 4096*ceil(K/4096)).  Columns beyond K are zero-filled up to ldq. */
+#define TB200_QLAYOUT_NATURAL 0
+#define TB200_QLAYOUT_GEMM    1
+#define TB200_QLAYOUT_GEMV    2
 int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K, int64_t ldx,
-                       int8_t* q_x, int64_t ldq, float* s_x, int32_t* sum_qx, int kperm,
+                       int8_t* q_x, int64_t ldq, float* s_x, int32_t* sum_qx, int layout,
                        void* stream);
 
 /* ---- the fused op: ops.ternary_matmul(x, pw, scale, bias, clip_val) ------ */
@@ -128,7 +136,8 @@ int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K, int64_t l
  *         quantisation the kernel used, for parity tests.                             */
 
 /* Decode shape, M <= TB200_GEMV_MAX_M.  HBM-bound: int8 activation quantisation in the
- * prologue, 128-bit loads of packed rows, dp4a, warp-shuffle reduction, fused epilogue. */
+ * prologue (8 tokens per pass over the weights), TMA-staged packed rows, in-register unpack,
+ * mma.sync.m16n8k32 (u8 x s8) integer dot products, fused epilogue.  K <= 20480. */
 #define TB200_GEMV_MAX_M 32
 /* flags bit 0: programmatic dependent launch.  The kernel prefetches its packed weights
  * before waiting for the previous kernel in the stream (which normally produces x); the
@@ -139,6 +148,15 @@ int tb200_gemv(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
                const float* scale, const float* bias, float clip_val,
                void* out, int out_dtype, int64_t ldo,
                int32_t* acc_out, float* sx_out, int8_t* qx_out, int flags, void* stream);
+
+/* Decode GEMV on activations pre-quantised by tb200_quant_act_i8(layout 1): one pass over the
+ * weights per 16 tokens (8 when K > 4096).  tb200_gemv quantises in its prologue instead, which
+ * every CTA repeats: preferable for 1-2 tokens only. */
+int tb200_gemv_q(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx,
+                 int64_t M, int64_t K,
+                 const uint8_t* packed, int64_t ld_packed, int64_t N,
+                 const float* scale, const float* bias, float clip_val,
+                 void* out, int out_dtype, int64_t ldo, int32_t* acc_out, int flags, void* stream);
 
 /* Same contract with float activations and fp32 accumulation (no activation
  * quantisation): the reference's exact semantics, for M <= TB200_GEMV_MAX_M. */
@@ -165,7 +183,9 @@ int tb200_gemm_i8(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_
                   void* out, int out_dtype, int64_t ldo,
                   int32_t* acc_out, void* stream);
 
-/* Convenience: quantise (kperm=1) + tb200_gemm_i8.  workspace: tb200_linear_workspace(M,K) bytes. */
+/* Whole layer by token count: M <= 2 tb200_gemv (fused quantisation); M <= 32 quantise
+ * (layout 1) + tb200_gemv_q; larger M quantise (layout 1) + tb200_gemm_i8.
+ * workspace: tb200_linear_workspace(M,K) bytes, 256-byte aligned. */
 size_t tb200_linear_workspace(int64_t M, int64_t K);
 int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
                          const uint8_t* packed, int64_t ld_packed, int64_t N,

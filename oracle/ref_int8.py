@@ -9,7 +9,8 @@ activations ``q_x * s_x`` to the reference layer must reproduce the fused output
 (tests/test_gpu_*.py, SURVEY.md §7 "Parity definition").
 
   s_x[m]  = max_k |x[m,k]| / 127            fp32 division; 1.0 for an all-zero row
-  q[m,k]  = clip(rint(x[m,k] / s_x[m]), -127, 127)        fp32 division, round-half-even
+  inv[m]  = 127 / max_k |x[m,k]|            fp32 division; 1.0 for an all-zero row
+  q[m,k]  = clip(rint(x[m,k] * inv[m]), -127, 127)        fp32 multiply, round-half-even
   acc     = q (int64) @ codes(W)^T (int64)                 codes per binary/modules.py:21-26
   y       = clip((float32(acc) * s_x) * scale + bias, +-clip_val)   all fp32
 """
@@ -22,8 +23,10 @@ def quant_act(x: np.ndarray):
     """x [M,K] float32 (bf16/fp16 inputs are widened exactly first) -> (q int8, s_x f32, sum i32)."""
     x = np.asarray(x, dtype=np.float32)
     amax = np.abs(x).max(axis=1) if x.shape[1] else np.zeros(x.shape[0], np.float32)
-    s = np.where(amax > 0, (amax / np.float32(127.0)).astype(np.float32), np.float32(1.0)).astype(np.float32)
-    q = np.rint((x / s[:, None]).astype(np.float32))
+    safe = np.where(amax > 0, amax, np.float32(1.0)).astype(np.float32)
+    s = np.where(amax > 0, (safe / np.float32(127.0)).astype(np.float32), np.float32(1.0)).astype(np.float32)
+    inv = np.where(amax > 0, (np.float32(127.0) / safe).astype(np.float32), np.float32(1.0)).astype(np.float32)
+    q = np.rint((x * inv[:, None]).astype(np.float32))
     q = np.clip(q, -127, 127).astype(np.int8)
     return q, s, q.astype(np.int32).sum(axis=1).astype(np.int32)
 
@@ -35,6 +38,19 @@ def kperm_index(K_padded: int) -> np.ndarray:
     p = np.arange(K_padded)
     g, r = p // 16, p % 16
     return g * 16 + 4 * (r % 4) + r // 4
+
+
+def gemv_layout_index(K: int) -> np.ndarray:
+    """tb200_quant_act_i8 layout 2 (the decode GEMV's shared-memory image): byte position p of the
+    row holds element gemv_layout_index[p] of the zero-padded activation row (ldq = 4096*ceil(K/4096)).
+    16-element group g (kperm order inside) lands at uint4 slot ((c>>5)*4 + j)*32 + (c&31), c=g>>2, j=g&3."""
+    ldq = (K + 4095) // 4096 * 4096
+    src = kperm_index(ldq).reshape(-1, 16)          # group g -> its 16 source elements in kperm order
+    out = np.empty((ldq // 16, 16), dtype=np.int64)
+    g = np.arange(ldq // 16)
+    c, j = g >> 2, g & 3
+    out[((c >> 5) * 4 + j) * 32 + (c & 31)] = src
+    return out.reshape(-1)
 
 
 def int_acc(q_x: np.ndarray, codes: np.ndarray) -> np.ndarray:

@@ -45,6 +45,7 @@ SIGNATURES = {
     "tb200_abi_version": (_i32, []),
     "tb200_last_error": (C.c_char_p, []),
     "tb200_launch_count": (C.c_uint64, []),
+    "tb200_debug_set_trace": (None, [_vp]),
     "tb200_quantize_pack": (_i32, [_vp, _i32, _i64, _i64, _i64, _i32, _vp, _i64, _vp, _vp]),
     "tb200_unpack": (_i32, [_vp, _i64, _i64, _i64, _vp, _vp]),
     "tb200_pack_format": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp]),
@@ -56,6 +57,8 @@ SIGNATURES = {
     "tb200_quant_act_i8": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i32, _vp]),
     "tb200_gemv": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
                           _vp, _i32, _i64, _vp, _vp, _vp, _i32, _vp]),
+    "tb200_gemv_q": (_i32, [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
+                            _vp, _i32, _i64, _vp, _i32, _vp]),
     "tb200_gemv_f32": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
                               _vp, _i32, _i64, _vp]),
     "tb200_gemv_grouped": (_i32, [_vp, _i32, _i64, _i64, _i64, _i64, _vp, _i64, _i64, _i64,

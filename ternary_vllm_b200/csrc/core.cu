@@ -1,7 +1,7 @@
 // core.cu — error reporting, device check, launch counter.
 #include <stdarg.h>
 #include <string.h>
-#include "common.cuh"
+#include "tma.cuh"
 
 namespace tb200 {
 
@@ -44,6 +44,40 @@ int check_device() {
 }
 
 int sm_count() { return g_sms > 0 ? g_sms : 148; }
+
+// cuTensorMapEncodeTiled is fetched through the runtime so that the library has no link-time
+// dependency on libcuda (it must load, and fail loudly, on machines without a driver).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dt, int rank, const void* ptr,
+                    const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
+                    CUtensorMapSwizzle swz) {
+    static EncodeTiledFn enc = nullptr;
+    if (!enc) {
+        void* fp = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess || !fp) {
+            cudaGetLastError();
+            set_error("cuTensorMapEncodeTiled is not available from the driver");
+            return TB200_ECUDA;
+        }
+        enc = (EncodeTiledFn)fp;
+    }
+    cuuint64_t d[3] = {1, 1, 1}, st[2] = {0, 0};
+    cuuint32_t bx[3] = {1, 1, 1}, es[3] = {1, 1, 1};
+    for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
+    for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
+    CUresult r = enc(map, dt, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d dims %llu,%llu,%llu)", (int)r, rank,
+                  (unsigned long long)d[0], (unsigned long long)d[1], (unsigned long long)d[2]);
+        return TB200_ECUDA;
+    }
+    return TB200_OK;
+}
 
 }  // namespace tb200
 

@@ -17,8 +17,7 @@
 //     clip and store bf16/f16/f32.
 // Reference semantics: ops.ternary_matmul (impl/tf/moondream/ternary.py:279-281) /
 // ScaledTernaryLinear.forward (binary/modules.py:101-109).
-#include <cuda.h>
-#include "common.cuh"
+#include "tma.cuh"
 
 namespace tb200 {
 
@@ -39,42 +38,7 @@ template <int BT> struct UmmaCfg {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SX_BYTES + TAIL_BYTES + 1024 /*align slack*/;
 };
 
-// ---- PTX wrappers -------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// Bounded wait: a protocol bug traps (launch failure) instead of hanging the GPU.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
-    uint32_t spins = 0;
-    while (true) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-        if (done) break;
-        if (++spins > 20000000u) {
-            printf("tb200 gemm: mbarrier timeout block %d thread %d bar %u parity %u\n",
-                   (int)blockIdx.x, (int)threadIdx.x, bar, parity);
-            __trap();
-        }
-    }
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// ---- tcgen05 PTX wrappers (mbarrier / TMA wrappers live in tma.cuh) ------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -166,8 +130,8 @@ umma_ternary_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_co
     const int total_tiles = p.m_tiles * p.n_tiles;
 
     if (warp == 0 && lane == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_act) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_pw) : "memory");
+        tma_prefetch_desc(&map_act);
+        tma_prefetch_desc(&map_pw);
         for (int s = 0; s < NS; ++s) {
             mbar_init(bar_full(s), 1);
             mbar_init(bar_aready(s), UM_EXP_WARPS);
@@ -177,7 +141,7 @@ umma_ternary_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_co
             mbar_init(bar_tfull(b), 1);
             mbar_init(bar_tempty(b), 4);
         }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_fence_init();
     }
     if (warp == 2) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sTmemPtr), "n"(Cfg::TMEM_COLS) : "memory");
@@ -314,34 +278,12 @@ umma_ternary_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_co
 }
 
 // ---- host side ------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static EncodeTiledFn get_encode() {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* ptr = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = (EncodeTiledFn)ptr;
-    }
-    return fn;
-}
-
 static int make_map_u8(CUtensorMap* map, const void* ptr, uint64_t inner, uint64_t outer, uint64_t pitch,
                        uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle swz) {
-    EncodeTiledFn enc = get_encode();
-    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return TB200_ECUDA; }
-    cuuint64_t dims[2] = {inner, outer};
-    cuuint64_t strides[1] = {pitch};
-    cuuint32_t box[2] = {box_inner, box_outer};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return TB200_ECUDA; }
-    return TB200_OK;
+    uint64_t dims[2] = {inner, outer};
+    uint64_t strides[1] = {pitch};
+    uint32_t box[2] = {box_inner, box_outer};
+    return make_tensor_map(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, ptr, dims, strides, box, swz);
 }
 
 template <typename OT, int BT>

@@ -18,8 +18,9 @@ static LinearWs carve_ws(void* ws, int64_t M, int64_t K) {
 using namespace tb200;
 
 extern "C" size_t tb200_linear_workspace(int64_t M, int64_t K) {
-    if (M <= TB200_GEMV_MAX_M || K <= 0) return 256;
-    return (size_t)(round_up(M * round_up(K, 16), 256) + 2 * round_up(M * 4, 256) + 256);
+    if (M <= 2 || K <= 0) return 256;
+    const int64_t ldq = round_up(K, 16);
+    return (size_t)(round_up(M * ldq, 256) + 2 * round_up(M * 4, 256) + 256);
 }
 
 extern "C" int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
@@ -27,12 +28,18 @@ extern "C" int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64
                                     const float* scale, const float* bias, float clip_val,
                                     void* out, int out_dtype, int64_t ldo,
                                     void* workspace, void* stream) {
-    if (M <= TB200_GEMV_MAX_M)
+    if (M <= 2)
         return tb200_gemv(x, x_dtype, M, K, ldx, packed, ld_packed, N, scale, bias, clip_val,
                           out, out_dtype, ldo, nullptr, nullptr, nullptr, 0, stream);
     TB_REQUIRE(workspace && (uintptr_t)workspace % 256 == 0, "linear_forward: workspace must be non-null and 256-byte aligned");
     LinearWs ws = carve_ws(workspace, M, K);
-    int rc = tb200_quant_act_i8(x, x_dtype, M, K, ldx, ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, 1, stream);
+    if (M <= TB200_GEMV_MAX_M) {
+        int rc = tb200_quant_act_i8(x, x_dtype, M, K, ldx, ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, TB200_QLAYOUT_GEMM, stream);
+        if (rc) return rc;
+        return tb200_gemv_q(ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, M, K, packed, ld_packed, N, scale, bias, clip_val,
+                            out, out_dtype, ldo, nullptr, TB200_FLAG_PDL, stream);
+    }
+    int rc = tb200_quant_act_i8(x, x_dtype, M, K, ldx, ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, TB200_QLAYOUT_GEMM, stream);
     if (rc) return rc;
     return tb200_gemm_i8(ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, M, K, packed, ld_packed, N, scale, bias, clip_val,
                          out, out_dtype, ldo, nullptr, stream);

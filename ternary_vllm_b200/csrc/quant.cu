@@ -3,16 +3,21 @@
 // consumes the output of this kernel with kperm=1.
 //
 //   s_x[m]  = max_k |x[m,k]| / 127          (1.0 when the row is all zero)
-//   q[m,k]  = clamp(rint(x[m,k] / s_x[m]), -127, 127)     rint = round-half-even
+//   inv[m]  = 127 / max_k |x[m,k]|          (1.0 when the row is all zero)
+//   q[m,k]  = clamp(rint(x[m,k] * inv[m]), -127, 127)     fp32 multiply, rint = round-half-even
 //   sum[m]  = sum_k q[m,k]
+// Output layouts: 0 natural K order; 1 "kperm" (tcgen05 GEMM operand order: within every group of
+// 16, position 4i+b holds element 4b+i); 2 the GEMV's shared-memory image (kperm words, 16-byte
+// chunks arranged [slab of 2048 k][word j of the packed chunk][lane]).
 #include "common.cuh"
 
 namespace tb200 {
 
-__device__ __forceinline__ int quant1(float v, float s) {
-    float r = rintf(__fdiv_rn(v, s));
+// rint + float->int via the 1.5*2^23 trick (no XU-pipe conversions); same bits as rintf + cast
+__device__ __forceinline__ int quant1(float v, float inv) {
+    float r = __fmul_rn(v, inv);
     r = fminf(fmaxf(r, -127.0f), 127.0f);
-    return (int)r;
+    return __float_as_int(__fadd_rn(r, 12582912.0f)) - 0x4B400000;
 }
 
 // one CTA per token row; thread owns 16-element groups (one 16-byte store each)
@@ -20,7 +25,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 quant_act_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
                  int8_t* __restrict__ q, int64_t ldq, float* __restrict__ s_x,
-                 int32_t* __restrict__ sum_qx, int kperm, bool vec_ok) {
+                 int32_t* __restrict__ sum_qx, int layout, bool vec_ok) {
+    const int kperm = layout != 0;
     __shared__ float sh_max[8];
     __shared__ int sh_sum[8];
     const int64_t m = blockIdx.x;
@@ -63,6 +69,7 @@ quant_act_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
 #pragma unroll
     for (int i = 1; i < 8; ++i) amax = fmaxf(amax, sh_max[i]);
     const float s = amax > 0.0f ? __fdiv_rn(amax, 127.0f) : 1.0f;
+    const float inv = amax > 0.0f ? __fdiv_rn(127.0f, amax) : 1.0f;
 
     int lsum = 0;
     for (int64_t g = threadIdx.x; g < groups; g += blockDim.x) {
@@ -70,7 +77,7 @@ quant_act_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
 #pragma unroll
         for (int t = 0; t < 16; ++t) {
             int64_t k = 16 * g + t;
-            qv[t] = k < K ? quant1(to_f32(xr[k]), s) : 0;
+            qv[t] = k < K ? quant1(to_f32(xr[k]), inv) : 0;
             lsum += qv[t];
         }
         uint32_t w[4];
@@ -81,7 +88,12 @@ quant_act_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
             w[i] = (uint32_t)(qv[e0] & 0xff) | ((uint32_t)(qv[e0 + st] & 0xff) << 8) |
                    ((uint32_t)(qv[e0 + 2 * st] & 0xff) << 16) | ((uint32_t)(qv[e0 + 3 * st] & 0xff) << 24);
         }
-        *reinterpret_cast<uint4*>(qr + 16 * g) = make_uint4(w[0], w[1], w[2], w[3]);
+        int64_t pos = g;
+        if (layout == 2) {
+            const int64_t c = g >> 2, j = g & 3;
+            pos = ((c >> 5) * 4 + j) * 32 + (c & 31);
+        }
+        *reinterpret_cast<uint4*>(qr + 16 * pos) = make_uint4(w[0], w[1], w[2], w[3]);
     }
     lsum = warp_sum(lsum);
     if ((threadIdx.x & 31) == 0) sh_sum[threadIdx.x >> 5] = lsum;
@@ -100,7 +112,7 @@ quant_act_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
 using namespace tb200;
 
 extern "C" int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K, int64_t ldx,
-                                  int8_t* q_x, int64_t ldq, float* s_x, int32_t* sum_qx, int kperm,
+                                  int8_t* q_x, int64_t ldq, float* s_x, int32_t* sum_qx, int layout,
                                   void* stream) {
     TB_DEVICE_OR_RETURN();
     if (M == 0) return TB200_OK;
@@ -109,12 +121,13 @@ extern "C" int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K
     TB_REQUIRE(ldq >= K && ldq % 16 == 0, "quant_act_i8: ldq=%lld must be >= K and a multiple of 16", (long long)ldq);
     TB_REQUIRE((uintptr_t)q_x % 16 == 0, "quant_act_i8: q_x must be 16-byte aligned");
     TB_REQUIRE(dtype_ok(dtype), "quant_act_i8: bad dtype %d", dtype);
-    if (M == 0) return TB200_OK;
+    TB_REQUIRE(layout >= 0 && layout <= 2, "quant_act_i8: bad layout %d", layout);
+    TB_REQUIRE(layout != 2 || ldq % 4096 == 0, "quant_act_i8: layout 2 needs ldq = 4096*ceil(K/4096)");
     const size_t es = dtype_size(dtype);
     const bool vec_ok = ((uintptr_t)x % 16 == 0) && ((ldx * es) % 16 == 0);
     TB_DISPATCH_DTYPE(dtype, T,
         (quant_act_kernel<T><<<(unsigned)M, 256, 0, (cudaStream_t)stream>>>(
-            (const T*)x, K, ldx, q_x, ldq, s_x, sum_qx, kperm, vec_ok)));
+            (const T*)x, K, ldx, q_x, ldq, s_x, sum_qx, layout, vec_ok)));
     TB_LAUNCH_CHECK();
     return TB200_OK;
 }

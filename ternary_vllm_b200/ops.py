@@ -147,18 +147,20 @@ def binary_init(weight: torch.Tensor, per_row: bool, positive_only: bool = False
 
 
 # ------------------------------------------------------------------ activations
-def quant_act_i8(x: torch.Tensor, kperm: bool = False):
-    """x [M,K] -> (q_x int8 [M, ldq], s_x f32 [M], sum_qx i32 [M]); ldq = K rounded up to 16."""
+def quant_act_i8(x: torch.Tensor, kperm: bool = False, layout: int | None = None):
+    """x [M,K] -> (q_x int8 [M, ldq], s_x f32 [M], sum_qx i32 [M]).  layout 0 natural, 1 tcgen05
+    GEMM operand order (``kperm=True``), 2 decode-GEMV image; ldq = K rounded up to 16 (4096 for 2)."""
     _cuda(x)
     assert x.dim() == 2 and x.stride(1) == 1
     M, K = x.shape
-    ldq = (K + 15) // 16 * 16
+    layout = int(kperm) if layout is None else layout
+    ldq = (K + 4095) // 4096 * 4096 if layout == 2 else (K + 15) // 16 * 16
     q = torch.empty((M, ldq), dtype=torch.int8, device=x.device)
     s = torch.empty((M,), dtype=torch.float32, device=x.device)
     sq = torch.empty((M,), dtype=torch.int32, device=x.device)
     with torch.cuda.device(x.device):
         L.check(L.lib().tb200_quant_act_i8(x.data_ptr(), _dt(x), M, K, x.stride(0), q.data_ptr(), ldq,
-                                           s.data_ptr(), sq.data_ptr(), int(kperm), _stream(x)), "quant_act_i8")
+                                           s.data_ptr(), sq.data_ptr(), layout, _stream(x)), "quant_act_i8")
     return q, s, sq
 
 
@@ -195,6 +197,22 @@ def gemv(x, packed, scale, bias, clip_val, out_dtype=None, debug=False, pdl=Fals
                                    out.stride(0), _ptr(acc), _ptr(sx), _ptr(qx), L.FLAG_PDL if pdl else 0,
                                    _stream(x)), "gemv")
     return (out, acc, sx, qx) if debug else out
+
+
+def gemv_q(q_x, s_x, sum_qx, K, packed, scale, bias, clip_val, out_dtype=torch.bfloat16, debug=False, pdl=False):
+    """Decode GEMV on activations pre-quantised with ``quant_act_i8(layout=2)`` (4 tokens per pass)."""
+    _cuda(q_x, s_x, sum_qx, packed, scale, bias)
+    M, N = q_x.shape[0], packed.shape[0]
+    scale = _f32_or_none(scale, N, q_x.device)
+    bias = _f32_or_none(bias, N, q_x.device)
+    out = torch.empty((M, N), dtype=out_dtype, device=q_x.device)
+    acc = torch.empty((M, N), dtype=torch.int32, device=q_x.device) if debug else None
+    with torch.cuda.device(q_x.device):
+        L.check(L.lib().tb200_gemv_q(q_x.data_ptr(), q_x.stride(0), s_x.data_ptr(), sum_qx.data_ptr(), M, K,
+                                     packed.data_ptr(), packed.stride(0), N, _ptr(scale), _ptr(bias), float(clip_val),
+                                     out.data_ptr(), _DT[out_dtype], out.stride(0), _ptr(acc),
+                                     L.FLAG_PDL if pdl else 0, _stream(q_x)), "gemv_q")
+    return (out, acc) if debug else out
 
 
 def gemv_f32(x, packed, scale, bias, clip_val):
@@ -243,7 +261,7 @@ def _workspace(M: int, K: int, device) -> torch.Tensor:
     return ws
 
 
-def ternary_matmul(x: torch.Tensor, pw: torch.Tensor, scale, bias, clip_val: float, out_dtype=None) -> torch.Tensor:
+def ternary_matmul(x: torch.Tensor, pw: torch.Tensor, scale, bias, clip_val: float, out_dtype=None, out=None) -> torch.Tensor:
     """``ops.ternary_matmul(x, pw, scale, bias, clip_val)`` (impl/tf/moondream/ternary.py:279-281):
     ``clip((x @ unpack(pw)^T) * scale + bias, +-clip_val)`` for ``x [..., K]`` and ``pw [N, ld]``.
     M <= 32 tokens run the HBM-bound GEMV, larger M the tcgen05 kind::i8 GEMM."""
@@ -257,7 +275,11 @@ def ternary_matmul(x: torch.Tensor, pw: torch.Tensor, scale, bias, clip_val: flo
     out_dtype = out_dtype or x.dtype
     scale = _f32_or_none(scale, N, x.device)
     bias = _f32_or_none(bias, N, x.device)
-    out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    else:
+        assert out.shape == (M, N) and out.stride(1) == 1
+        out_dtype = out.dtype
     if M > 0:
         ws = _workspace(M, K, x.device)
         with torch.cuda.device(x.device):

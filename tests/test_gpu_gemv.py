@@ -55,6 +55,46 @@ def test_gemv_parity(cuda, M, N, K):
     check_against_oracle(W, x, scale, bias, 100.0, out, acc, sx, qx)
 
 
+@pytest.mark.parametrize("M", [3, 4, 7, 8, 9, 16, 17, 32])
+@pytest.mark.parametrize("N,K", [(48, 100), (512, 2048), (1000, 4096), (130, 11008), (2000, 5000), (40, 20000)])
+def test_gemv_prequantised_parity(cuda, M, N, K):
+    """tb200_quant_act_i8(layout 1) + tb200_gemv_q: the path tb200_linear_forward takes for 3..32 tokens."""
+    W, x, scale, bias = make(N, K, M, seed=M * 31 + N + K)
+    packed = ops.quantize_pack(W.to(cuda), "ternary")
+    q, s, sq = ops.quant_act_i8(x.to(cuda), layout=1)
+    out, acc = ops.gemv_q(q, s, sq, K, packed, scale.to(cuda), bias.to(cuda), 100.0, debug=True, pdl=True)
+    qo, so, sqo = ref_int8.quant_act(x.float().numpy())
+    assert np.array_equal(s.cpu().numpy(), so) and np.array_equal(sq.cpu().numpy(), sqo)
+    acc_o = ref_int8.int_acc(qo, ref_int8.codes_of(W.numpy()))
+    assert np.array_equal(acc.cpu().numpy().astype(np.int64), acc_o)
+    y_o = ref_int8.fused_out(acc_o, so, scale.numpy(), bias.numpy(), 100.0)
+    want = torch.from_numpy(y_o).bfloat16().float().numpy()
+    assert np.all(np.abs(out.float().cpu().numpy() - want) <= np.abs(want) * 2.0 ** -7 + 1e-6)
+    # and the public op (quantise + GEMV chosen by token count) gives the same bits
+    y = ops.ternary_matmul(x.to(cuda), packed, scale.to(cuda), bias.to(cuda), 100.0)
+    assert torch.equal(y, out)
+
+
+def test_gemv_grouped_matches_single(cuda):
+    R, N, K = 5, 300, 1024
+    g = torch.Generator().manual_seed(8)
+    packs, outs = [], []
+    x = torch.randn(R, 2, K, generator=g).bfloat16().to(cuda)
+    scale = (torch.rand(R, N, generator=g) * 0.1).to(cuda)
+    bias = torch.randn(R, N, generator=g).to(cuda)
+    for r in range(R):
+        packs.append(ops.quantize_pack(torch.randn(N, K, generator=g).clip(-1, 1).to(cuda), "ternary"))
+        outs.append(ops.gemv(x[r], packs[r], scale[r], bias[r], 100.0))
+    stacked = torch.stack(packs)
+    from ternary_vllm_b200 import _lib as L
+    out = torch.empty(R, 2, N, dtype=torch.bfloat16, device=cuda)
+    L.check(L.lib().tb200_gemv_grouped(x.data_ptr(), L.TB200_BF16, 2, K, K, 2 * K, stacked.data_ptr(), stacked.stride(1),
+                                       stacked.stride(0), N, scale.data_ptr(), bias.data_ptr(), N, 100.0, out.data_ptr(),
+                                       L.TB200_BF16, N, 2 * N, R, 0, torch.cuda.current_stream().cuda_stream), "gemv_grouped")
+    torch.cuda.synchronize()
+    assert torch.equal(out, torch.stack(outs))
+
+
 @pytest.mark.parametrize("xdtype,odtype", [(torch.float32, torch.float32), (torch.float16, torch.float16),
                                            (torch.bfloat16, torch.float32), (torch.float16, torch.float32)])
 def test_gemv_dtypes_and_options(cuda, xdtype, odtype):

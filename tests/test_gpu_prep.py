@@ -134,19 +134,22 @@ def test_ternary_init_vs_oracle(cuda, N, K, dtype):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("kperm", [False, True])
-@pytest.mark.parametrize("M,K", [(1, 64), (5, 77), (3, 4096), (40, 1000)])
-def test_quant_act_bit_exact(cuda, dtype, kperm, M, K):
+@pytest.mark.parametrize("layout", [0, 1, 2])
+@pytest.mark.parametrize("M,K", [(1, 64), (5, 77), (3, 4096), (40, 1000), (2, 11008)])
+def test_quant_act_bit_exact(cuda, dtype, layout, M, K):
     g = torch.Generator().manual_seed(M * 7 + K)
     x = (torch.randn(M, K, generator=g) * 3).to(dtype)
     if M > 2:
         x[1] = 0
-    q, s, sq = ops.quant_act_i8(x.to(cuda), kperm=kperm)
+    q, s, sq = ops.quant_act_i8(x.to(cuda), layout=layout)
     qo, so, sqo = ref_int8.quant_act(x.float().numpy())
     assert np.array_equal(s.cpu().numpy(), so) and np.array_equal(sq.cpu().numpy(), sqo)
     ldq = q.shape[1]
     qpad = np.zeros((M, ldq), np.int8)
     qpad[:, :K] = qo
-    if kperm:
+    if layout == 1:
         qpad = qpad[:, ref_int8.kperm_index(ldq)]
+    elif layout == 2:
+        assert ldq == (K + 4095) // 4096 * 4096
+        qpad = qpad[:, ref_int8.gemv_layout_index(K)]
     assert np.array_equal(q.cpu().numpy(), qpad)

@@ -27,6 +27,23 @@ if case == "gemv":
         for r in range(R):
             ops.gemv(x, packed[r], scale, bias, 100.0, pdl=True, out=out)
     torch.cuda.synchronize()
+elif case == "grouped":
+    from ternary_vllm_b200 import _lib as L
+    M = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    K, N, R = 4096, 11008, 25
+    ld = ops.packed_pitch(K)
+    packed = torch.empty(R, N, ld, dtype=torch.uint8, device=dev)
+    for r in range(R):
+        packed[r] = ops.quantize_pack(torch.randn(N, K, generator=g, device=dev).clip_(-1, 1), "ternary")
+    scale = torch.full((R, N), 1 / math.sqrt(K), device=dev)
+    bias = torch.randn(R, N, generator=g, device=dev)
+    xs = torch.randn(R, M, K, generator=g, device=dev, dtype=torch.bfloat16)
+    out = torch.empty(R, M, N, device=dev, dtype=torch.bfloat16)
+    for _ in range(3):
+        L.check(L.lib().tb200_gemv_grouped(xs.data_ptr(), L.TB200_BF16, M, K, K, M * K, packed.data_ptr(), ld, N * ld, N,
+                                           scale.data_ptr(), bias.data_ptr(), N, 100.0, out.data_ptr(), L.TB200_BF16, N, M * N,
+                                           R, 0, torch.cuda.current_stream().cuda_stream), "grouped")
+    torch.cuda.synchronize()
 else:
     M, K, N = 4096, 4096, 11008
     packed = ops.quantize_pack(torch.randn(N, K, generator=g, device=dev).clip_(-1, 1), "ternary")
