@@ -317,7 +317,7 @@ def run_b200(args):
     print(json.dumps(line))
 
 
-TRAFFIC_BYTES = None    # dram__bytes_read+write per launch of the dominant kernel, from profiles/ (ncu --set full)
+TRAFFIC_BYTES = 11408384    # dram__bytes_read+write per launch of the dominant kernel (profiles/r1_gemv_mma.summary.txt)
 
 
 def run_e2e(args, lib, dev, rings, cases, step_bytes):
