@@ -1,0 +1,415 @@
+// gemm_ts.cu — prefill-shaped ternary GEMM, weights as the TMEM A operand.
+//
+//   out[m, n] = clip( (sum_k q_x[m,k] * w[n,k]) * s_x[m] * scale[n] + bias[n] )
+//
+// Orientation ("swap-AB"): 128 weight rows = UMMA M / TMEM lanes, BT tokens = UMMA N.  Per 256-wide
+// k-block (one pipeline stage):
+//   * TMA brings the packed weight tile (128 rows x 64 bytes, SWIZZLE_64B) and the int8 activation tile
+//     (two BT x 128-byte SWIZZLE_128B sub-tiles);
+//   * expander warp q (TMEM lane quarter q; two warp sets alternate k-blocks) reads the 64 packed bytes of
+//     its rows (4 conflict-free LDS.128 per thread), turns the 16 words into 64 registers of u8 codes
+//     (3 shifts + 4 ANDs per word) and writes them with two tcgen05.st.32x32b.x32 into one of two A
+//     slots in tensor memory (64 columns each): the expanded weights never touch shared memory;
+//   * ONE thread issues 8 x tcgen05.mma.cta_group::1.kind::i8 (A from TMEM, B from shared memory) after
+//     ONE mbarrier wait (ready[s] = activation bytes landed + A slot written) and signals ONE
+//     tcgen05.commit (done[s] frees the shared-memory stage and the A slot).  The issuing thread's loop
+//     latency, not the tensor pipe, bounded the first versions (profiles/README.md, ablation table);
+//   * accumulators are double-buffered in TMEM (2 x BT columns); the epilogue warps read them with
+//     tcgen05.ld, apply -sum_qx, s_x*scale, bias, clip, and hand 32-token x 128-channel chunks to TMA
+//     stores through a double-buffered shared-memory staging tile (2-byte scattered stores cost 60 us).
+// TMEM budget at BT=192: 2*192 (D) + 2*64 (A) = 512 columns.
+#include <stdlib.h>
+#include <type_traits>
+#include "umma.cuh"
+
+namespace tb200 {
+
+constexpr int TS_ROWS = 128;
+constexpr int TS_BK = 256;           // int8 k per stage = two 128-byte swizzle atoms per token row
+constexpr int TS_KS = TS_BK / 128;   // activation sub-tiles per stage
+constexpr int TS_EXP_SETS = 2;       // expander warp sets (4 warps each) taking k-blocks round-robin
+constexpr int TS_THREADS = 256 + 128 * TS_EXP_SETS;   // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8.. expanders
+constexpr int TS_P_BYTES = TS_ROWS * (TS_BK / 4);   // 8 KB packed weights per stage (64 bytes per row)
+constexpr int TS_NSA = 2;            // A tiles in TMEM
+constexpr int TS_A_COLS = TS_BK / 4; // 64 columns per A tile
+
+template <int BT> struct TsCfg {
+    static constexpr int B_BYTES = BT * TS_BK;
+    static constexpr int STAGE_BYTES = B_BYTES + TS_P_BYTES;
+    static constexpr int STAGES = BT >= 192 ? 3 : BT >= 128 ? 4 : BT >= 64 ? 6 : 8;
+    static_assert(true, "");
+    static constexpr int D_COLS = 2 * BT;
+    static constexpr int NEED = D_COLS + TS_NSA * TS_A_COLS;
+    static constexpr int TMEM_COLS = NEED <= 32 ? 32 : NEED <= 64 ? 64 : NEED <= 128 ? 128 : NEED <= 256 ? 256 : 512;
+    static_assert(NEED <= 512, "TMEM budget");
+    static constexpr int SX_BYTES = 2 * BT * 8;
+    static constexpr int OUT_STAGE_BYTES = 32 * TS_ROWS * 4;          // one 32-token x 128-channel chunk, up to fp32
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SX_BYTES + 2 * OUT_STAGE_BYTES + 1024 + 1024;
+    static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+};
+
+// CL = thread-block cluster size: the CL CTAs of a cluster work on CL adjacent weight tiles and the SAME
+// token tile; each loads 1/CL of the activation tile and TMA-multicasts it to all of them, which divides
+// the L2 -> SM operand traffic that bounds the single-CTA kernel (profiles/README.md, ablation table).
+template <typename OT, int BT, int CL>
+__global__ void __launch_bounds__(TS_THREADS, 1)
+umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_pw,
+               const __grid_constant__ CUtensorMap map_out, const UmmaParams p) {
+    using Cfg = TsCfg<BT>;
+    constexpr int NS = Cfg::STAGES;
+    extern __shared__ uint8_t smem_dyn[];
+    const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+    uint8_t* gbase = smem_dyn + (base - smem_u32(smem_dyn));
+    const uint32_t sB = base;                                     // [NS][BT*128] activations (SWIZZLE_128B)
+    const uint32_t sP = sB + NS * Cfg::B_BYTES;                   // [NS][4 KB] packed weights (SWIZZLE_32B)
+    const uint32_t sSX = sP + NS * TS_P_BYTES;
+    const uint32_t sOut = sSX + Cfg::SX_BYTES;                    // [2][32 tokens][128 channels] output staging for TMA stores
+    const uint32_t sBar = sOut + 2 * Cfg::OUT_STAGE_BYTES;
+    // One wait and one commit per k-block for the single MMA-issuing thread (its loop latency, not the
+    // tensor pipe, bounded the first versions): ready[s] completes when the activation bytes have landed
+    // AND the stage's A tile is in TMEM; done[s] frees both the shared-memory stage and the A slot.
+    auto bar_pfull = [&](int s) { return sBar + 8u * s; };                       // packed weights landed
+    auto bar_ready = [&](int s) { return sBar + 8u * (NS + s); };                // activations landed + A expanded
+    auto bar_done = [&](int s) { return sBar + 8u * (2 * NS + s); };             // MMAs of the stage retired
+    auto bar_tfull = [&](int b) { return sBar + 8u * (3 * NS + b); };
+    auto bar_tempty = [&](int b) { return sBar + 8u * (3 * NS + 2 + b); };
+    const uint32_t sTmemPtr = sBar + 8u * (3 * NS + 4);
+    float* sx_sm = reinterpret_cast<float*>(gbase + (sSX - base));
+    int* sq_sm = reinterpret_cast<int*>(sx_sm + 2 * BT);
+    volatile uint32_t* tmem_ptr_sm = reinterpret_cast<volatile uint32_t*>(gbase + (sTmemPtr - base));
+    const uint8_t* gP = gbase + (sP - base);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t cta_rank = 0;
+    if (CL > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+    const int cluster_id = blockIdx.x / CL, num_clusters = gridDim.x / CL;
+    const int n_groups = (p.n_tiles + CL - 1) / CL;
+    const int total_tiles = p.m_tiles * n_groups;           // super-tiles: CL weight tiles x one token tile
+    constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1u);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&map_act);
+        tma_prefetch_desc(&map_pw);
+        for (int s = 0; s < NS; ++s) {
+            mbar_init(bar_pfull(s), 1);
+            mbar_init(bar_ready(s), 1 + 4);                  // producer (with the activation bytes) + 4 expander warps
+            mbar_init(bar_done(s), CL);                      // every CTA of the cluster must have retired the stage
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(bar_tfull(b), 1);
+            mbar_init(bar_tempty(b), 4);
+        }
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sTmemPtr), "n"(Cfg::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (CL > 1) {   // peers' barriers must be initialised before the first multicast load / remote arrive
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_sm;
+    const uint32_t tmem_a0 = tmem_base + (uint32_t)Cfg::D_COLS;     // first A tile column
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0;
+            for (int t = cluster_id; t < total_tiles; t += num_clusters) {
+                const int n_group = t / p.m_tiles, m_tile = t - n_group * p.m_tiles;
+                const int n_tile = n_group * CL + (int)cta_rank;
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait(bar_done(s), ph ^ 1u);
+                    mbar_arrive_expect_tx(bar_pfull(s), TS_P_BYTES);
+                    tma_load_2d(sP + s * TS_P_BYTES, &map_pw, bar_pfull(s), kb * (TS_BK / 4), n_tile * TS_ROWS);
+                    mbar_arrive_expect_tx(bar_ready(s), Cfg::B_BYTES);
+#pragma unroll
+                    for (int j = 0; j < TS_KS; ++j) {
+                        const uint32_t dst = sB + s * Cfg::B_BYTES + j * (BT * 128);
+                        if (CL == 1) {
+                            tma_load_2d(dst, &map_act, bar_ready(s), kb * TS_BK + j * 128, m_tile * BT);
+                        } else {   // my 1/CL slice of the token tile, delivered to every CTA of the cluster
+                            constexpr int SL = BT / CL;
+                            tma_load_2d_mc(dst + cta_rank * (SL * 128), &map_act, bar_ready(s),
+                                           kb * TS_BK + j * 128, m_tile * BT + (int)cta_rank * SL, kMask);
+                        }
+                    }
+                    if (++s == NS) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_i8(TS_ROWS, BT);
+            int s = 0; uint32_t ph = 0; int a = 0; int it = 0;
+            for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
+                const int buf = it & 1;
+                mbar_wait(bar_tempty(buf), (((uint32_t)it >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BT);
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait(bar_ready(s), ph);
+                    tc_fence_after();
+                    const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
+                    if (!(p.dbg & 4)) {
+#pragma unroll
+                        for (int j = 0; j < TS_KS; ++j) {
+                            const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)   // K=32 int8 per MMA = 8 TMEM columns of A, 32 bytes of B
+                                umma_i8_ts(d_tmem, a_tmem + (uint32_t)(j * 32 + k * 8), bdesc + 2u * k, idesc,
+                                           (kb | j | k) ? 1u : 0u);
+                        }
+                    }
+                    if (CL == 1) umma_commit(bar_done(s));
+                    else         umma_commit_mc(bar_done(s), kMask);   // frees the stage in every CTA of the cluster
+                    if (kb == p.k_blocks - 1) umma_commit(bar_tfull(buf));
+                    if (++s == NS) { s = 0; ph ^= 1u; }
+                    a ^= 1;
+                }
+            }
+        }
+    } else if (warp >= 4 && warp < 8) {
+        // ===================== epilogue =====================
+        const int q = warp & 3;
+        const int et = threadIdx.x - 128;
+        OT* out = reinterpret_cast<OT*>(p.out);
+        int it = 0, chunk_no = 0;
+        if (et == 0 && p.tma_out) tma_prefetch_desc(&map_out);
+        for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
+            const int buf = it & 1;
+            const int n_group = t / p.m_tiles, m_tile = t - n_group * p.m_tiles;
+            const int n_tile = n_group * CL + (int)cta_rank;
+            const int64_t m0 = (int64_t)m_tile * BT;
+            const int64_t n = (int64_t)n_tile * TS_ROWS + q * 32 + lane;
+            for (int j = et; j < BT; j += 128) {
+                const int64_t m = m0 + j;
+                sx_sm[buf * BT + j] = m < p.M ? p.s_x[m] : 0.0f;
+                sq_sm[buf * BT + j] = m < p.M ? p.sum_qx[m] : 0;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            const float sc = (n < p.N && p.scale) ? p.scale[n] : 1.0f;
+            const float bi = (n < p.N && p.bias) ? p.bias[n] : 0.0f;
+            mbar_wait(bar_tfull(buf), ((uint32_t)it >> 1) & 1u);
+            tc_fence_after();
+            constexpr int CH = BT >= 32 ? 32 : 16;
+            const uint32_t sx_s = sSX + (uint32_t)(buf * BT) * 4u;                 // shared-space addresses: explicit
+            const uint32_t sq_s = sSX + (uint32_t)(2 * BT + buf * BT) * 4u;       // ld.shared keeps them off the generic path
+#pragma unroll 1
+            for (int c0 = 0; c0 < ((p.dbg & 1) ? 0 : BT); c0 += CH) {
+                // per-token scale and code offset of the chunk first (registers), so that the 32 output
+                // chains below are independent of each other and of the global stores
+                float sxv[CH]; int sqv[CH];
+#pragma unroll
+                for (int j = 0; j < CH; j += 4) {
+                    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                                 : "=f"(sxv[j]), "=f"(sxv[j + 1]), "=f"(sxv[j + 2]), "=f"(sxv[j + 3]) : "r"(sx_s + (c0 + j) * 4));
+                    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];"
+                                 : "=r"(sqv[j]), "=r"(sqv[j + 1]), "=r"(sqv[j + 2]), "=r"(sqv[j + 3]) : "r"(sq_s + (c0 + j) * 4));
+                }
+                uint32_t r[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0);
+                if (CH == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
+                if (p.tma_out && CH == 32) {
+                    // registers -> shared staging [token][channel] -> one TMA store of 32 tokens x 128 channels
+                    // (256-byte rows, asynchronous); the staging buffers alternate per chunk
+                    const uint32_t stg = sOut + (uint32_t)(chunk_no & 1) * Cfg::OUT_STAGE_BYTES;
+                    if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store that last read `stg` is done
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+                    for (int j = 0; j < CH; ++j) {
+                        const int a = (int)r[j] - sqv[j];
+                        const float tv = __fmul_rn((float)a, sxv[j]);
+                        const OT yv = from_f32<OT>(epilogue(tv, sc, bi, p.clip_val));
+                        const uint32_t addr = stg + (uint32_t)((j * TS_ROWS + q * 32 + lane) * sizeof(OT));
+                        if (sizeof(OT) == 4) asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(to_f32(yv)) : "memory");
+                        else asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(*reinterpret_cast<const unsigned short*>(&yv)) : "memory");
+                        if (p.acc_out && n < p.N && m0 + c0 + j < p.M) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
+                    }
+                    fence_proxy_async();
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (et == 0) {
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                                     ::"l"(&map_out), "r"(stg), "r"(n_tile * TS_ROWS), "r"((int)(m0 + c0)) : "memory");
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                    ++chunk_no;
+                } else if (n < p.N) {
+                    OT* orow = out + m0 * p.ldo + n + (int64_t)c0 * p.ldo;
+                    int valid = (int)((p.M - m0 - c0) < CH ? (p.M - m0 - c0) : CH);            // tokens of the chunk in range
+                    if (p.dbg & 256) valid = (sc == 12345.678f) ? valid : 0;
+#pragma unroll
+                    for (int j = 0; j < CH; ++j) {
+                        const int a = (int)r[j] - sqv[j];
+                        const float tv = __fmul_rn((float)a, sxv[j]);
+                        const OT yv = from_f32<OT>(epilogue(tv, sc, bi, p.clip_val));
+                        if (j < valid) {
+                            if (p.acc_out) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
+                            orow[(int64_t)j * p.ldo] = yv;
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty(buf));
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+        }
+        if (et == 0 && p.tma_out) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // staging must outlive the reads
+    } else if (warp >= 8) {
+        // ===================== expanders: packed 2-bit -> u8 codes -> TMEM A tile =====================
+        const int q = warp & 3;                       // TMEM lane quarter; thread = weight row q*32 + lane
+        const int row = q * 32 + lane;
+        const int set = (warp - 8) >> 2;              // this warp set expands k-blocks set, set+SETS, ...
+        static_assert(TS_NSA == 2, "slot bookkeeping below assumes two A slots");
+        int s = 0; uint32_t ph = 0;                   // ring position of the current k-block
+        int s2 = 0; uint32_t ph2 = 0;                 // ring position of the k-block TS_NSA earlier (A-slot reuse)
+        int a = 0, turn = 0; long long kbc = 0;
+        for (int t = cluster_id; t < total_tiles; t += num_clusters) {
+            for (int kb = 0; kb < p.k_blocks; ++kb, ++kbc) {
+                const bool mine = turn == set;
+                if (++turn == TS_EXP_SETS) turn = 0;
+                if (mine) {
+                    mbar_wait(bar_pfull(s), ph);
+                    // SWIZZLE_64B: 16-byte chunk index ^= address bits [7:8] = (row >> 1) & 3 at a 64-byte row pitch
+                    const uint8_t* P = gP + s * TS_P_BYTES + row * 64;
+                    const int sw = (row >> 1) & 3;
+                    uint32_t w[16];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const uint4 v = *reinterpret_cast<const uint4*>(P + ((c ^ sw) << 4));
+                        w[4 * c] = v.x; w[4 * c + 1] = v.y; w[4 * c + 2] = v.z; w[4 * c + 3] = v.w;
+                    }
+                    uint32_t r0[32], r1[32];
+                    if (!(p.dbg & 2)) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            r0[4 * j + 0] = w[j] & 0x03030303u;
+                            r0[4 * j + 1] = (w[j] >> 2) & 0x03030303u;
+                            r0[4 * j + 2] = (w[j] >> 4) & 0x03030303u;
+                            r0[4 * j + 3] = (w[j] >> 6) & 0x03030303u;
+                            r1[4 * j + 0] = w[8 + j] & 0x03030303u;
+                            r1[4 * j + 1] = (w[8 + j] >> 2) & 0x03030303u;
+                            r1[4 * j + 2] = (w[8 + j] >> 4) & 0x03030303u;
+                            r1[4 * j + 3] = (w[8 + j] >> 6) & 0x03030303u;
+                        }
+                    }
+                    if (kbc >= TS_NSA) mbar_wait(bar_done(s2), ph2);   // the MMAs that read this A slot have retired
+                    tc_fence_after();
+                    if (!(p.dbg & 2)) {
+                        const uint32_t ta = tmem_a0 + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * TS_A_COLS);
+                        tmem_st32(ta, r0);
+                        tmem_st32(ta + 32u, r1);
+                        tmem_wait_st();
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_ready(s));
+                }
+                if (++s == NS) { s = 0; ph ^= 1u; }
+                if (kbc >= TS_NSA) { if (++s2 == NS) { s2 = 0; ph2 ^= 1u; } }
+                a ^= 1;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (CL > 1) {   // no CTA may exit while a peer can still multicast into its shared memory or arrive on its barriers
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(Cfg::TMEM_COLS) : "memory");
+    }
+}
+
+template <typename OT, int BT, int CL>
+static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed, UmmaParams p, cudaStream_t s) {
+    using Cfg = TsCfg<BT>;
+    static_assert(BT % (8 * CL) == 0, "token-tile slices must be whole 8-row swizzle atoms");
+    CUtensorMap map_act, map_pw;
+    uint64_t dims_a[2] = {(uint64_t)ldq, (uint64_t)p.M}, str_a[1] = {(uint64_t)ldq};
+    uint32_t box_a[2] = {128, BT / CL};
+    int rc = make_tensor_map(&map_act, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, q_x, dims_a, str_a, box_a, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    uint64_t dims_p[2] = {(uint64_t)((p.K + 3) / 4), (uint64_t)p.N}, str_p[1] = {(uint64_t)ld_packed};
+    uint32_t box_p[2] = {TS_BK / 4, TS_ROWS};
+    rc = make_tensor_map(&map_pw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, packed, dims_p, str_p, box_p, CU_TENSOR_MAP_SWIZZLE_64B);
+    if (rc) return rc;
+    // output tile stores through TMA need a 16-byte aligned base and row pitch
+    CUtensorMap map_out = map_pw;
+    p.tma_out = (BT >= 32) && ((uintptr_t)p.out % 16 == 0) && ((p.ldo * sizeof(OT)) % 16 == 0) && !(p.dbg & 512);
+    if (p.tma_out) {
+        uint64_t dims_o[2] = {(uint64_t)p.N, (uint64_t)p.M}, str_o[1] = {(uint64_t)(p.ldo * sizeof(OT))};
+        uint32_t box_o[2] = {TS_ROWS, 32};
+        rc = make_tensor_map(&map_out, sizeof(OT) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (std::is_same<OT, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16),
+                             2, p.out, dims_o, str_o, box_o, CU_TENSOR_MAP_SWIZZLE_NONE);
+        if (rc) return rc;
+    }
+    auto kern = umma_ts_kernel<OT, BT, CL>;
+    static bool configured = false;
+    if (!configured) {
+        TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        configured = true;
+    }
+    p.m_tiles = (int)((p.M + BT - 1) / BT);
+    p.n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);
+    p.k_blocks = (int)((p.K + TS_BK - 1) / TS_BK);
+    const int super_tiles = p.m_tiles * ((p.n_tiles + CL - 1) / CL);
+    int clusters = sm_count() / CL;
+    if (super_tiles < clusters) clusters = super_tiles;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(clusters * CL), 1, 1);
+    cfg.blockDim = dim3(TS_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = CL > 1 ? 1 : 0;
+    TB_CUDA(cudaLaunchKernelEx(&cfg, kern, map_act, map_pw, map_out, p));
+    TB_LAUNCH_CHECK();
+    return TB200_OK;
+}
+
+static int ts_cluster_size() {
+    static int cl = -1;
+    if (cl < 0) {
+        const char* e = getenv("TB200_GEMM_CLUSTER");
+        cl = e ? atoi(e) : 1;     // measured: multicast clusters do not pay (the kernel is not L2-bound); kept as an option
+        if (cl != 1 && cl != 2 && cl != 4) cl = 1;
+    }
+    return cl;
+}
+
+template <typename OT>
+static int ts_dispatch_bt(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed,
+                          const UmmaParams& p, cudaStream_t s) {
+    if (p.M <= 32) return launch_ts<OT, 32, 1>(q_x, ldq, packed, ld_packed, p, s);
+    if (p.M <= 64) return launch_ts<OT, 64, 1>(q_x, ldq, packed, ld_packed, p, s);
+    if (p.M <= 128) return launch_ts<OT, 128, 1>(q_x, ldq, packed, ld_packed, p, s);
+    const int n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);
+    const int cl = n_tiles >= 8 ? ts_cluster_size() : 1;
+    if (cl == 4) return launch_ts<OT, 192, 4>(q_x, ldq, packed, ld_packed, p, s);
+    if (cl == 2) return launch_ts<OT, 192, 2>(q_x, ldq, packed, ld_packed, p, s);
+    return launch_ts<OT, 192, 1>(q_x, ldq, packed, ld_packed, p, s);
+}
+
+int gemm_ts_launch(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed, UmmaParams p,
+                   int out_dtype, cudaStream_t s) {
+    switch (out_dtype) {
+        case TB200_F32:  return ts_dispatch_bt<float>(q_x, ldq, packed, ld_packed, p, s);
+        case TB200_BF16: return ts_dispatch_bt<__nv_bfloat16>(q_x, ldq, packed, ld_packed, p, s);
+        default:         return ts_dispatch_bt<__half>(q_x, ldq, packed, ld_packed, p, s);
+    }
+}
+
+}  // namespace tb200
