@@ -312,7 +312,8 @@ def run_b200(args):
         "config": CONFIG_N1, "tokens_per_s": step_tokens * args.steps / (ms * 1e-3),
         "frac_hbm_measured": value / pk["hbm_gbs"], "clocks": clocks,
         "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
-        "cases": per_case, "roofline": roofline, "gemm": gemm, "cpu_baseline": cb,
+        "cases": per_case, "roofline": roofline, "gemm": gemm, "vit_l14": None if args.no_gemm else run_vit(dev),
+        "cpu_baseline": cb,
     }
     print(json.dumps(line))
 
@@ -365,6 +366,38 @@ def run_e2e(args, lib, dev, rings, cases, step_bytes):
             "api": "tb200_linear_forward_host (pinned host x -> device, kernel, device -> pinned host y), one call per layer"}
 
 
+VIT_SHAPES = [(1024, 3072), (1024, 1024), (1024, 4096), (4096, 1024)]     # configs[3]: ViT-L/14 QKV, proj, fc1, fc2; M = 32 x 257
+
+
+def run_vit(dev):
+    """configs[3]: ViT-L/14 ternary linears, 32 images x 257 tokens (quantise + tcgen05 GEMM per layer)."""
+    import torch
+    from ternary_vllm_b200 import ops
+    M = 32 * 257
+    g = torch.Generator(device=dev).manual_seed(11)
+    rows = []
+    for (K, N) in VIT_SHAPES:
+        packed = ops.quantize_pack(torch.randn(N, K, generator=g, device=dev).clip_(-1, 1), "ternary")
+        x = torch.randn(M, K, generator=g, device=dev, dtype=torch.bfloat16)
+        scale = torch.full((N,), 1.0 / math.sqrt(K), device=dev)
+        bias = torch.randn(N, generator=g, device=dev)
+        for _ in range(3):
+            ops.ternary_matmul(x, packed, scale, bias, 100.0)
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            ops.ternary_matmul(x, packed, scale, bias, 100.0)
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        t = statistics.median(ts) * 1e-3
+        rows.append({"K": K, "N": N, "M": M, "us": t * 1e6, "tops_incl_act_quant": 2.0 * M * N * K / t / 1e12,
+                     "tokens_per_s": M / t})
+    return rows
+
+
 def run_gemm(dev, pk, M=4096, K=4096, N=11008):
     import torch
     from ternary_vllm_b200 import ops
@@ -377,25 +410,41 @@ def run_gemm(dev, pk, M=4096, K=4096, N=11008):
     bias = torch.randn(N, generator=g, device=dev)
     flush = torch.empty(int(256e6), dtype=torch.uint8, device=dev)
     q, s, sq = ops.quant_act_i8(x, kperm=True)
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
     for _ in range(3):
         ops.gemm_i8(q, s, sq, K, packed, scale, bias, 100.0)
+        ops.ternary_matmul(x, packed, scale, bias, 100.0, out=out)
+    torch.cuda.synchronize()
+    # the whole layer (quantise + GEMM = tb200_linear_forward) as a CUDA graph: the Python call overhead
+    # between the two launches is longer than the quantisation kernel
+    st = torch.cuda.Stream(dev)
+    with torch.cuda.stream(st):
+        gl = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gl, stream=st):
+            ops.ternary_matmul(x, packed, scale, bias, 100.0, out=out)
     torch.cuda.synchronize()
     t_mm, t_all = [], []
     for _ in range(10):
         flush.zero_()                                   # L2 flush between timed iterations
-        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        q, s, sq = ops.quant_act_i8(x, kperm=True)
-        e1.record()
         ops.gemm_i8(q, s, sq, K, packed, scale, bias, 100.0)
-        e2.record()
+        e1.record()
         torch.cuda.synchronize()
-        t_mm.append(e1.elapsed_time(e2))
-        t_all.append(e0.elapsed_time(e2))
+        t_mm.append(e0.elapsed_time(e1))
+        flush.zero_()
+        torch.cuda.synchronize()
+        with torch.cuda.stream(st):
+            e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e2.record(st)
+            gl.replay()
+            e3.record(st)
+            st.synchronize()
+        t_all.append(e2.elapsed_time(e3))
     ops_ = 2.0 * M * N * K
     mm, al = statistics.median(t_mm) * 1e-3, statistics.median(t_all) * 1e-3
     tops = ops_ / mm / 1e12
-    return {"workload": f"configs[2] prefill GEMM M={M} K={K} N={N}, int8 activations, tcgen05 kind::i8",
+    return {"workload": f"configs[2] prefill GEMM M={M} K={K} N={N}, int8 activations, tcgen05 kind::i8 (weights through TMEM)",
             "ms_gemm": mm * 1e3, "ms_quant_plus_gemm": al * 1e3, "tops": tops, "tops_incl_act_quant": ops_ / al / 1e12,
             "tokens_per_s": M / al,
             "roofline": {"bound": "tensor", "achieved": tops, "peak": 4500.0, "unit": "TOP/s", "frac": tops / 4500.0,

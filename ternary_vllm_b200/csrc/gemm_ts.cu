@@ -33,17 +33,16 @@ constexpr int TS_P_BYTES = TS_ROWS * (TS_BK / 4);   // 8 KB packed weights per s
 constexpr int TS_NSA = 2;            // A tiles in TMEM
 constexpr int TS_A_COLS = TS_BK / 4; // 64 columns per A tile
 
-template <int BT> struct TsCfg {
+template <int BT, int OSZ = 4> struct TsCfg {
     static constexpr int B_BYTES = BT * TS_BK;
     static constexpr int STAGE_BYTES = B_BYTES + TS_P_BYTES;
-    static constexpr int STAGES = BT >= 192 ? 3 : BT >= 128 ? 4 : BT >= 64 ? 6 : 8;
-    static_assert(true, "");
+    static constexpr int STAGES = BT >= 192 ? 3 : BT >= 128 ? 4 : BT >= 64 ? 6 : 8;   // 160 -> 4 stages of 48 KB
     static constexpr int D_COLS = 2 * BT;
     static constexpr int NEED = D_COLS + TS_NSA * TS_A_COLS;
     static constexpr int TMEM_COLS = NEED <= 32 ? 32 : NEED <= 64 ? 64 : NEED <= 128 ? 128 : NEED <= 256 ? 256 : 512;
     static_assert(NEED <= 512, "TMEM budget");
     static constexpr int SX_BYTES = 2 * BT * 8;
-    static constexpr int OUT_STAGE_BYTES = 32 * TS_ROWS * 4;          // one 32-token x 128-channel chunk, up to fp32
+    static constexpr int OUT_STAGE_BYTES = 32 * TS_ROWS * OSZ;        // one 32-token x 128-channel output chunk
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + SX_BYTES + 2 * OUT_STAGE_BYTES + 1024 + 1024;
     static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
@@ -55,7 +54,7 @@ template <typename OT, int BT, int CL>
 __global__ void __launch_bounds__(TS_THREADS, 1)
 umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_pw,
                const __grid_constant__ CUtensorMap map_out, const UmmaParams p) {
-    using Cfg = TsCfg<BT>;
+    using Cfg = TsCfg<BT, (int)sizeof(OT)>;
     constexpr int NS = Cfg::STAGES;
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
@@ -332,7 +331,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
 
 template <typename OT, int BT, int CL>
 static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed, UmmaParams p, cudaStream_t s) {
-    using Cfg = TsCfg<BT>;
+    using Cfg = TsCfg<BT, (int)sizeof(OT)>;
     static_assert(BT % (8 * CL) == 0, "token-tile slices must be whole 8-row swizzle atoms");
     CUtensorMap map_act, map_pw;
     uint64_t dims_a[2] = {(uint64_t)ldq, (uint64_t)p.M}, str_a[1] = {(uint64_t)ldq};
@@ -398,6 +397,9 @@ static int ts_dispatch_bt(const int8_t* q_x, int64_t ldq, const uint8_t* packed,
     if (p.M <= 128) return launch_ts<OT, 128, 1>(q_x, ldq, packed, ld_packed, p, s);
     const int n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);
     const int cl = n_tiles >= 8 ? ts_cluster_size() : 1;
+    static int bt = -1;
+    if (bt < 0) { const char* e = getenv("TB200_GEMM_BT"); bt = e ? atoi(e) : 192; }
+    if constexpr (sizeof(OT) == 2) { if (bt == 160) return launch_ts<OT, 160, 1>(q_x, ldq, packed, ld_packed, p, s); }
     if (cl == 4) return launch_ts<OT, 192, 4>(q_x, ldq, packed, ld_packed, p, s);
     if (cl == 2) return launch_ts<OT, 192, 2>(q_x, ldq, packed, ld_packed, p, s);
     return launch_ts<OT, 192, 1>(q_x, ldq, packed, ld_packed, p, s);

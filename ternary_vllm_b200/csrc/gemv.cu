@@ -199,6 +199,7 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
         }
     }
     if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");   // x comes from the previous kernel
+    GV_STAMP(14);    // previous kernel complete (PDL) / consumers start
 
     if (FUSED) {
         const XT* x = reinterpret_cast<const XT*>(p.x) + layer * p.stride_x;
@@ -381,8 +382,12 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
                         const uint32_t mk = 0x03030303u << (2 * i);
 #pragma unroll
                         for (int nt = 0; nt < NT; ++nt) {
-                            const uint4 xv = *reinterpret_cast<const uint4*>(
-                                xq + (size_t)nt * xq_words_nt + ((sgp * 4 + i) * 32 + lane) * 4);
+                            // only the lanes whose token (n = lane>>2) exists load their B fragment: column n of the
+                            // MMA feeds output column n only, and the shared-memory wavefronts scale with M, not 8
+                            uint4 xv = make_uint4(0u, 0u, 0u, 0u);
+                            if (g < p.M - nt * GV_TOK)
+                                xv = *reinterpret_cast<const uint4*>(
+                                    xq + (size_t)nt * xq_words_nt + ((sgp * 4 + i) * 32 + lane) * 4);
                             imma_16832(acc[nt][i], wlo.x & mk, whi.x & mk, wlo.y & mk, whi.y & mk, xv.x, xv.y);
                             imma_16832(acc[nt][i], wlo.z & mk, whi.z & mk, wlo.w & mk, whi.w & mk, xv.z, xv.w);
                         }

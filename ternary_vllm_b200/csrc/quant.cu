@@ -20,46 +20,161 @@ __device__ __forceinline__ int quant1(float v, float inv) {
     return __float_as_int(__fadd_rn(r, 12582912.0f)) - 0x4B400000;
 }
 
-// one CTA per token row; thread owns 16-element groups (one 16-byte store each)
+// 16 consecutive elements as fp32 (zero beyond K); 128-bit loads when the row is 16-byte aligned
 template <typename T>
-__global__ void __launch_bounds__(256)
-quant_act_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
+__device__ __forceinline__ void load16q(const T* __restrict__ xr, int64_t g, int64_t K, bool vec, float v[16]) {
+    if (vec && 16 * g + 16 <= K) {
+        if (sizeof(T) == 4) {
+            const float4* q = reinterpret_cast<const float4*>(xr + 16 * g);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float4 f = q[j];
+                v[4 * j] = f.x; v[4 * j + 1] = f.y; v[4 * j + 2] = f.z; v[4 * j + 3] = f.w;
+            }
+        } else {
+            const uint4* q = reinterpret_cast<const uint4*>(xr + 16 * g);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint4 u = q[j];
+                const T* e = reinterpret_cast<const T*>(&u);
+#pragma unroll
+                for (int t = 0; t < 8; ++t) v[8 * j + t] = to_f32(e[t]);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int t = 0; t < 16; ++t) {
+            int64_t k = 16 * g + t;
+            v[t] = k < K ? to_f32(xr[k]) : 0.0f;
+        }
+    }
+}
+
+__device__ __forceinline__ void store16q(int8_t* qr, int64_t g, const float (&v)[16], float inv, int layout, int& lsum) {
+    int qv[16];
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+        qv[t] = quant1(v[t], inv);
+        lsum += qv[t];
+    }
+    const int kperm = layout != 0;
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        // natural: word i = elements 4i..4i+3 ; kperm: word i = elements i, 4+i, 8+i, 12+i
+        int e0 = kperm ? i : 4 * i, st = kperm ? 4 : 1;
+        w[i] = (uint32_t)(qv[e0] & 0xff) | ((uint32_t)(qv[e0 + st] & 0xff) << 8) |
+               ((uint32_t)(qv[e0 + 2 * st] & 0xff) << 16) | ((uint32_t)(qv[e0 + 3 * st] & 0xff) << 24);
+    }
+    int64_t pos = g;
+    if (layout == 2) {
+        const int64_t c = g >> 2, j = g & 3;
+        pos = ((c >> 5) * 4 + j) * 32 + (c & 31);
+    }
+    *reinterpret_cast<uint4*>(qr + 16 * pos) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// One WARP per token row (no shared memory, no block barrier): lane owns 16-element groups lane, lane+32, ...
+// Rows of up to 32*GC groups (K <= 4096 for GC=8) are held in registers between the absmax pass and the
+// quantisation pass, so the activations are read from HBM once; longer rows are re-read (L2).
+constexpr int QW = 4;     // warps (rows) per CTA
+constexpr int GC = 8;     // cached groups per lane
+template <typename T>
+__global__ void __launch_bounds__(QW * 32)
+quant_act_kernel(const T* __restrict__ x, int64_t M, int64_t K, int64_t ldx,
                  int8_t* __restrict__ q, int64_t ldq, float* __restrict__ s_x,
                  int32_t* __restrict__ sum_qx, int layout, bool vec_ok) {
-    const int kperm = layout != 0;
+    const int lane = threadIdx.x & 31;
+    const int64_t m = (int64_t)blockIdx.x * QW + (threadIdx.x >> 5);
+    if (m >= M) return;
+    const T* xr = x + m * ldx;
+    int8_t* qr = q + m * ldq;
+    const int64_t groups = ldq >> 4;          // ldq is a multiple of 16; groups beyond K quantise to zero
+    const bool cached = groups <= 32 * GC;
+
+    float vc[GC][16];
+    float amax = 0.0f;
+    if (cached) {
+#pragma unroll
+        for (int u = 0; u < GC; ++u) {
+            const int64_t g = lane + 32 * u;
+            if (g < groups) load16q<T>(xr, g, K, vec_ok, vc[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < GC; ++u) {
+            if (lane + 32 * u < groups) {
+#pragma unroll
+                for (int t = 0; t < 16; ++t) amax = fmaxf(amax, fabsf(vc[u][t]));
+            }
+        }
+    } else {
+        for (int64_t g = lane; g * 16 < K; g += 32) {
+            float v[16];
+            load16q<T>(xr, g, K, vec_ok, v);
+#pragma unroll
+            for (int t = 0; t < 16; ++t) amax = fmaxf(amax, fabsf(v[t]));
+        }
+    }
+    amax = warp_max(amax);
+    const float s = amax > 0.0f ? __fdiv_rn(amax, 127.0f) : 1.0f;
+    const float inv = amax > 0.0f ? __fdiv_rn(127.0f, amax) : 1.0f;
+
+    int lsum = 0;
+    if (cached) {
+#pragma unroll
+        for (int u = 0; u < GC; ++u) {
+            const int64_t g = lane + 32 * u;
+            if (g < groups) store16q(qr, g, vc[u], inv, layout, lsum);
+        }
+    } else {
+        for (int64_t g = lane; g < groups; g += 32) {
+            float v[16];
+            load16q<T>(xr, g, K, vec_ok, v);
+            store16q(qr, g, v, inv, layout, lsum);
+        }
+    }
+    lsum = warp_sum(lsum);
+    if (lane == 0) {
+        s_x[m] = s;
+        if (sum_qx) sum_qx[m] = lsum;
+    }
+}
+
+// Long rows (more than 32*GC groups): one CTA of 256 threads per row, up to 4 cached groups per thread
+// (K <= 16384 stays a single HBM pass); absmax and sum meet in shared memory.
+constexpr int GCB = 4;
+template <typename T>
+__global__ void __launch_bounds__(256)
+quant_act_row_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
+                     int8_t* __restrict__ q, int64_t ldq, float* __restrict__ s_x,
+                     int32_t* __restrict__ sum_qx, int layout, bool vec_ok) {
     __shared__ float sh_max[8];
     __shared__ int sh_sum[8];
     const int64_t m = blockIdx.x;
     const T* xr = x + m * ldx;
     int8_t* qr = q + m * ldq;
-    const int64_t groups = ldq >> 4;          // ldq is a multiple of 16
-    const int64_t full = K >> 4;              // groups entirely in range
-
+    const int64_t groups = ldq >> 4;
+    const bool cached = groups <= 256 * GCB;
+    float vc[GCB][16];
     float amax = 0.0f;
-    for (int64_t g = threadIdx.x; g < groups; g += blockDim.x) {
-        if (g < full && vec_ok) {
-            if (sizeof(T) == 4) {
-                const float4* p = reinterpret_cast<const float4*>(xr + 16 * g);
+    if (cached) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    float4 f = p[j];
-                    amax = fmaxf(amax, fmaxf(fmaxf(fabsf(f.x), fabsf(f.y)), fmaxf(fabsf(f.z), fabsf(f.w))));
-                }
-            } else {
-                const uint4* p = reinterpret_cast<const uint4*>(xr + 16 * g);
+        for (int u = 0; u < GCB; ++u) {
+            const int64_t g = threadIdx.x + 256 * u;
+            if (g < groups) load16q<T>(xr, g, K, vec_ok, vc[u]);
+        }
 #pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    uint4 u = p[j];
-                    const T* e = reinterpret_cast<const T*>(&u);
+        for (int u = 0; u < GCB; ++u)
+            if ((int64_t)threadIdx.x + 256 * u < groups) {
 #pragma unroll
-                    for (int t = 0; t < 8; ++t) amax = fmaxf(amax, fabsf(to_f32(e[t])));
-                }
+                for (int t = 0; t < 16; ++t) amax = fmaxf(amax, fabsf(vc[u][t]));
             }
-        } else {
-            for (int t = 0; t < 16; ++t) {
-                int64_t k = 16 * g + t;
-                if (k < K) amax = fmaxf(amax, fabsf(to_f32(xr[k])));
-            }
+    } else {
+        for (int64_t g = threadIdx.x; g * 16 < K; g += 256) {
+            float v[16];
+            load16q<T>(xr, g, K, vec_ok, v);
+#pragma unroll
+            for (int t = 0; t < 16; ++t) amax = fmaxf(amax, fabsf(v[t]));
         }
     }
     amax = warp_max(amax);
@@ -70,30 +185,19 @@ quant_act_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
     for (int i = 1; i < 8; ++i) amax = fmaxf(amax, sh_max[i]);
     const float s = amax > 0.0f ? __fdiv_rn(amax, 127.0f) : 1.0f;
     const float inv = amax > 0.0f ? __fdiv_rn(127.0f, amax) : 1.0f;
-
     int lsum = 0;
-    for (int64_t g = threadIdx.x; g < groups; g += blockDim.x) {
-        int qv[16];
+    if (cached) {
 #pragma unroll
-        for (int t = 0; t < 16; ++t) {
-            int64_t k = 16 * g + t;
-            qv[t] = k < K ? quant1(to_f32(xr[k]), inv) : 0;
-            lsum += qv[t];
+        for (int u = 0; u < GCB; ++u) {
+            const int64_t g = threadIdx.x + 256 * u;
+            if (g < groups) store16q(qr, g, vc[u], inv, layout, lsum);
         }
-        uint32_t w[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            // natural: word i = elements 4i..4i+3 ; kperm: word i = elements i, 4+i, 8+i, 12+i
-            int e0 = kperm ? i : 4 * i, st = kperm ? 4 : 1;
-            w[i] = (uint32_t)(qv[e0] & 0xff) | ((uint32_t)(qv[e0 + st] & 0xff) << 8) |
-                   ((uint32_t)(qv[e0 + 2 * st] & 0xff) << 16) | ((uint32_t)(qv[e0 + 3 * st] & 0xff) << 24);
+    } else {
+        for (int64_t g = threadIdx.x; g < groups; g += 256) {
+            float v[16];
+            load16q<T>(xr, g, K, vec_ok, v);
+            store16q(qr, g, v, inv, layout, lsum);
         }
-        int64_t pos = g;
-        if (layout == 2) {
-            const int64_t c = g >> 2, j = g & 3;
-            pos = ((c >> 5) * 4 + j) * 32 + (c & 31);
-        }
-        *reinterpret_cast<uint4*>(qr + 16 * pos) = make_uint4(w[0], w[1], w[2], w[3]);
     }
     lsum = warp_sum(lsum);
     if ((threadIdx.x & 31) == 0) sh_sum[threadIdx.x >> 5] = lsum;
@@ -125,9 +229,15 @@ extern "C" int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K
     TB_REQUIRE(layout != 2 || ldq % 4096 == 0, "quant_act_i8: layout 2 needs ldq = 4096*ceil(K/4096)");
     const size_t es = dtype_size(dtype);
     const bool vec_ok = ((uintptr_t)x % 16 == 0) && ((ldx * es) % 16 == 0);
-    TB_DISPATCH_DTYPE(dtype, T,
-        (quant_act_kernel<T><<<(unsigned)M, 256, 0, (cudaStream_t)stream>>>(
-            (const T*)x, K, ldx, q_x, ldq, s_x, sum_qx, layout, vec_ok)));
+    if ((ldq >> 4) <= 32 * GC) {
+        TB_DISPATCH_DTYPE(dtype, T,
+            (quant_act_kernel<T><<<(unsigned)((M + QW - 1) / QW), QW * 32, 0, (cudaStream_t)stream>>>(
+                (const T*)x, M, K, ldx, q_x, ldq, s_x, sum_qx, layout, vec_ok)));
+    } else {
+        TB_DISPATCH_DTYPE(dtype, T,
+            (quant_act_row_kernel<T><<<(unsigned)M, 256, 0, (cudaStream_t)stream>>>(
+                (const T*)x, K, ldx, q_x, ldq, s_x, sum_qx, layout, vec_ok)));
+    }
     TB_LAUNCH_CHECK();
     return TB200_OK;
 }

@@ -100,3 +100,24 @@ def test_gemm_full_size_properties(cuda):
     assert torch.equal(acc_n, -acc)
     # the last tile column / row were written
     assert torch.isfinite(out[-1]).all() and torch.isfinite(out[:, -1]).all()
+
+
+@pytest.mark.parametrize("K,N", [(1024, 3072), (1024, 1024), (1024, 4096), (4096, 1024)])
+def test_vit_l14_shapes(cuda, K, N):
+    """BASELINE configs[3]: ViT-L/14 linears at 32 images x 257 tokens (M = 8224 = 42 x 192 + 160: ragged token tile).
+    Sampled accumulators against the oracle plus agreement with the GEMV kernel on the last 32 tokens."""
+    M = 32 * 257
+    g = torch.Generator().manual_seed(K + N)
+    W = torch.randn(N, K, generator=g).clip(-1, 1)
+    x = torch.randn(M, K, generator=g).bfloat16()
+    packed = ops.quantize_pack(W.to(cuda), "ternary")
+    q, s, sq = ops.quant_act_i8(x.to(cuda), kperm=True)
+    out, acc = ops.gemm_i8(q, s, sq, K, packed, None, None, 1e9, out_dtype=torch.float32, debug=True)
+    rows = torch.cat([torch.randint(0, M, (20,), generator=g), torch.tensor([0, M - 1, M - 33, 8063, 8064])])
+    qo, so, _ = ref_int8.quant_act(x[rows].float().numpy())
+    want = ref_int8.int_acc(qo, ref_int8.codes_of(W.numpy()))
+    assert np.array_equal(acc[rows.to(cuda)].cpu().numpy().astype(np.int64), want)
+    _, acc_v, _, _ = ops.gemv(x[-32:].to(cuda).contiguous(), packed, None, None, 1e9, debug=True)
+    assert torch.equal(acc_v, acc[-32:])
+    y = ops.ternary_matmul(x.to(cuda).reshape(32, 257, K), packed, None, None, 1e9)
+    assert y.shape == (32, 257, N) and torch.isfinite(y).all()

@@ -21,3 +21,15 @@ for (M, K, N) in shapes:
         ts.append(e0.elapsed_time(e1))
     t = statistics.median(ts) * 1e-3
     print(f"path={os.environ.get('TB200_GEMM_PATH','ts')} M={M} K={K} N={N}: {t*1e6:8.1f} us  {2*M*N*K/t/1e12:8.1f} TOPS  ({2*M*N*K/t/4.5e15:.3f} of 4.5 POPS)")
+    # activation quantisation alone (CUDA graph of 20 launches: the Python call overhead exceeds the kernel)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        ops.quant_act_i8(x, kperm=True); st.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=st):
+            for _ in range(20): ops.quant_act_i8(x, kperm=True)
+        gr.replay(); st.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st); gr.replay(); e1.record(st); st.synchronize()
+    tq = e0.elapsed_time(e1) * 1e-3 / 20
+    print(f"   quant_act_i8 M={M} K={K}: {tq*1e6:8.1f} us  {(M*K*3)/tq/1e9:8.1f} GB/s")

@@ -7,3 +7,5 @@ for c in d['cases']:
 if d.get('gemm'):
     g = d['gemm']; print('gemm %.1f TOPS (%.3f of 4.5P) ms %.4f  incl quant %.1f TOPS' % (g['tops'], g['roofline']['frac'], g['ms_gemm'], g['tops_incl_act_quant']))
 if d.get('cpu_baseline'): print('cpu', d['cpu_baseline']['value'], d['cpu_baseline']['cores'])
+if d.get('vit_l14'):
+    for v in d['vit_l14']: print('  vit K=%d N=%d M=%d %.1f us %.0f TOPS' % (v['K'], v['N'], v['M'], v['us'], v['tops_incl_act_quant']))
