@@ -26,6 +26,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"        # NCCL prints its version banner on stdout; stdout carries one JSON line
 
 SHAPES = [(4096, 4096), (4096, 11008)]          # (K, N)
 BATCHES = [1, 8, 32]

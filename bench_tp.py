@@ -45,18 +45,23 @@ def run_tp(args, metric):
             packed = ops.quantize_pack(W, "ternary")
             scale = torch.full((b - a,), 1.0 / math.sqrt(K), device=dev)
             bias = torch.randn(b - a, generator=gl, device=dev)
-            layers.append(TPShardedLinear(packed, scale, bias, K, N, 100.0))
+            layers.append(TPShardedLinear(packed, scale, bias, K, N, 100.0).enable_peer_gather(32))
         rings[(K, N)] = layers
     cases = [(K, N, M) for (K, N) in TP_SHAPES for M in TP_BATCHES]
     xs = {c: torch.randn(c[2], c[0], device=dev, dtype=torch.bfloat16) for c in cases}
 
     def step(gather=True):
+        """gather=True: the product path (all-gather fused into the GEMV epilogue over NVLink peer memory + one
+        cross-rank barrier per layer); gather=False: local compute only; gather="nccl": NCCL all-gather baseline."""
         with torch.no_grad():
             for c in cases:
                 for layer in rings[c[:2]]:
-                    y = layer.local_forward(xs[c])
-                    if gather:
-                        layer.gather(y)
+                    if gather is True:
+                        layer(xs[c])
+                    else:
+                        y = layer.local_forward(xs[c])
+                        if gather == "nccl":
+                            layer.gather(y)
 
     def timed(fn, iters):
         dist.barrier()
@@ -74,13 +79,42 @@ def run_tp(args, metric):
 
     for _ in range(max(3, args.warmup)):
         step()
+    torch.cuda.synchronize()
+    # one step = one CUDA graph (local kernels + NCCL all-gathers): decode layers are a few microseconds,
+    # eager launches from Python would measure the host
     n0 = ops.launch_count()
+    mode = "cuda graph"
+    try:
+        if os.environ.get("TB200_TP_GRAPH", "1") != "1":      # the step holds no NCCL call (peer-memory gather), so it captures
+            raise RuntimeError("graph capture disabled")
+        st = torch.cuda.Stream(dev)
+        with torch.cuda.stream(st):
+            g_full = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g_full, stream=st):
+                step()
+            launches_per_step = ops.launch_count() - n0
+            g_local = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g_local, stream=st):
+                step(False)
+        torch.cuda.synchronize()
+        run_full, run_local = g_full.replay, g_local.replay
+    except Exception as e:                               # capture of the collective refused: eager fallback
+        mode = f"eager ({type(e).__name__})"
+        torch.cuda.synchronize()
+        launches_per_step = None
+        run_full, run_local = step, (lambda: step(False))
+    for _ in range(3):
+        run_full()
+    n1 = ops.launch_count()
     sampler = ClockSampler(local)
     sampler.start()
-    ms = timed(step, args.steps)
+    ms = timed(run_full, args.steps)
     clocks = sampler.stop()
-    launches = ops.launch_count() - n0
-    ms_nogather = timed(lambda: step(False), max(2, args.steps // 2)) / max(2, args.steps // 2)
+    launches = launches_per_step * args.steps if launches_per_step is not None else ops.launch_count() - n1
+    ms_nogather = timed(run_local, max(2, args.steps // 2)) / max(2, args.steps // 2)
+    step("nccl")
+    ms_nccl = timed(lambda: step("nccl"), 2) / 2            # eager NCCL all-gather baseline (never captured)
+    ms_eager = timed(step, 2) / 2                           # the product path launched eagerly, for the same comparison
 
     # end to end: pinned host activations in, full gathered output back to pinned host memory, per layer
     hx = {c: torch.randn(c[2], c[0], dtype=torch.bfloat16).pin_memory() for c in cases}
@@ -110,8 +144,10 @@ def run_tp(args, metric):
             "vs_baseline": None, "dtype": "int8 (u8 codes x s8 activations, s32 accumulate)", "data": "synthetic",
             "config": dict(CONFIG_TP, parallelism=f"tp{world} (N-sharded, all-gather)"),
             "tokens_per_s": step_tokens * args.steps / (ms * 1e-3), "clocks": clocks,
-            "gpu_launches": launches, "ms_per_step_without_all_gather": ms_nogather,
+            "gpu_launches": launches, "launch_mode": mode, "ms_per_step_without_all_gather": ms_nogather,
             "all_gather_share": max(0.0, 1.0 - ms_nogather / (ms / args.steps)),
+            "gather": "fused into the GEMV epilogue: stores to every rank's buffer over NVLink peer memory + 1 barrier per layer",
+            "eager_ms_per_step": {"fused_peer_gather": ms_eager, "nccl_all_gather_baseline": ms_nccl},
             "e2e": {"value": step_bytes / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
                     "api": "TPShardedLinear.forward on pinned host activations, gathered output copied back to pinned host"},

@@ -193,6 +193,17 @@ int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64_t K, int64
                          void* out, int out_dtype, int64_t ldo,
                          void* workspace, void* stream);
 
+/* Tensor-parallel decode layer (M <= 32) with the all-gather fused into the epilogue: this rank's
+ * [M, N_local] output block is stored into EVERY rank's [M, ldo] buffer through peer-mapped (NVLink)
+ * pointers; out_peers[r] addresses element (0, first column of this rank's block) of rank r's buffer
+ * (own buffer included).  A cross-rank barrier by the caller makes the gathered rows consumable.
+ * Replaces the NCCL all-gather of SURVEY.md §8e for decode shapes; the reference has no counterpart. */
+int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+                            const uint8_t* packed, int64_t ld_packed, int64_t N_local,
+                            const float* scale, const float* bias, float clip_val,
+                            void* const* out_peers, int n_peers, int out_dtype, int64_t ldo,
+                            void* workspace, void* stream);
+
 /* End-to-end with HOST activations/outputs (weights stay resident on the device):
  * H2D x, forward (GEMV or GEMM by M), D2H out, all on `stream`; x_host/out_host should be
  * pinned.  dev_x / dev_out are caller-provided device staging buffers ([M,K] / [M,N]).    */

@@ -52,6 +52,9 @@ struct GemvParams {
     int pdl;
     bool xvec;
     long long* trace;   // debug: per-CTA clock64 stamps (tb200_debug_set_trace), normally null
+    // tensor-parallel gather fused into the epilogue: when n_peers > 0 the output element is stored into every
+    // rank's [M, ldo] buffer (peer-mapped NVLink addresses, already offset to this rank's column block)
+    void* peers[8]; int n_peers;
 };
 static long long* g_trace = nullptr;
 #define GV_STAMP(slot) do { if (p.trace && threadIdx.x == 0 && blockIdx.y == 0) p.trace[blockIdx.x * 16 + (slot)] = clock64(); } while (0)
@@ -349,6 +352,7 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
     GV_STAMP(1);     // prologue done
 
     const int grp = warp >> 2, wl = warp & 3, gt = ct & (GV_GWARPS * 32 - 1);
+    bool wrote_peer = false;
     int s = 0; uint32_t ph = 0; int buf = 0; int tile_no = 0; int rbi = 0;
     for (int rb = blockIdx.x; rb < p.row_blocks; rb += gridDim.x, ++rbi) {
         if ((rbi & 1) != grp) {                       // the other group's row block: just track the ring
@@ -430,11 +434,20 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
                 if (p.acc_out && layer == 0) p.acc_out[(int64_t)tok * p.N + row] = a;
                 const float tv = __fmul_rn((float)a, sh_sx[tok]);
                 const float y = epilogue(tv, sh_scale[rbi * GV_ROWS + rl], sh_bias[rbi * GV_ROWS + rl], p.clip_val);
-                out[(int64_t)tok * p.ldo + row] = from_f32<OT>(y);
+                const OT yv = from_f32<OT>(y);
+                if (p.n_peers == 0) {
+                    out[(int64_t)tok * p.ldo + row] = yv;
+                } else {
+#pragma unroll 1
+                    for (int r = 0; r < p.n_peers; ++r)     // one small store per peer over NVLink (P2P-mapped memory)
+                        reinterpret_cast<OT*>(p.peers[r])[(int64_t)tok * p.ldo + row] = yv;
+                    wrote_peer = true;
+                }
             }
         }
         buf ^= 1;
     }
+    if (wrote_peer) __threadfence_system();      // peer stores are visible system-wide before the grid completes
     GV_STAMP(15);
 }
 
@@ -589,11 +602,17 @@ static void fill_common(GemvParams& p, int64_t K, int64_t N, const float* scale,
 }
 
 // fused-quantisation entry (raw activations), <= 8 tokens per pass over the weights
-static int gemv_fused(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+static void set_peers(GemvParams& p, void* const* peers, int n_peers, int64_t row_offset_bytes) {
+    p.n_peers = peers ? n_peers : 0;
+    for (int r = 0; r < p.n_peers; ++r) p.peers[r] = (char*)peers[r] + row_offset_bytes;
+}
+
+int gemv_fused(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
                       const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
                       const float* scale, const float* bias, int64_t stride_sb, float clip_val,
                       void* out, int out_dtype, int64_t ldo, int64_t stride_out,
-                      int32_t* acc_out, float* sx_out, int8_t* qx_out, int layers, int flags, cudaStream_t s) {
+                      int32_t* acc_out, float* sx_out, int8_t* qx_out, int layers, int flags, cudaStream_t s,
+                      void* const* peers = nullptr, int n_peers = 0) {
     CUtensorMap map;
     int rc = get_weight_map(packed, ld_packed, N, stride_packed, layers, &map);
     if (rc) return rc;
@@ -609,6 +628,7 @@ static int gemv_fused(const void* x, int x_dtype, int64_t M, int64_t K, int64_t 
         p.acc_out = acc_out ? acc_out + m0 * N : nullptr;
         p.sx_out = sx_out ? sx_out + m0 : nullptr;
         p.qx_out = qx_out ? qx_out + m0 * K : nullptr;
+        set_peers(p, peers, n_peers, m0 * ldo * (int64_t)os);
         rc = gemv_dispatch<1, true>(x_dtype, out_dtype, map, p, layers, s);
         if (rc) return rc;
     }
@@ -621,11 +641,13 @@ using namespace tb200;
 
 extern "C" void tb200_debug_set_trace(long long* dev_buf) { g_trace = dev_buf; }
 
-extern "C" int tb200_gemv_q(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx,
+namespace tb200 {
+int gemv_q_impl(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx,
                             int64_t M, int64_t K,
                             const uint8_t* packed, int64_t ld_packed, int64_t N,
                             const float* scale, const float* bias, float clip_val,
-                            void* out, int out_dtype, int64_t ldo, int32_t* acc_out, int flags, void* stream) {
+                            void* out, int out_dtype, int64_t ldo, int32_t* acc_out, int flags, void* stream,
+                void* const* peers, int n_peers) {
     TB_DEVICE_OR_RETURN();
     if (M == 0 || N == 0) return TB200_OK;
     TB_REQUIRE(q_x && s_x && sum_qx && packed && out, "gemv_q: null pointer");
@@ -650,12 +672,23 @@ extern "C" int tb200_gemv_q(const int8_t* q_x, int64_t ldq, const float* s_x, co
         p.sx_in = s_x + m0; p.sumq_in = sum_qx + m0;
         p.out = (char*)out + m0 * ldo * os;
         p.acc_out = acc_out ? acc_out + m0 * N : nullptr;
+        set_peers(p, peers, n_peers, m0 * ldo * (int64_t)os);
         // activations are int8 already: the XT template parameter is unused on this path
         if (two && p.M > GV_TOK) rc = gemv_dispatch<2, false>(out_dtype, out_dtype, map, p, 1, (cudaStream_t)stream);
         else                     rc = gemv_dispatch<1, false>(out_dtype, out_dtype, map, p, 1, (cudaStream_t)stream);
         if (rc) return rc;
     }
     return TB200_OK;
+}
+}  // namespace tb200
+
+extern "C" int tb200_gemv_q(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx,
+                            int64_t M, int64_t K,
+                            const uint8_t* packed, int64_t ld_packed, int64_t N,
+                            const float* scale, const float* bias, float clip_val,
+                            void* out, int out_dtype, int64_t ldo, int32_t* acc_out, int flags, void* stream) {
+    return gemv_q_impl(q_x, ldq, s_x, sum_qx, M, K, packed, ld_packed, N, scale, bias, clip_val, out, out_dtype, ldo,
+                       acc_out, flags, stream, nullptr, 0);
 }
 
 extern "C" int tb200_gemv(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,

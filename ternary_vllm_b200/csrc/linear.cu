@@ -15,6 +15,18 @@ static LinearWs carve_ws(void* ws, int64_t M, int64_t K) {
     return r;
 }
 }  // namespace tb200
+namespace tb200 {
+int gemv_fused(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+               const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+               const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+               void* out, int out_dtype, int64_t ldo, int64_t stride_out,
+               int32_t* acc_out, float* sx_out, int8_t* qx_out, int layers, int flags, cudaStream_t s,
+               void* const* peers, int n_peers);
+int gemv_q_impl(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx, int64_t M, int64_t K,
+                const uint8_t* packed, int64_t ld_packed, int64_t N, const float* scale, const float* bias, float clip_val,
+                void* out, int out_dtype, int64_t ldo, int32_t* acc_out, int flags, void* stream,
+                void* const* peers, int n_peers);
+}
 using namespace tb200;
 
 extern "C" size_t tb200_linear_workspace(int64_t M, int64_t K) {
@@ -60,4 +72,32 @@ extern "C" int tb200_linear_forward_host(const void* x_host, int x_dtype, int64_
     if (rc) return rc;
     TB_CUDA(cudaMemcpyAsync(out_host, dev_out, (size_t)(M * N) * dtype_size(out_dtype), cudaMemcpyDeviceToHost, s));
     return TB200_OK;
+}
+
+// Tensor-parallel decode layer with the all-gather fused into the GEMV epilogue: this rank's [M, N_local]
+// output block is stored straight into every rank's [M, ldo] buffer through peer-mapped (NVLink) pointers.
+// out_peers[r] = address, in rank r's buffer, of element (0, first column of THIS rank's block).  The caller
+// issues a cross-rank barrier afterwards (ternary_vllm_b200.parallel).  M <= 32 only.
+extern "C" int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+                                       const uint8_t* packed, int64_t ld_packed, int64_t N_local,
+                                       const float* scale, const float* bias, float clip_val,
+                                       void* const* out_peers, int n_peers, int out_dtype, int64_t ldo,
+                                       void* workspace, void* stream) {
+    TB_DEVICE_OR_RETURN();
+    if (M == 0 || N_local == 0) return TB200_OK;
+    TB_REQUIRE(x && packed && out_peers && n_peers >= 1 && n_peers <= 8, "linear_forward_tp: bad peer list");
+    TB_REQUIRE(M <= TB200_GEMV_MAX_M, "linear_forward_tp: M=%lld > %d tokens is not fused (gather with NCCL instead)", (long long)M, TB200_GEMV_MAX_M);
+    TB_REQUIRE(K > 0 && ldx >= K && ldo >= N_local, "linear_forward_tp: bad shape");
+    const int64_t kc = (K + 63) / 64;
+    TB_REQUIRE(ld_packed % 16 == 0 && ld_packed >= kc * 16 && (uintptr_t)packed % 16 == 0, "linear_forward_tp: bad packed layout");
+    if (M <= 2)
+        return gemv_fused(x, x_dtype, M, K, ldx, 0, packed, ld_packed, 0, N_local, scale, bias, 0, clip_val,
+                          out_peers[0], out_dtype, ldo, 0, nullptr, nullptr, nullptr, 1, 0, (cudaStream_t)stream,
+                          out_peers, n_peers);
+    TB_REQUIRE(workspace && (uintptr_t)workspace % 256 == 0, "linear_forward_tp: workspace must be non-null and 256-byte aligned");
+    LinearWs ws = carve_ws(workspace, M, K);
+    int rc = tb200_quant_act_i8(x, x_dtype, M, K, ldx, ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, TB200_QLAYOUT_GEMM, stream);
+    if (rc) return rc;
+    return gemv_q_impl(ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, M, K, packed, ld_packed, N_local, scale, bias, clip_val,
+                       out_peers[0], out_dtype, ldo, nullptr, TB200_FLAG_PDL, stream, out_peers, n_peers);
 }

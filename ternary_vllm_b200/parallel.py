@@ -13,6 +13,9 @@ import torch
 import torch.distributed as dist
 from torch import nn
 
+import ctypes
+
+from . import _lib as L
 from . import ops
 
 ROW_ALIGN = 16      # the decode GEMV works on 16-row tiles, the tcgen05 GEMM on 128-row tiles
@@ -81,7 +84,53 @@ class TPShardedLinear(nn.Module):
         dist.all_gather_into_tensor(buf, y_local.contiguous(), group=self.group)      # rank-major concatenation
         return buf.view(self.world, M, self.n_shard).permute(1, 0, 2).reshape(M, self.world * self.n_shard)[:, : self.out_features]
 
+    # -- fused gather over NVLink peer memory (decode shapes) -------------------------------------------
+    def enable_peer_gather(self, max_tokens: int = 32, dtype=torch.bfloat16):
+        """Allocate two symmetric (peer-mapped) output buffers [max_tokens, world*n_shard] and exchange their
+        addresses.  Afterwards ``forward`` for <= 32 tokens runs ``tb200_linear_forward_tp``: the GEMV epilogue
+        stores this rank's column block into every rank's buffer, then ONE cross-rank barrier replaces the
+        NCCL all-gather.  Buffers alternate per call, so a peer may start the next call while this rank's
+        consumers still read the previous result."""
+        import torch.distributed._symmetric_memory as symm_mem
+
+        dev = self.packed.device
+        self._peer_ld = self.world * self.n_shard
+        self._peer_tokens = max_tokens
+        self._peer_dtype = dtype
+        grp = self.group if self.group is not None else dist.group.WORLD
+        self._peer_bufs, self._peer_hdls, self._peer_ptrs = [], [], []
+        esz = torch.empty((), dtype=dtype).element_size()
+        for _ in range(2):
+            buf = symm_mem.empty((max_tokens, self._peer_ld), dtype=dtype, device=dev)
+            hdl = symm_mem.rendezvous(buf, grp)
+            ptrs = (ctypes.c_void_p * self.world)(*[int(hdl.buffer_ptrs[r]) + self.rank * self.n_shard * esz
+                                                    for r in range(self.world)])
+            self._peer_bufs.append(buf)
+            self._peer_hdls.append(hdl)
+            self._peer_ptrs.append(ptrs)
+        self._peer_turn = 0
+        return self
+
+    def forward_peer(self, x2: torch.Tensor) -> torch.Tensor:
+        M, K = x2.shape
+        i = self._peer_turn
+        self._peer_turn ^= 1
+        buf, hdl, ptrs = self._peer_bufs[i], self._peer_hdls[i], self._peer_ptrs[i]
+        n_local = self.stop - self.start
+        ws = ops._workspace(M, K, x2.device)
+        with torch.cuda.device(x2.device):
+            L.check(L.lib().tb200_linear_forward_tp(
+                x2.data_ptr(), ops._dt(x2), M, K, x2.stride(0), self.packed.data_ptr(), self.packed.stride(0), n_local,
+                ops._ptr(self.scale), ops._ptr(self.bias), float(self.maxval), ptrs, self.world,
+                ops._DT[self._peer_dtype], self._peer_ld, ws.data_ptr(), ops._stream(x2)), "linear_forward_tp")
+        hdl.barrier(channel=0)                   # every rank's block has landed in every buffer
+        return buf[:M, : self.out_features]
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         x2 = x.reshape(-1, x.shape[-1])
-        y = self.gather(self.local_forward(x2))
+        if getattr(self, "_peer_bufs", None) and x2.shape[0] <= min(self._peer_tokens, L.GEMV_MAX_M) \
+                and x2.is_cuda and x2.dtype == self._peer_dtype and self.stop > self.start:
+            y = self.forward_peer(x2 if x2.stride(-1) == 1 else x2.contiguous())
+        else:
+            y = self.gather(self.local_forward(x2))
         return y.reshape(*x.shape[:-1], self.out_features)
