@@ -222,7 +222,7 @@ def run_b200(args):
         ring = rings[(K, N)]
         x, out = xs[c], outs[c]
         for r in range(ring.R):
-            if M <= 2:     # fused activation quantisation, programmatic dependent launch between layers
+            if M <= 8:     # fused activation quantisation, programmatic dependent launch between layers
                 ops.gemv(x, ring.packed[r], ring.scale[r], ring.bias[r], 100.0, pdl=pdl, out=out[r])
             else:          # tb200_linear_forward: quantise once + GEMV on int8 activations
                 ops.ternary_matmul(x, ring.packed[r], ring.scale[r], ring.bias[r], 100.0, out=out[r])
@@ -280,7 +280,7 @@ def run_b200(args):
             e1.record(stream)
             stream.synchronize()
             t = e0.elapsed_time(e1) * 1e-3 / (reps * R)          # seconds per layer
-            nl = 1 if M <= 2 else 1 + (M + 15) // 16
+            nl = 1 if M <= 8 else 1 + (M + 7) // 8
             per_case.append({"K": K, "N": N, "M": M, "us_per_layer": t * 1e6, "launches_per_layer": nl,
                              "gbs": algorithmic_bytes(K, N, M) / t / 1e9,
                              "frac_hbm_measured": algorithmic_bytes(K, N, M) / t / 1e9 / pk["hbm_gbs"],

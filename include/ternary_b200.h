@@ -139,6 +139,7 @@ int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K, int64_t l
  * prologue (8 tokens per pass over the weights), TMA-staged packed rows, in-register unpack,
  * mma.sync.m16n8k32 (u8 x s8) integer dot products, fused epilogue.  K <= 20480. */
 #define TB200_GEMV_MAX_M 32
+#define TB200_GEMV_FUSED_M 8 /* tokens per pass over the weights; up to here tb200_linear_forward is ONE launch */
 /* flags bit 0: programmatic dependent launch.  The kernel prefetches its packed weights
  * before waiting for the previous kernel in the stream (which normally produces x); the
  * caller asserts that the previous kernel does NOT write `packed`. */
@@ -150,8 +151,8 @@ int tb200_gemv(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
                int32_t* acc_out, float* sx_out, int8_t* qx_out, int flags, void* stream);
 
 /* Decode GEMV on activations pre-quantised by tb200_quant_act_i8(layout 1): one pass over the
- * weights per 16 tokens (8 when K > 4096).  tb200_gemv quantises in its prologue instead, which
- * every CTA repeats: preferable for 1-2 tokens only. */
+ * weights per 8 tokens.  tb200_gemv quantises in its prologue instead, which every CTA repeats
+ * (each CTA reads all M*K activations from L2): preferable up to 8 tokens. */
 int tb200_gemv_q(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx,
                  int64_t M, int64_t K,
                  const uint8_t* packed, int64_t ld_packed, int64_t N,
@@ -183,7 +184,7 @@ int tb200_gemm_i8(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_
                   void* out, int out_dtype, int64_t ldo,
                   int32_t* acc_out, void* stream);
 
-/* Whole layer by token count: M <= 2 tb200_gemv (fused quantisation); M <= 32 quantise
+/* Whole layer by token count: M <= 8 tb200_gemv (fused quantisation, one launch); M <= 32 quantise
  * (layout 1) + tb200_gemv_q; larger M quantise (layout 1) + tb200_gemm_i8.
  * workspace: tb200_linear_workspace(M,K) bytes, 256-byte aligned. */
 size_t tb200_linear_workspace(int64_t M, int64_t K);

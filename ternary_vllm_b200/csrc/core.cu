@@ -65,8 +65,8 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dt, int rank, const vo
         }
         enc = (EncodeTiledFn)fp;
     }
-    cuuint64_t d[3] = {1, 1, 1}, st[2] = {0, 0};
-    cuuint32_t bx[3] = {1, 1, 1}, es[3] = {1, 1, 1};
+    cuuint64_t d[5] = {1, 1, 1, 1, 1}, st[4] = {0, 0, 0, 0};
+    cuuint32_t bx[5] = {1, 1, 1, 1, 1}, es[5] = {1, 1, 1, 1, 1};
     for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
     for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
     CUresult r = enc(map, dt, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,

@@ -22,18 +22,23 @@
 // Reference semantics: ScaledTernaryLinear.forward (binary/modules.py:101-109) and
 // ops.ternary_matmul (impl/tf/moondream/ternary.py:279-281).
 #include <mutex>
+#include <cstdlib>
 #include "tma.cuh"
 
 namespace tb200 {
 
 constexpr int GV_ROWS = 16;                       // rows per tile = MMA M
 constexpr int GV_SLICE = 1024;                    // packed bytes per row per tile (4096 weights)
-constexpr int GV_SEG = 128;                       // bytes per row per TMA box / per warp
+constexpr int GV_SEG = 128;                       // bytes per row per TMA box / per consumer warp
 constexpr int GV_TILE_BYTES = GV_ROWS * GV_SLICE; // 16 KB
-constexpr int GV_CWARPS = GV_SLICE / GV_SEG;      // 8 consumer warps, one per segment
-constexpr int GV_THREADS = (GV_CWARPS + 1) * 32;  // + producer warp
-constexpr int GV_MAX_STAGES = 6;
-constexpr int GV_TOK = 8;                         // tokens per MMA n-tile
+constexpr int GV_CWARPS = GV_SLICE / GV_SEG;      // 8 consumer warps, one per 128-byte K segment
+constexpr int GV_CTHREADS = GV_CWARPS * 32;
+constexpr int GV_WARP_PRODUCER = GV_CWARPS;       // warp 8: TMA producer
+constexpr int GV_WARP_EPILOGUE = GV_CWARPS + 1;   // warp 9: K-partial reduction + fused epilogue
+constexpr int GV_THREADS = (GV_CWARPS + 2) * 32;
+constexpr int GV_MAX_STAGES = 12;
+constexpr int GV_SLOTS = 4;                       // partial-sum slots (4 KB each) between consumers and epilogue warp
+constexpr int GV_TOK = 8;                         // tokens per pass = MMA N
 
 struct GemvParams {
     const void* x; int64_t ldx; int64_t stride_x;            // raw activations (fused quantisation)
@@ -41,23 +46,28 @@ struct GemvParams {
     const float* sx_in; const int32_t* sumq_in; int64_t stride_s;
     const float* scale; const float* bias; int64_t stride_sb;
     void* out; int64_t ldo; int64_t stride_out;
-    int32_t* acc_out; float* sx_out; int8_t* qx_out;
+    int32_t* acc_out;
     int64_t N, K;
-    int M;            // tokens in this launch (<= 8*NT)
+    int M;            // tokens in this launch (<= 8)
     int nks;          // k-slices of 4096 weights
     int row_blocks;   // ceil(N / 16)
     int nrb;          // row blocks per CTA = ceil(row_blocks / gridDim.x)
     int stages;       // ring depth
+    int inflight;     // tiles requested ahead of the last one that has landed (paces the prefetch)
     float clip_val;
     int pdl;
+    int one_box;      // the tensor map is 4-D (word, row, segment, layer): one 16 KB box per tile
+    int dbg;          // experiment switches (TB200_GEMV_DBG): 1 skip MMAs, 2 skip x load+quantisation, 4 skip epilogue stores
     bool xvec;
-    long long* trace;   // debug: per-CTA clock64 stamps (tb200_debug_set_trace), normally null
+    long long* trace;   // debug: per-CTA globaltimer stamps (tb200_debug_set_trace), normally null
     // tensor-parallel gather fused into the epilogue: when n_peers > 0 the output element is stored into every
     // rank's [M, ldo] buffer (peer-mapped NVLink addresses, already offset to this rank's column block)
     void* peers[8]; int n_peers;
 };
 static long long* g_trace = nullptr;
-#define GV_STAMP(slot) do { if (p.trace && threadIdx.x == 0 && blockIdx.y == 0) p.trace[blockIdx.x * 16 + (slot)] = clock64(); } while (0)
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define GV_STAMP(slot) do { if (p.trace && blockIdx.y == 0) { if ((slot) == 0 || (slot) == 15 || (slot) == 1) p.trace[blockIdx.x * 64 + (slot)] = (long long)gtimer(); p.trace[blockIdx.x * 64 + 16 + (slot)] = clock64(); } } while (0)
+#define GV_CLK(slot) do { if (p.trace && blockIdx.y == 0) p.trace[blockIdx.x * 64 + 32 + (slot)] = clock64(); } while (0)
 
 // q = clamp(rint(v * inv), +-127): the activation quantiser (ternary_b200.h, tb200_quant_act_i8)
 // rint() and the float->int conversion are done by adding 1.5*2^23 (the FADD rounds to nearest-even
@@ -68,40 +78,33 @@ __device__ __forceinline__ int quant_mul(float v, float inv) {
     return __float_as_int(__fadd_rn(r, 12582912.0f)) - 0x4B400000;
 }
 
-// 16 consecutive activations of one token as fp32 (zero beyond K); vector loads when aligned
-template <typename XT>
-__device__ __forceinline__ void load16(const XT* __restrict__ xr, int64_t g, int64_t K, bool vec, float v[16]) {
-    if (vec && 16 * g + 16 <= K) {
-        if (sizeof(XT) == 4) {
-            const float4* q = reinterpret_cast<const float4*>(xr + 16 * g);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                float4 f = q[j];
-                v[4 * j] = f.x; v[4 * j + 1] = f.y; v[4 * j + 2] = f.z; v[4 * j + 3] = f.w;
-            }
-        } else {
+// 16 consecutive activations of one token in their storage type (zero beyond K): NV 16-byte vectors.
+// VEC: rows are 16-byte aligned and K % 16 == 0 (the hot instantiation: vector loads only, small code).
+template <typename XT> struct Raw16 { static constexpr int NV = sizeof(XT); uint4 v[NV]; };   // 2 (16-bit) or 4 (fp32) vectors
+template <typename XT, bool VEC>
+__device__ __forceinline__ void load_raw16(const XT* __restrict__ xr, int64_t g, int64_t K, Raw16<XT>& r) {
+    if (VEC) {
+        if (16 * g < K) {
             const uint4* q = reinterpret_cast<const uint4*>(xr + 16 * g);
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                uint4 u = q[j];
-                const XT* e = reinterpret_cast<const XT*>(&u);
+            for (int j = 0; j < Raw16<XT>::NV; ++j) r.v[j] = q[j];
+        } else {
 #pragma unroll
-                for (int t = 0; t < 8; ++t) v[8 * j + t] = to_f32(e[t]);
-            }
+            for (int j = 0; j < Raw16<XT>::NV; ++j) r.v[j] = make_uint4(0u, 0u, 0u, 0u);
         }
     } else {
-#pragma unroll
+        XT* e = reinterpret_cast<XT*>(r.v);
+#pragma unroll 1
         for (int t = 0; t < 16; ++t) {
-            int64_t k = 16 * g + t;
-            v[t] = k < K ? to_f32(xr[k]) : 0.0f;
+            const int64_t k = 16 * g + t;
+            e[t] = k < K ? xr[k] : from_f32<XT>(0.0f);
         }
     }
 }
+template <typename XT>
+__device__ __forceinline__ float raw_get(const Raw16<XT>& r, int e) { return to_f32(reinterpret_cast<const XT*>(r.v)[e]); }
 
-__device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(GV_CWARPS * 32) : "memory"); }
-// the 8 consumer warps work as two groups of 4 that alternate row blocks (one reduces while the other issues MMAs)
-constexpr int GV_GWARPS = GV_CWARPS / 2;
-__device__ __forceinline__ void group_bar(int grp) { asm volatile("bar.sync %0, %1;" ::"r"(3 + grp), "n"(GV_GWARPS * 32) : "memory"); }
+__device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(GV_CTHREADS) : "memory"); }
 
 // D(16x8,s32) += A(16x32,u8 row) * B(32x8,s8 col)
 __device__ __forceinline__ void imma_16832(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
@@ -112,66 +115,79 @@ __device__ __forceinline__ void imma_16832(int (&c)[4], uint32_t a0, uint32_t a1
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// Shared-memory image of the quantised activations, in 32-bit words.  For token n (0..7 of an
-// n-tile), 16-byte chunk c of the packed row (64 weights), packed word j (16 weights) and field
-// i, the word holds bytes b=0..3 = q[64c + 16j + 4b + i].  Lane (g = lane>>2, t = lane&3) of
-// warp `seg` reads, for its chunk pair p, the 4 words j=0..3 of (c = 8*seg + 2t + p, i, n = g)
-// with one LDS.128; lane l reads the l-th 16 bytes of a 512-byte run (conflict-free).  Token
-// slots >= M are never initialised: column n of the MMA only feeds output column n.
-__device__ __forceinline__ int xq_word(int c, int j, int i, int n) {
-    const int sg = c >> 3, lc = c & 7, t = lc >> 1, pp = lc & 1;
-    return ((((sg * 2 + pp) * 4 + i) * GV_TOK + n) * 4 + t) * 4 + j;     // uint4 index = ... + lane (lane = 4n + t)
+// Shared-memory image of the quantised activations of the M tokens of this pass, in 32-bit words.  For
+// 16-byte chunk c of the packed row (64 weights; c counts across k-slices), packed word j (16 weights),
+// field i and token n, the word holds bytes b=0..3 = q[n][64c + 16j + 4b + i]: the four activations that
+// meet field i of the four bytes of packed word j.  The words j=0..3 form one uint4, which is exactly
+// the B fragments {b0,b1} of two m16n8k32 MMAs for lane (g = n, t) with chunk c = 8*segment + 2t + p.
+// uint4 index = (((segment*2 + p)*4 + i) * M + n) * 4 + t.
+__device__ __forceinline__ int xq_vec(int sg, int pp, int i, int n, int t, int M) {
+    return ((((sg * 2 + pp) * 4 + i) * M + n) << 2) + t;
 }
 
-template <typename XT, typename OT, int NT, bool FUSED>
+template <typename XT, typename OT, bool FUSED, bool VEC>
 __global__ void __launch_bounds__(GV_THREADS, 2)
 gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;         // SWIZZLE_128B boxes: 1024-B aligned
     uint8_t* gbase = smem_dyn + (base - smem_u32(smem_dyn));
-    // layout: ring[stages][16 KB] | xq[NT][8 tokens][nks*4096] | slots[2][NT][8 warps][32] uint4 | sx | sumq | red | barriers
+    // layout: ring[stages][16 KB] | image[nks*4096*M] | slots[2][8 warps][32] uint4 | sx | red_f | red_i | barriers | scale | bias
     const uint32_t sRing = base;
-    const int xq_words_nt = p.nks * 4096 * GV_TOK / 4;
     uint32_t* xq = reinterpret_cast<uint32_t*>(gbase + p.stages * GV_TILE_BYTES);
-    uint4* slots = reinterpret_cast<uint4*>(xq + (size_t)NT * xq_words_nt);
-    float* sh_sx = reinterpret_cast<float*>(slots + 2 * NT * GV_CWARPS * 32);   // slots: [2 groups][2 bufs][NT][4 warps][32]
-    int* sh_sumq = reinterpret_cast<int*>(sh_sx + NT * GV_TOK);
-    float* red_f = reinterpret_cast<float*>(sh_sumq + NT * GV_TOK);       // [8 tokens][8 warps]
-    int* red_i = reinterpret_cast<int*>(red_f + GV_TOK * GV_CWARPS);
+    uint4* slots = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(xq) + (size_t)p.nks * 4096 * p.M);
+    float* sh_sx = reinterpret_cast<float*>(slots + GV_SLOTS * GV_CTHREADS);
+    float* red_f = sh_sx + GV_TOK;                                        // [8 tokens][8 warps]
+    int* red_i = reinterpret_cast<int*>(red_f + GV_TOK * GV_CWARPS);      // [8 tokens][8 warps]
     uint64_t* bars = reinterpret_cast<uint64_t*>(red_i + GV_TOK * GV_CWARPS);
-    float* sh_scale = reinterpret_cast<float*>(bars + 2 * GV_MAX_STAGES); // [nrb][16] this CTA's rows
+    float* sh_scale = reinterpret_cast<float*>(bars + 2 * GV_MAX_STAGES + 2 * GV_SLOTS);   // [nrb][16] this CTA's rows
     float* sh_bias = sh_scale + p.nrb * GV_ROWS;
     const uint32_t sBar = smem_u32(bars);
     auto bar_full = [&](int s) { return sBar + 8u * s; };
     auto bar_empty = [&](int s) { return sBar + 8u * (GV_MAX_STAGES + s); };
+    auto slot_full = [&](int s) { return sBar + 8u * (2 * GV_MAX_STAGES + s); };
+    auto slot_empty = [&](int s) { return sBar + 8u * (2 * GV_MAX_STAGES + GV_SLOTS + s); };
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int layer = blockIdx.y;
-    GV_STAMP(0);
-
+    const int M = p.M;
     if (threadIdx.x == 0) {
+        GV_STAMP(0);
         tma_prefetch_desc(&map_w);
         for (int s = 0; s < p.stages; ++s) {
             mbar_init(bar_full(s), 1);
-            mbar_init(bar_empty(s), GV_GWARPS);
+            mbar_init(bar_empty(s), GV_CWARPS);
+        }
+        for (int s = 0; s < GV_SLOTS; ++s) {
+            mbar_init(slot_full(s), GV_CWARPS);
+            mbar_init(slot_empty(s), 1);
         }
         mbar_fence_init();
     }
     __syncthreads();
-    GV_STAMP(10);    // barriers initialised
     if (p.pdl) asm volatile("griddepcontrol.launch_dependents;");
 
-    if (warp == GV_CWARPS) {
+    if (warp == GV_WARP_PRODUCER) {
         // ===================== producer: weights do not depend on the previous kernel =====================
         // Without PDL the activations are requested at the same time as the weights and would queue
         // behind a ring-full of weight traffic: let the consumers issue their x loads first.
-        if (!p.pdl) asm volatile("bar.sync 2, %0;" ::"n"(GV_THREADS) : "memory");
+        if (!p.pdl) asm volatile("bar.sync 2, %0;" ::"n"(GV_CTHREADS + 32) : "memory");
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;
+            int idx = 0, ls = 0; uint32_t lph = 0;     // (ls, lph): stage and phase of tile idx - inflight
             for (int rb = blockIdx.x; rb < p.row_blocks; rb += gridDim.x) {
-                for (int ks = 0; ks < p.nks; ++ks) {
+                for (int ks = 0; ks < p.nks; ++ks, ++idx) {
+                    // Pacing: at most `inflight` tiles outstanding per SM.  Requesting the whole share at once parks
+                    // ~12 MB in the memory system and the (small, latency-critical) activation loads of the kernel
+                    // that is running queue behind it.
+                    if (idx >= p.inflight) {
+                        mbar_wait(bar_full(ls), lph);
+                        if (++ls == p.stages) { ls = 0; lph ^= 1u; }
+                    }
                     mbar_wait(bar_empty(s), ph ^ 1u);
                     mbar_arrive_expect_tx(bar_full(s), GV_TILE_BYTES);
+                    if (p.one_box) {
+                        tma_load_4d(sRing + s * GV_TILE_BYTES, &map_w, bar_full(s), 0, rb * GV_ROWS, ks * GV_CWARPS, layer);
+                    } else
 #pragma unroll
                     for (int sg = 0; sg < GV_CWARPS; ++sg)
                         tma_load_3d(sRing + s * GV_TILE_BYTES + sg * (GV_ROWS * GV_SEG), &map_w, bar_full(s),
@@ -179,276 +195,323 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
                     if (++s == p.stages) { s = 0; ph ^= 1u; }
                 }
             }
+            GV_STAMP(10);
         }
+        return;
+    }
+
+    if (warp == GV_WARP_EPILOGUE) {
+        // ===================== epilogue warp: sums the 8 K-partials of a row block, scale/bias/clip, store ===========
+        {   // this CTA's per-row scale and bias are weights: fetched before the dependency wait
+            const float* scale_g = p.scale ? p.scale + layer * p.stride_sb : nullptr;
+            const float* bias_g = p.bias ? p.bias + layer * p.stride_sb : nullptr;
+            for (int i = lane; i < p.nrb * GV_ROWS; i += 32) {
+                const int64_t row = ((int64_t)blockIdx.x + (int64_t)(i >> 4) * gridDim.x) * GV_ROWS + (i & 15);
+                sh_scale[i] = (scale_g && row < p.N) ? scale_g[row] : 1.0f;
+                sh_bias[i] = (bias_g && row < p.N) ? bias_g[row] : 0.0f;
+            }
+        }
+        if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+        __syncwarp();
+        OT* out = reinterpret_cast<OT*>(p.out) + layer * p.stride_out;
+        const int g = lane >> 2, t = lane & 3;
+        float sx[2] = {0.0f, 0.0f}; int sumq[2] = {0, 0};
+        bool have_tok = false, wrote_peer = false;
+        int rbi = 0;
+        for (int rb = blockIdx.x; rb < p.row_blocks && !(p.dbg & 16); rb += gridDim.x, ++rbi) {
+            const int slot = rbi % GV_SLOTS;
+            mbar_wait(slot_full(slot), (uint32_t)(rbi / GV_SLOTS) & 1u);
+            if (lane == 0 && rb + (int)gridDim.x >= p.row_blocks) GV_STAMP(11);     // last row block handed over
+            if (!have_tok) {      // the consumers' prologue is complete: per-token scale and sum of codes
+                if (lane == 0) GV_STAMP(9);
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int tok = 2 * t + e;
+                    if (tok < M) {
+                        if (FUSED) {
+                            sx[e] = sh_sx[tok];
+                            int v = 0;
+#pragma unroll
+                            for (int w = 0; w < GV_CWARPS; ++w) v += red_i[tok * GV_CWARPS + w];
+                            sumq[e] = v;
+                        } else {
+                            sx[e] = p.sx_in[layer * p.stride_s + tok];
+                            sumq[e] = p.sumq_in[layer * p.stride_s + tok];
+                        }
+                    }
+                }
+                have_tok = true;
+            }
+            const uint4* sl = slots + slot * GV_CTHREADS + lane;
+            int v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+#pragma unroll
+            for (int w = 0; w < GV_CWARPS; ++w) {
+                const uint4 u = sl[w * 32];
+                v0 += (int)u.x; v1 += (int)u.y; v2 += (int)u.z; v3 += (int)u.w;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(slot_empty(slot));
+            if (lane == 0 && rb + (int)gridDim.x >= p.row_blocks) GV_STAMP(12);     // last partials summed
+            // accumulator fragment: v0 (row g, tok 2t), v1 (row g, tok 2t+1), v2 (row g+8, tok 2t), v3 (row g+8, tok 2t+1)
+            const int vv[4] = {v0, v1, v2, v3};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int rl = g + 8 * (q >> 1), e = q & 1, tok = 2 * t + e;
+                const int64_t row = (int64_t)rb * GV_ROWS + rl;
+                if (row < p.N && tok < M && !(p.dbg & 4)) {
+                    const int a = vv[q] - sumq[e];
+                    if (p.acc_out && layer == 0) p.acc_out[(int64_t)tok * p.N + row] = a;
+                    const float tv = __fmul_rn((float)a, sx[e]);
+                    const float y = epilogue(tv, sh_scale[rbi * GV_ROWS + rl], sh_bias[rbi * GV_ROWS + rl], p.clip_val);
+                    const OT yv = from_f32<OT>(y);
+                    if (p.n_peers == 0) {
+                        out[(int64_t)tok * p.ldo + row] = yv;
+                    } else {
+#pragma unroll 1
+                        for (int r = 0; r < p.n_peers; ++r)     // one small store per peer over NVLink (P2P-mapped memory)
+                            reinterpret_cast<OT*>(p.peers[r])[(int64_t)tok * p.ldo + row] = yv;
+                        wrote_peer = true;
+                    }
+                }
+            }
+        }
+        if (wrote_peer) __threadfence_system();      // peer stores are visible system-wide before the grid completes
+        if (lane == 0) GV_STAMP(15);
         return;
     }
 
     // ===================== consumers =====================
     const int ct = threadIdx.x;                       // 0..255
     const int g = lane >> 2, t = lane & 3;
-    // this CTA's per-row scale and bias (weights: independent of the previous kernel): loads are issued
-    // now, the values are parked in shared memory at the end of the prologue
-    float sb_scale[2], sb_bias[2];
-    {
-        const float* scale_g = p.scale ? p.scale + layer * p.stride_sb : nullptr;
-        const float* bias_g = p.bias ? p.bias + layer * p.stride_sb : nullptr;
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-            const int i = ct + u * GV_CWARPS * 32;
-            const int64_t row = ((int64_t)blockIdx.x + (int64_t)(i >> 4) * gridDim.x) * GV_ROWS + (i & 15);
-            const bool ok = i < p.nrb * GV_ROWS && row < p.N;
-            sb_scale[u] = (scale_g && ok) ? scale_g[row] : 1.0f;
-            sb_bias[u] = (bias_g && ok) ? bias_g[row] : 0.0f;
-        }
-    }
     if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");   // x comes from the previous kernel
-    GV_STAMP(14);    // previous kernel complete (PDL) / consumers start
+    if (ct == 0) GV_STAMP(1);
+    bool released = p.pdl != 0;                       // producer already running under PDL
+    auto release_producer = [&]() {
+        if (!released) { asm volatile("bar.arrive 2, %0;" ::"n"(GV_CTHREADS + 32) : "memory"); released = true; }
+    };
 
+    int lsum_tok[GV_TOK];                             // this thread's sum of codes per token (reduced after the image barrier)
+#pragma unroll
+    for (int m = 0; m < GV_TOK; ++m) lsum_tok[m] = 0;
     if (FUSED) {
         const XT* x = reinterpret_cast<const XT*>(p.x) + layer * p.stride_x;
-        const int groups = p.nks * 256;                      // 16-element groups incl. zero padding up to the slice
-        constexpr int GC = 1;                                // groups cached in registers per thread (K <= 4096)
-        const bool cached = groups <= GC * GV_CWARPS * 32;
-        if (!cached && !p.pdl) asm volatile("bar.arrive 2, %0;" ::"n"(GV_THREADS) : "memory");
-        for (int m = 0; m < p.M; ++m) {
-            const XT* xr = x + (int64_t)m * p.ldx;
-            float vc[GC][16];
-            float amax = 0.0f;
-            if (cached) {
+        constexpr int TB = sizeof(XT) == 4 ? 2 : 4;           // tokens whose loads are in flight together (32 registers)
 #pragma unroll
-                for (int u = 0; u < GC; ++u) {
-                    const int gi = ct + u * GV_CWARPS * 32;
-                    if (gi < groups) load16<XT>(xr, gi, p.K, p.xvec, vc[u]);
-                }
-                // the activation loads are in flight: now let the producer start the weight stream
-                if (m == 0 && !p.pdl) asm volatile("bar.arrive 2, %0;" ::"n"(GV_THREADS) : "memory");
+        for (int mb = 0; mb < GV_TOK / TB; ++mb) {
+            const int m0 = mb * TB;
+            if (m0 >= M || (p.dbg & 2)) break;
+            Raw16<XT> raw[TB];
+            float amax[TB];
 #pragma unroll
-                for (int u = 0; u < GC; ++u) {
-                    const int gi = ct + u * GV_CWARPS * 32;
-                    if (gi < groups) {
+            for (int tb = 0; tb < TB; ++tb) amax[tb] = 0.0f;
+            // pass A: row maxima.  Thread ct owns 16-element group ct of every k-slice; the last slice stays in registers.
+#pragma unroll 1
+            for (int u = 0; u < p.nks; ++u) {
 #pragma unroll
-                        for (int e = 0; e < 16; ++e) amax = fmaxf(amax, fabsf(vc[u][e]));
+                for (int tb = 0; tb < TB; ++tb)
+                    if (m0 + tb < M) load_raw16<XT, VEC>(x + (int64_t)(m0 + tb) * p.ldx, u * GV_CTHREADS + ct, p.K, raw[tb]);
+                release_producer();
+#pragma unroll
+                for (int tb = 0; tb < TB; ++tb)
+                    if (m0 + tb < M) {
+#pragma unroll
+                        for (int e = 0; e < 16; ++e) amax[tb] = fmaxf(amax[tb], fabsf(raw_get<XT>(raw[tb], e)));
                     }
-                }
-            } else {
-                for (int gi = ct; (int64_t)gi * 16 < p.K; gi += GV_CWARPS * 32) {
-                    float v[16];
-                    load16<XT>(xr, gi, p.K, p.xvec, v);
+            }
 #pragma unroll
-                    for (int e = 0; e < 16; ++e) amax = fmaxf(amax, fabsf(v[e]));
+            for (int tb = 0; tb < TB; ++tb) {
+                if (m0 + tb < M) {
+                    // non-negative floats order like their bit patterns: one REDUX instead of five shuffles
+                    const uint32_t a = __reduce_max_sync(0xffffffffu, __float_as_uint(amax[tb]));
+                    if (lane == 0) red_f[(m0 + tb) * GV_CWARPS + warp] = __uint_as_float(a);
                 }
             }
-            amax = warp_max(amax);
-            if (lane == 0) red_f[m * GV_CWARPS + warp] = amax;
-            GV_STAMP(11);    // activations arrived, amax of this warp known
+            if (ct == 0 && m0 == 0) GV_STAMP(2);     // activations arrived
             consumer_bar();
-            GV_STAMP(12);
-            float v = red_f[m * GV_CWARPS];
+            if (ct == 0 && m0 == 0) GV_STAMP(6);     // every warp's activations arrived
+            float inv[TB];
 #pragma unroll
-            for (int w = 1; w < GV_CWARPS; ++w) v = fmaxf(v, red_f[m * GV_CWARPS + w]);
-            const float sxm = v > 0.0f ? __fdiv_rn(v, 127.0f) : 1.0f;
-            const float inv = v > 0.0f ? __fdiv_rn(127.0f, v) : 1.0f;
-            if (ct == 0) {
-                sh_sx[m] = sxm;
-                if (p.sx_out && blockIdx.x == 0 && layer == 0) p.sx_out[m] = sxm;
-            }
-            int lsum = 0;
-            auto emit = [&](int gi, const float (&v16)[16]) {
-                int qv[16];
-#pragma unroll
-                for (int e = 0; e < 16; ++e) {
-                    qv[e] = quant_mul(v16[e], inv);          // v is 0 beyond K -> q = 0
-                    lsum += qv[e];
+            for (int tb = 0; tb < TB; ++tb) {
+                inv[tb] = 1.0f;
+                if (m0 + tb < M) {
+                    const int m = m0 + tb;
+                    const float4 r0 = *reinterpret_cast<const float4*>(red_f + m * GV_CWARPS);
+                    const float4 r1 = *reinterpret_cast<const float4*>(red_f + m * GV_CWARPS + 4);
+                    const float v = fmaxf(fmaxf(fmaxf(r0.x, r0.y), fmaxf(r0.z, r0.w)), fmaxf(fmaxf(r1.x, r1.y), fmaxf(r1.z, r1.w)));
+                    inv[tb] = v > 0.0f ? __fdiv_rn(127.0f, v) : 1.0f;
+                    if (ct == 0) sh_sx[m] = v > 0.0f ? __fdiv_rn(v, 127.0f) : 1.0f;
                 }
-                if (p.qx_out && blockIdx.x == 0 && layer == 0) {
+            }
+            // pass B: quantise, last slice first (its values are still in registers).  |x*inv| < 127.5 by construction
+            // (|x| <= amax, two roundings), so the clamp of the definition never binds and is not evaluated.
+#pragma unroll 1
+            for (int u = p.nks - 1; u >= 0; --u) {
+                const int gi = u * GV_CTHREADS + ct;
+                const int c = gi >> 2, j = gi & 3, lc = c & 7;
 #pragma unroll
-                    for (int e = 0; e < 16; ++e) {
-                        int64_t k = 16 * (int64_t)gi + e;
-                        if (k < p.K) p.qx_out[(int64_t)m * p.K + k] = (int8_t)qv[e];
+                for (int tb = 0; tb < TB; ++tb) {
+                    if (m0 + tb < M) {
+                        if (u != p.nks - 1) load_raw16<XT, VEC>(x + (int64_t)(m0 + tb) * p.ldx, gi, p.K, raw[tb]);
+                        uint32_t qb[16];      // low byte = two's-complement code (rint via the 1.5*2^23 trick)
+#pragma unroll
+                        for (int e = 0; e < 16; ++e)
+                            qb[e] = __float_as_uint(__fadd_rn(__fmul_rn(raw_get<XT>(raw[tb], e), inv[tb]), 12582912.0f));
+                        int ls = lsum_tok[m0 + tb];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {  // word i = elements i, 4+i, 8+i, 12+i (field i of bytes 0..3)
+                            const uint32_t w = __byte_perm(__byte_perm(qb[i], qb[4 + i], 0x0040), __byte_perm(qb[8 + i], qb[12 + i], 0x0040), 0x5410);
+                            ls = __dp4a((int)w, 0x01010101, ls);
+                            xq[xq_vec(c >> 3, lc & 1, i, m0 + tb, lc >> 1, M) * 4 + j] = w;
+                        }
+                        lsum_tok[m0 + tb] = ls;
                     }
                 }
-                const int c = gi >> 2, j = gi & 3;
-#pragma unroll
-                for (int i = 0; i < 4; ++i)   // word i = elements i, 4+i, 8+i, 12+i (field i of bytes 0..3)
-                    xq[xq_word(c, j, i, m)] = (uint32_t)(qv[i] & 0xff) | ((uint32_t)(qv[4 + i] & 0xff) << 8) |
-                                              ((uint32_t)(qv[8 + i] & 0xff) << 16) | ((uint32_t)(qv[12 + i] & 0xff) << 24);
-            };
-            if (cached) {
-#pragma unroll
-                for (int u = 0; u < GC; ++u) {
-                    const int gi = ct + u * GV_CWARPS * 32;
-                    if (gi < groups) emit(gi, vc[u]);
-                }
-            } else {
-                for (int gi = ct; gi < groups; gi += GV_CWARPS * 32) {
-                    float v16[16];
-                    load16<XT>(xr, gi, p.K, p.xvec, v16);      // zero beyond K
-                    emit(gi, v16);
-                }
             }
-            lsum = warp_sum(lsum);
-            if (lane == 0) red_i[m * GV_CWARPS + warp] = lsum;
-            GV_STAMP(13);    // quantised image written
         }
     } else {
         // pre-quantised activations (tb200_quant_act_i8 layout 1): rows of kperm words
         const int8_t* q = p.qx + layer * p.stride_q;
         const int groups = p.nks * 256, have = (int)(p.ldq >> 4);   // zero padding up to the slice
-        const int total = p.M * groups;
-        bool arrived = p.pdl != 0;
-        for (int base_i = 0; base_i < total; base_i += 8 * GV_CWARPS * 32) {
+        const int total = M * groups;
+        for (int base_i = 0; base_i < total; base_i += 8 * GV_CTHREADS) {
             uint4 u[8];
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
-                const int idx = base_i + r * GV_CWARPS * 32 + ct;
+                const int idx = base_i + r * GV_CTHREADS + ct;
                 const int m = idx / groups, gi = idx - m * groups;
                 u[r] = (idx < total && gi < have) ? *reinterpret_cast<const uint4*>(q + (int64_t)m * p.ldq + 16 * (int64_t)gi)
                                                    : make_uint4(0u, 0u, 0u, 0u);
             }
-            if (!arrived) {   // first batch of activation loads is in flight: release the weight stream
-                asm volatile("bar.arrive 2, %0;" ::"n"(GV_THREADS) : "memory");
-                arrived = true;
-            }
+            release_producer();
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
-                const int idx = base_i + r * GV_CWARPS * 32 + ct;
+                const int idx = base_i + r * GV_CTHREADS + ct;
                 if (idx < total) {
                     const int m = idx / groups, gi = idx - m * groups;
-                    const int c = gi >> 2, j = gi & 3;
-                    uint32_t* dst = xq + (size_t)(m >> 3) * xq_words_nt;
-                    dst[xq_word(c, j, 0, m & 7)] = u[r].x;
-                    dst[xq_word(c, j, 1, m & 7)] = u[r].y;
-                    dst[xq_word(c, j, 2, m & 7)] = u[r].z;
-                    dst[xq_word(c, j, 3, m & 7)] = u[r].w;
+                    const int c = gi >> 2, j = gi & 3, lc = c & 7;
+                    const uint32_t w4[4] = {u[r].x, u[r].y, u[r].z, u[r].w};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) xq[xq_vec(c >> 3, lc & 1, i, m, lc >> 1, M) * 4 + j] = w4[i];
                 }
             }
         }
-        if (!arrived) asm volatile("bar.arrive 2, %0;" ::"n"(GV_THREADS) : "memory");
-        if (ct < p.M) {
-            sh_sx[ct] = p.sx_in[layer * p.stride_s + ct];
-            sh_sumq[ct] = p.sumq_in[layer * p.stride_s + ct];
-        }
     }
+    release_producer();
+    if (ct == 0) GV_STAMP(3);     // quantised image written
+    consumer_bar();               // activation image (and sh_sx) complete
+    if (ct == 0) GV_STAMP(7);
 
-    OT* out = reinterpret_cast<OT*>(p.out) + layer * p.stride_out;
+    // B fragments of this warp's K segment: 32 registers, loaded once when K <= 4096
+    const uint4* xqv = reinterpret_cast<const uint4*>(xq);
+    uint4 bq[2][4];
+    auto load_b = [&](int ks) {
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-        const int i = ct + u * GV_CWARPS * 32;
-        if (i < p.nrb * GV_ROWS) { sh_scale[i] = sb_scale[u]; sh_bias[i] = sb_bias[u]; }
-    }
-    for (int i = ct + 2 * GV_CWARPS * 32; i < p.nrb * GV_ROWS; i += GV_CWARPS * 32) {   // > 32 row blocks per CTA
-        const int64_t row = ((int64_t)blockIdx.x + (int64_t)(i >> 4) * gridDim.x) * GV_ROWS + (i & 15);
-        sh_scale[i] = (p.scale && row < p.N) ? p.scale[layer * p.stride_sb + row] : 1.0f;
-        sh_bias[i] = (p.bias && row < p.N) ? p.bias[layer * p.stride_sb + row] : 0.0f;
-    }
-    consumer_bar();      // activation image, scale/bias and the per-warp sum_q partials are visible
-    if (FUSED && ct < p.M) {   // consumed only by the epilogue, which sits behind another barrier
-        int tsum = 0;
+        for (int pp = 0; pp < 2; ++pp)
 #pragma unroll
-        for (int w = 0; w < GV_CWARPS; ++w) tsum += red_i[ct * GV_CWARPS + w];
-        sh_sumq[ct] = tsum;
+            for (int i = 0; i < 4; ++i)
+                bq[pp][i] = g < M ? xqv[xq_vec(ks * GV_CWARPS + warp, pp, i, g, t, M)] : make_uint4(0u, 0u, 0u, 0u);
+    };
+    load_b(0);
+    if (FUSED) {                  // per-token sum of codes: needed by the epilogue warp only, off the critical path
+#pragma unroll
+        for (int m = 0; m < GV_TOK; ++m)
+            if (m < M) {
+                const int v = __reduce_add_sync(0xffffffffu, lsum_tok[m]);
+                if (lane == 0) red_i[m * GV_CWARPS + warp] = v;
+            }
     }
-    if (FUSED) consumer_bar();
-    GV_STAMP(1);     // prologue done
+    if (ct == 0) GV_STAMP(8);
 
-    const int grp = warp >> 2, wl = warp & 3, gt = ct & (GV_GWARPS * 32 - 1);
-    bool wrote_peer = false;
-    int s = 0; uint32_t ph = 0; int buf = 0; int tile_no = 0; int rbi = 0;
-    for (int rb = blockIdx.x; rb < p.row_blocks; rb += gridDim.x, ++rbi) {
-        if ((rbi & 1) != grp) {                       // the other group's row block: just track the ring
-            s += p.nks;
-            while (s >= p.stages) { s -= p.stages; ph ^= 1u; }
-            continue;
-        }
-        int acc[NT][4][4];
+    // Main loop, software-pipelined: the packed rows of tile i+1 are fetched into registers (and its ring stage
+    // released) between the two halves of the MMAs of tile i.
+    const uint32_t sSeg = warp * (GV_ROWS * GV_SEG) + g * GV_SEG;
+    const uint32_t phys0 = ((2 * t) ^ g) << 4, phys1 = ((2 * t + 1) ^ g) << 4;   // SWIZZLE_128B: chunk ^= row & 7
+    const int ntiles = p.nks * ((p.row_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x);
+    int s = 0; uint32_t ph = 0;
+    uint4 wlo[2], whi[2], nlo[2], nhi[2];
+    auto fetch = [&](uint4 (&lo)[2], uint4 (&hi)[2]) {
+        mbar_wait(bar_full(s), ph);
+        const uint8_t* seg = gbase + s * GV_TILE_BYTES + sSeg;
+        lo[0] = *reinterpret_cast<const uint4*>(seg + phys0);
+        hi[0] = *reinterpret_cast<const uint4*>(seg + 8 * GV_SEG + phys0);
+        lo[1] = *reinterpret_cast<const uint4*>(seg + phys1);
+        hi[1] = *reinterpret_cast<const uint4*>(seg + 8 * GV_SEG + phys1);
+        __syncwarp();
+        if (lane == 0 && !(p.dbg & 8)) mbar_arrive(bar_empty(s));            // the tile lives in registers now
+        if (++s == p.stages) { s = 0; ph ^= 1u; }
+    };
+    auto mma_half = [&](int (&acc)[4][4], const uint4& lo, const uint4& hi, const uint4 (&b)[4]) {
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t mk = 0x03030303u << (2 * i);
+            imma_16832(acc[i], lo.x & mk, hi.x & mk, lo.y & mk, hi.y & mk, b[i].x, b[i].y);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t mk = 0x03030303u << (2 * i);
+            imma_16832(acc[i], lo.z & mk, hi.z & mk, lo.w & mk, hi.w & mk, b[i].z, b[i].w);
+        }
+    };
+    int acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[i][q] = 0;
+    if (ntiles > 0) fetch(wlo, whi);
+    int ks = 0, rbi = 0;
+#pragma unroll 1
+    for (int it = 0; it < ntiles; ++it) {
+        if (!(p.dbg & 1)) mma_half(acc, wlo[0], whi[0], bq[0]);
+        if (it + 1 < ntiles) fetch(nlo, nhi);
+        if (!(p.dbg & 1)) mma_half(acc, wlo[1], whi[1], bq[1]);
+        if (p.dbg & 1) acc[0][0] += (int)(wlo[0].x ^ whi[0].y ^ wlo[1].z ^ whi[1].w);
+#pragma unroll
+        for (int pp = 0; pp < 2; ++pp) { wlo[pp] = nlo[pp]; whi[pp] = nhi[pp]; }
+        if (++ks == p.nks) {
+            // recombine fields (exact: set i is a multiple of 4^i) and hand this warp's K-partials to the epilogue warp
+            uint4 v;
+            v.x = (uint32_t)(acc[0][0] + (acc[1][0] >> 2) + (acc[2][0] >> 4) + (acc[3][0] >> 6));
+            v.y = (uint32_t)(acc[0][1] + (acc[1][1] >> 2) + (acc[2][1] >> 4) + (acc[3][1] >> 6));
+            v.z = (uint32_t)(acc[0][2] + (acc[1][2] >> 2) + (acc[2][2] >> 4) + (acc[3][2] >> 6));
+            v.w = (uint32_t)(acc[0][3] + (acc[1][3] >> 2) + (acc[2][3] >> 4) + (acc[3][3] >> 6));
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
-                for (int q = 0; q < 4; ++q) acc[nt][i][q] = 0;
-
-        for (int ks = 0; ks < p.nks; ++ks) {
-            mbar_wait(bar_full(s), ph);
-            if (tile_no < 4 && grp == 0) GV_STAMP(2 + 2 * tile_no);          // tile arrived
-#pragma unroll
-            for (int sl2 = 0; sl2 < 2; ++sl2) {
-                const int sgi = wl * 2 + sl2;                               // 128-byte segment of the row
-                const uint8_t* seg = gbase + s * GV_TILE_BYTES + sgi * (GV_ROWS * GV_SEG);
-#pragma unroll
-                for (int pp = 0; pp < 2; ++pp) {
-                    const int phys = ((2 * t + pp) ^ g) << 4;           // SWIZZLE_128B: chunk ^= row & 7
-                    const uint4 wlo = *reinterpret_cast<const uint4*>(seg + g * GV_SEG + phys);
-                    const uint4 whi = *reinterpret_cast<const uint4*>(seg + (g + 8) * GV_SEG + phys);
-                    const int sgp = (ks * GV_CWARPS + sgi) * 2 + pp;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const uint32_t mk = 0x03030303u << (2 * i);
-#pragma unroll
-                        for (int nt = 0; nt < NT; ++nt) {
-                            // only the lanes whose token (n = lane>>2) exists load their B fragment: column n of the
-                            // MMA feeds output column n only, and the shared-memory wavefronts scale with M, not 8
-                            uint4 xv = make_uint4(0u, 0u, 0u, 0u);
-                            if (g < p.M - nt * GV_TOK)
-                                xv = *reinterpret_cast<const uint4*>(
-                                    xq + (size_t)nt * xq_words_nt + ((sgp * 4 + i) * 32 + lane) * 4);
-                            imma_16832(acc[nt][i], wlo.x & mk, whi.x & mk, wlo.y & mk, whi.y & mk, xv.x, xv.y);
-                            imma_16832(acc[nt][i], wlo.z & mk, whi.z & mk, wlo.w & mk, whi.w & mk, xv.z, xv.w);
-                        }
-                    }
-                }
-            }
+                for (int q = 0; q < 4; ++q) acc[i][q] = 0;
+            const int slot = rbi % GV_SLOTS;
+            if (p.dbg & 16) { if (v.x == 0x12345u) slots[0] = v; } else {
+            if (rbi >= GV_SLOTS) mbar_wait(slot_empty(slot), (uint32_t)(rbi / GV_SLOTS - 1) & 1u);
+            slots[slot * GV_CTHREADS + warp * 32 + lane] = v;
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_empty(s));
-            if (tile_no < 4 && grp == 0) GV_STAMP(3 + 2 * tile_no);          // tile consumed (warp 0)
-            ++tile_no;
-            if (++s == p.stages) { s = 0; ph ^= 1u; }
-        }
-
-        // recombine fields (exact: set i is a multiple of 4^i) and publish this warp's K-partials
-        uint4* gslots = slots + (size_t)(grp * 2 + buf) * NT * GV_GWARPS * 32;
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-            uint4 v;
-            v.x = (uint32_t)(acc[nt][0][0] + (acc[nt][1][0] >> 2) + (acc[nt][2][0] >> 4) + (acc[nt][3][0] >> 6));
-            v.y = (uint32_t)(acc[nt][0][1] + (acc[nt][1][1] >> 2) + (acc[nt][2][1] >> 4) + (acc[nt][3][1] >> 6));
-            v.z = (uint32_t)(acc[nt][0][2] + (acc[nt][1][2] >> 2) + (acc[nt][2][2] >> 4) + (acc[nt][3][2] >> 6));
-            v.w = (uint32_t)(acc[nt][0][3] + (acc[nt][1][3] >> 2) + (acc[nt][2][3] >> 4) + (acc[nt][3][3] >> 6));
-            gslots[(nt * GV_GWARPS + wl) * 32 + lane] = v;
-        }
-        group_bar(grp);
-        // reduce over the group's 4 K-quarters and run the fused epilogue: one thread per (row, token)
-        const int* sl = reinterpret_cast<const int*>(gslots);
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-            const int lq = gt;                                   // lane*4 + q of the accumulator fragment
-            int v = 0;
-#pragma unroll
-            for (int w = 0; w < GV_GWARPS; ++w) v += sl[(nt * GV_GWARPS + w) * 128 + lq];
-            const int l = lq >> 2, q = lq & 3;
-            const int rl = (l >> 2) + 8 * (q >> 1);
-            const int64_t row = (int64_t)rb * GV_ROWS + rl;
-            const int tok = nt * GV_TOK + 2 * (l & 3) + (q & 1);
-            if (row < p.N && tok < p.M) {
-                const int a = v - sh_sumq[tok];
-                if (p.acc_out && layer == 0) p.acc_out[(int64_t)tok * p.N + row] = a;
-                const float tv = __fmul_rn((float)a, sh_sx[tok]);
-                const float y = epilogue(tv, sh_scale[rbi * GV_ROWS + rl], sh_bias[rbi * GV_ROWS + rl], p.clip_val);
-                const OT yv = from_f32<OT>(y);
-                if (p.n_peers == 0) {
-                    out[(int64_t)tok * p.ldo + row] = yv;
-                } else {
-#pragma unroll 1
-                    for (int r = 0; r < p.n_peers; ++r)     // one small store per peer over NVLink (P2P-mapped memory)
-                        reinterpret_cast<OT*>(p.peers[r])[(int64_t)tok * p.ldo + row] = yv;
-                    wrote_peer = true;
-                }
+            if (lane == 0) mbar_arrive(slot_full(slot));
             }
+            if (ct == 0 && rbi == 0) GV_STAMP(4);
+            if (ct == 0 && rbi == 1) GV_STAMP(13);
+            if (ct == 0 && rbi == 2) GV_STAMP(14);
+            ks = 0; ++rbi;
         }
-        buf ^= 1;
+        if (p.nks > 1) load_b(ks);
     }
-    if (wrote_peer) __threadfence_system();      // peer stores are visible system-wide before the grid completes
-    GV_STAMP(15);
+    if (ct == 0) GV_STAMP(5);
+}
+
+// ---- parity aid: the activation quantisation of the fused prologue, written out densely (sx_out / qx_out of tb200_gemv)
+template <typename XT>
+__global__ void __launch_bounds__(256)
+gemv_debug_quant_kernel(const XT* __restrict__ x, int64_t ldx, int64_t K, float* __restrict__ sx_out, int8_t* __restrict__ qx_out) {
+    __shared__ float red[8];
+    const XT* xr = x + (int64_t)blockIdx.x * ldx;
+    float amax = 0.0f;
+    for (int64_t k = threadIdx.x; k < K; k += 256) amax = fmaxf(amax, fabsf(to_f32(xr[k])));
+    amax = warp_max(amax);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = amax;
+    __syncthreads();
+    float v = red[0];
+    for (int w = 1; w < 8; ++w) v = fmaxf(v, red[w]);
+    const float inv = v > 0.0f ? __fdiv_rn(127.0f, v) : 1.0f;
+    if (threadIdx.x == 0 && sx_out) sx_out[blockIdx.x] = v > 0.0f ? __fdiv_rn(v, 127.0f) : 1.0f;
+    if (qx_out)
+        for (int64_t k = threadIdx.x; k < K; k += 256) qx_out[(int64_t)blockIdx.x * K + k] = (int8_t)quant_mul(to_f32(xr[k]), inv);
 }
 
 // ---- float-activation variant: the reference's exact semantics (no activation quantisation)
@@ -493,58 +556,78 @@ gemv_f32_kernel(const XT* __restrict__ x, int64_t ldx, int M, int64_t K,
 
 // ---- host side ------------------------------------------------------------------------------
 // tensor maps are cached per (pointer, geometry): encoding costs ~1 us of host time per call
-struct MapKey { const void* ptr; int64_t ld, N, stride; int layers; };
-struct MapEntry { MapKey key; CUtensorMap map; bool used; };
+struct MapKey { const void* ptr; int64_t ld, N, stride; int layers; };   // one map per weight tensor
+struct MapEntry { MapKey key; CUtensorMap map; bool used; bool one_box; };
 static std::mutex g_map_mu;
 static MapEntry g_maps[64];
 static int g_map_next = 0;
 
-static int get_weight_map(const uint8_t* packed, int64_t ld, int64_t N, int64_t stride, int layers, CUtensorMap* out) {
+static int get_weight_map(const uint8_t* packed, int64_t ld, int64_t N, int64_t stride, int layers, CUtensorMap* out, int* one_box) {
     std::lock_guard<std::mutex> lk(g_map_mu);
     for (auto& e : g_maps)
         if (e.used && e.key.ptr == packed && e.key.ld == ld && e.key.N == N && e.key.stride == stride && e.key.layers == layers) {
             *out = e.map;
+            *one_box = e.one_box;
             return TB200_OK;
         }
+    MapEntry& e = g_maps[g_map_next];
+    static const int no4d = getenv("TB200_GEMV_NO4D") ? atoi(getenv("TB200_GEMV_NO4D")) : 0;
+    int rc = TB200_ECUDA;
+    e.one_box = false;
+    if (ld % GV_SEG == 0 && !no4d) {
+        // 4-D view (word in segment, row, 128-byte segment of the row, layer): a whole 16-row x 1024-byte tile is ONE box
+        // that lands as [segment][row][128 B], the layout the consumers read (SWIZZLE_128B on the row index).
+        uint64_t dims4[4] = {GV_SEG / 4, (uint64_t)N, (uint64_t)(ld / GV_SEG), (uint64_t)layers};
+        uint64_t strides4[3] = {(uint64_t)ld, (uint64_t)GV_SEG, (uint64_t)(layers > 1 ? stride : ld * N)};
+        uint32_t box4[4] = {GV_SEG / 4, GV_ROWS, GV_CWARPS, 1};
+        rc = make_tensor_map(&e.map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, packed, dims4, strides4, box4, CU_TENSOR_MAP_SWIZZLE_128B);
+        e.one_box = rc == TB200_OK;
+    }
     uint64_t dims[3] = {(uint64_t)(ld / 4), (uint64_t)N, (uint64_t)layers};
     uint64_t strides[2] = {(uint64_t)ld, (uint64_t)(layers > 1 ? stride : ld * N)};
     uint32_t box[3] = {GV_SEG / 4, GV_ROWS, 1};
-    MapEntry& e = g_maps[g_map_next];
-    int rc = make_tensor_map(&e.map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, packed, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) rc = make_tensor_map(&e.map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, packed, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) { e.used = false; return rc; }
     e.key = MapKey{packed, ld, N, stride, layers};
     e.used = true;
     g_map_next = (g_map_next + 1) % 64;
     *out = e.map;
+    *one_box = e.one_box;
     return TB200_OK;
 }
 
 int gemv_nks(int64_t K) { return (int)((K + 4095) / 4096); }
 
-static size_t gemv_smem(int nt, int nks, int stages, int nrb = 8) {
-    return 1024 + (size_t)stages * GV_TILE_BYTES + (size_t)nt * GV_TOK * nks * 4096 + (size_t)2 * nt * GV_CWARPS * 32 * 16 +
-           (size_t)nt * GV_TOK * 8 + GV_TOK * GV_CWARPS * 8 + 2 * GV_MAX_STAGES * 8 + (size_t)nrb * GV_ROWS * 8 + 64;
+static size_t gemv_smem(int m, int nks, int stages, int nrb) {
+    return 1024 + (size_t)stages * GV_TILE_BYTES + (size_t)nks * 4096 * m + (size_t)GV_SLOTS * GV_CTHREADS * 16 +
+           GV_TOK * 4 + 2 * GV_TOK * GV_CWARPS * 4 + (2 * GV_MAX_STAGES + 2 * GV_SLOTS) * 8 + (size_t)nrb * GV_ROWS * 8 + 64;
 }
-// deepest ring (<= 6, >= 2 stages) that fits next to the activation image; 0 if nothing fits
-static int gemv_pick_stages(int nt, int nks, int nrb = 8) {
-    // two CTAs per SM (this layer's and, under programmatic dependent launch, the next layer's)
-    // when a >= 3-deep ring still fits in half of the SM's shared memory ...
-    for (int s = GV_MAX_STAGES - 1; s >= 3; --s)
-        if (gemv_smem(nt, nks, s, nrb) <= 113 * 1024) return s;
-    // ... else the deepest ring that fits at one CTA per SM
-    for (int s = GV_MAX_STAGES - 1; s >= 2; --s)
-        if (gemv_smem(nt, nks, s, nrb) <= 227 * 1024) return s;
+// Ring depth: the CTA's whole share of the weights when it fits (then every load is issued before the kernel
+// waits for its predecessor).  Two CTAs per SM must fit (this layer's and, under programmatic dependent
+// launch, the next layer's): 2 x (smem + 1 KB reserved) <= 228 KB.  Falls back to one CTA per SM for large K*M.
+static int gemv_pick_stages(int m, int nks, int nrb) {
+    const int tiles = nrb * nks;
+    const int want = tiles < GV_MAX_STAGES ? tiles : GV_MAX_STAGES;
+    for (int s = want; s >= 2; --s)
+        if (gemv_smem(m, nks, s, nrb) <= 113 * 1024) return s;
+    for (int s = want; s >= 1; --s)
+        if (gemv_smem(m, nks, s, nrb) <= 227 * 1024) return s;
     return 0;
 }
 
-template <typename XT, typename OT, int NT, bool FUSED>
+template <typename XT, typename OT, bool FUSED, bool VEC>
 static int launch_gemv(const CUtensorMap& map, GemvParams p, int layers, cudaStream_t s) {
     const int ctas = p.row_blocks < sm_count() ? p.row_blocks : sm_count();
     p.nrb = (p.row_blocks + ctas - 1) / ctas;
-    p.stages = gemv_pick_stages(NT, p.nks, p.nrb);
-    TB_REQUIRE(p.stages >= 2, "gemv: K=%lld N=%lld is too large for the shared-memory activation image", (long long)p.K, (long long)p.N);
-    const size_t smem = gemv_smem(NT, p.nks, p.stages, p.nrb);
-    auto kern = gemv_mma_kernel<XT, OT, NT, FUSED>;
+    p.stages = gemv_pick_stages(p.M, p.nks, p.nrb);
+    static const int inflight_env = getenv("TB200_GEMV_INFLIGHT") ? atoi(getenv("TB200_GEMV_INFLIGHT")) : 0;
+    p.inflight = inflight_env > 0 ? inflight_env : GV_MAX_STAGES;
+    static const int dbg_env = getenv("TB200_GEMV_DBG") ? atoi(getenv("TB200_GEMV_DBG")) : 0;
+    p.dbg = dbg_env;
+    if (p.inflight > p.stages) p.inflight = p.stages;
+    TB_REQUIRE(p.stages >= 1, "gemv: K=%lld N=%lld is too large for the shared-memory activation image", (long long)p.K, (long long)p.N);
+    const size_t smem = gemv_smem(p.M, p.nks, p.stages, p.nrb);
+    auto kern = gemv_mma_kernel<XT, OT, FUSED, VEC>;
     static size_t configured = 0;   // per instantiation
     if (smem > configured) {
         TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -565,10 +648,12 @@ static int launch_gemv(const CUtensorMap& map, GemvParams p, int layers, cudaStr
     return TB200_OK;
 }
 
-template <int NT, bool FUSED>
+template <bool FUSED>
 static int gemv_dispatch(int x_dtype, int out_dtype, const CUtensorMap& map, const GemvParams& p, int layers, cudaStream_t s) {
 #define TB_GEMV_CASE(XD, XT, OD, OT) \
-    if (x_dtype == XD && out_dtype == OD) return launch_gemv<XT, OT, NT, FUSED>(map, p, layers, s)
+    if (x_dtype == XD && out_dtype == OD) \
+        return (!FUSED || p.xvec) ? launch_gemv<XT, OT, FUSED, true>(map, p, layers, s) \
+                                  : launch_gemv<XT, OT, FUSED, false>(map, p, layers, s)
     TB_GEMV_CASE(TB200_BF16, __nv_bfloat16, TB200_BF16, __nv_bfloat16);
     TB_GEMV_CASE(TB200_BF16, __nv_bfloat16, TB200_F32, float);
     TB_GEMV_CASE(TB200_F32, float, TB200_F32, float);
@@ -611,25 +696,24 @@ int gemv_fused(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, in
                       const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
                       const float* scale, const float* bias, int64_t stride_sb, float clip_val,
                       void* out, int out_dtype, int64_t ldo, int64_t stride_out,
-                      int32_t* acc_out, float* sx_out, int8_t* qx_out, int layers, int flags, cudaStream_t s,
+                      int32_t* acc_out, int layers, int flags, cudaStream_t s,
                       void* const* peers = nullptr, int n_peers = 0) {
     CUtensorMap map;
-    int rc = get_weight_map(packed, ld_packed, N, stride_packed, layers, &map);
+    int one_box = 0;
+    int rc = get_weight_map(packed, ld_packed, N, stride_packed, layers, &map, &one_box);
     if (rc) return rc;
     const size_t xs = dtype_size(x_dtype), os = dtype_size(out_dtype);
     GemvParams p = {};
     fill_common(p, K, N, scale, bias, stride_sb, clip_val, ldo, stride_out, flags);
-    p.ldx = ldx; p.stride_x = stride_x;
-    p.xvec = ((uintptr_t)x % 16 == 0) && ((ldx * xs) % 16 == 0) && ((stride_x * xs) % 16 == 0);
+    p.ldx = ldx; p.stride_x = stride_x; p.one_box = one_box;
+    p.xvec = ((uintptr_t)x % 16 == 0) && ((ldx * xs) % 16 == 0) && ((stride_x * xs) % 16 == 0) && (K % 16 == 0);
     for (int64_t m0 = 0; m0 < M; m0 += GV_TOK) {
         p.M = (int)(M - m0 < GV_TOK ? M - m0 : GV_TOK);
         p.x = (const char*)x + m0 * ldx * xs;
         p.out = (char*)out + m0 * ldo * os;
         p.acc_out = acc_out ? acc_out + m0 * N : nullptr;
-        p.sx_out = sx_out ? sx_out + m0 : nullptr;
-        p.qx_out = qx_out ? qx_out + m0 * K : nullptr;
         set_peers(p, peers, n_peers, m0 * ldo * (int64_t)os);
-        rc = gemv_dispatch<1, true>(x_dtype, out_dtype, map, p, layers, s);
+        rc = gemv_dispatch<true>(x_dtype, out_dtype, map, p, layers, s);
         if (rc) return rc;
     }
     return TB200_OK;
@@ -657,25 +741,22 @@ int gemv_q_impl(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t*
                "gemv_q: q_x must come from tb200_quant_act_i8(layout 1): ldq >= K, multiple of 16, 16-byte aligned");
     TB_REQUIRE(dtype_ok(out_dtype), "gemv_q: bad out dtype");
     CUtensorMap map;
-    rc = get_weight_map(packed, ld_packed, N, 0, 1, &map);
+    int one_box = 0;
+    rc = get_weight_map(packed, ld_packed, N, 0, 1, &map, &one_box);
     if (rc) return rc;
     const size_t os = dtype_size(out_dtype);
     GemvParams p = {};
     fill_common(p, K, N, scale, bias, 0, clip_val, ldo, 0, flags);
-    p.ldq = ldq;
-    // 16 tokens per pass when the activation image fits next to a >= 4-deep ring, else 8
-    const bool two = M > GV_TOK && gemv_pick_stages(2, p.nks) >= 4;
-    const int64_t step = two ? 2 * GV_TOK : GV_TOK;
-    for (int64_t m0 = 0; m0 < M; m0 += step) {
-        p.M = (int)(M - m0 < step ? M - m0 : step);
+    p.ldq = ldq; p.one_box = one_box;
+    for (int64_t m0 = 0; m0 < M; m0 += GV_TOK) {     // one pass over the weights per 8 tokens
+        p.M = (int)(M - m0 < GV_TOK ? M - m0 : GV_TOK);
         p.qx = q_x + m0 * ldq;
         p.sx_in = s_x + m0; p.sumq_in = sum_qx + m0;
         p.out = (char*)out + m0 * ldo * os;
         p.acc_out = acc_out ? acc_out + m0 * N : nullptr;
         set_peers(p, peers, n_peers, m0 * ldo * (int64_t)os);
         // activations are int8 already: the XT template parameter is unused on this path
-        if (two && p.M > GV_TOK) rc = gemv_dispatch<2, false>(out_dtype, out_dtype, map, p, 1, (cudaStream_t)stream);
-        else                     rc = gemv_dispatch<1, false>(out_dtype, out_dtype, map, p, 1, (cudaStream_t)stream);
+        rc = gemv_dispatch<false>(out_dtype, out_dtype, map, p, 1, (cudaStream_t)stream);
         if (rc) return rc;
     }
     return TB200_OK;
@@ -702,8 +783,13 @@ extern "C" int tb200_gemv(const void* x, int x_dtype, int64_t M, int64_t K, int6
     TB_REQUIRE(ldx >= K, "gemv: ldx < K");
     int rc = gemv_check(M, K, N, ldo, packed, ld_packed, 0, 1);
     if (rc) return rc;
+    if (sx_out || qx_out) {
+        TB_DISPATCH_DTYPE(x_dtype, T,
+            (gemv_debug_quant_kernel<T><<<(unsigned)M, 256, 0, (cudaStream_t)stream>>>((const T*)x, ldx, K, sx_out, qx_out)));
+        TB_LAUNCH_CHECK();
+    }
     return gemv_fused(x, x_dtype, M, K, ldx, 0, packed, ld_packed, 0, N, scale, bias, 0, clip_val,
-                      out, out_dtype, ldo, 0, acc_out, sx_out, qx_out, 1, flags, (cudaStream_t)stream);
+                      out, out_dtype, ldo, 0, acc_out, 1, flags, (cudaStream_t)stream);
 }
 
 extern "C" int tb200_gemv_grouped(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
@@ -718,7 +804,7 @@ extern "C" int tb200_gemv_grouped(const void* x, int x_dtype, int64_t M, int64_t
     int rc = gemv_check(M, K, N, ldo, packed, ld_packed, stride_packed, count);
     if (rc) return rc;
     return gemv_fused(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N, scale, bias,
-                      stride_sb, clip_val, out, out_dtype, ldo, stride_out, nullptr, nullptr, nullptr,
+                      stride_sb, clip_val, out, out_dtype, ldo, stride_out, nullptr,
                       count, flags, (cudaStream_t)stream);
 }
 

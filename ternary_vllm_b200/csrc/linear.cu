@@ -20,7 +20,7 @@ int gemv_fused(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, in
                const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
                const float* scale, const float* bias, int64_t stride_sb, float clip_val,
                void* out, int out_dtype, int64_t ldo, int64_t stride_out,
-               int32_t* acc_out, float* sx_out, int8_t* qx_out, int layers, int flags, cudaStream_t s,
+               int32_t* acc_out, int layers, int flags, cudaStream_t s,
                void* const* peers, int n_peers);
 int gemv_q_impl(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx, int64_t M, int64_t K,
                 const uint8_t* packed, int64_t ld_packed, int64_t N, const float* scale, const float* bias, float clip_val,
@@ -30,7 +30,7 @@ int gemv_q_impl(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t*
 using namespace tb200;
 
 extern "C" size_t tb200_linear_workspace(int64_t M, int64_t K) {
-    if (M <= 2 || K <= 0) return 256;
+    if (M <= TB200_GEMV_FUSED_M || K <= 0) return 256;
     const int64_t ldq = round_up(K, 16);
     return (size_t)(round_up(M * ldq, 256) + 2 * round_up(M * 4, 256) + 256);
 }
@@ -40,7 +40,7 @@ extern "C" int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64
                                     const float* scale, const float* bias, float clip_val,
                                     void* out, int out_dtype, int64_t ldo,
                                     void* workspace, void* stream) {
-    if (M <= 2)
+    if (M <= TB200_GEMV_FUSED_M)
         return tb200_gemv(x, x_dtype, M, K, ldx, packed, ld_packed, N, scale, bias, clip_val,
                           out, out_dtype, ldo, nullptr, nullptr, nullptr, 0, stream);
     TB_REQUIRE(workspace && (uintptr_t)workspace % 256 == 0, "linear_forward: workspace must be non-null and 256-byte aligned");
@@ -90,9 +90,9 @@ extern "C" int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, in
     TB_REQUIRE(K > 0 && ldx >= K && ldo >= N_local, "linear_forward_tp: bad shape");
     const int64_t kc = (K + 63) / 64;
     TB_REQUIRE(ld_packed % 16 == 0 && ld_packed >= kc * 16 && (uintptr_t)packed % 16 == 0, "linear_forward_tp: bad packed layout");
-    if (M <= 2)
+    if (M <= TB200_GEMV_FUSED_M)
         return gemv_fused(x, x_dtype, M, K, ldx, 0, packed, ld_packed, 0, N_local, scale, bias, 0, clip_val,
-                          out_peers[0], out_dtype, ldo, 0, nullptr, nullptr, nullptr, 1, 0, (cudaStream_t)stream,
+                          out_peers[0], out_dtype, ldo, 0, nullptr, 1, 0, (cudaStream_t)stream,
                           out_peers, n_peers);
     TB_REQUIRE(workspace && (uintptr_t)workspace % 256 == 0, "linear_forward_tp: workspace must be non-null and 256-byte aligned");
     LinearWs ws = carve_ws(workspace, M, K);

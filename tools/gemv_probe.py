@@ -34,7 +34,7 @@ for M in Ms:
     bytes_layer = N * K / 4 + M * K * 2 + M * N * 2 + N * 8
     def chain(pdl, fn="matmul"):
         for r in range(R):
-            if M <= 2:
+            if M <= 8:
                 ops.gemv(x, packed[r], scale[r], bias[r], 100.0, pdl=pdl, out=out[r])
             else:
                 ops.ternary_matmul(x, packed[r], scale[r], bias[r], 100.0)
@@ -48,7 +48,7 @@ for M in Ms:
             with torch.cuda.graph(gr, stream=s):
                 chain(pdl)
         res[f"graph  pdl={pdl}"] = timeit(gr.replay) / R
-    if M <= 2:
+    if M <= 8:
         def grouped():
             L.check(lib.tb200_gemv_grouped(xs.data_ptr(), L.TB200_BF16, M, K, K, M * K, packed.data_ptr(), ld, N * ld, N,
                                            scale.data_ptr(), bias.data_ptr(), N, 100.0, out.data_ptr(), L.TB200_BF16, N, M * N,
