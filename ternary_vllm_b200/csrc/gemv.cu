@@ -34,10 +34,9 @@ constexpr int GV_TILE_BYTES = GV_ROWS * GV_SLICE; // 16 KB
 constexpr int GV_CWARPS = GV_SLICE / GV_SEG;      // 8 consumer warps, one per 128-byte K segment
 constexpr int GV_CTHREADS = GV_CWARPS * 32;
 constexpr int GV_WARP_PRODUCER = GV_CWARPS;       // warp 8: TMA producer
-constexpr int GV_WARP_EPILOGUE = GV_CWARPS + 1;   // warp 9: K-partial reduction + fused epilogue
-constexpr int GV_THREADS = (GV_CWARPS + 2) * 32;
+constexpr int GV_THREADS = (GV_CWARPS + 1) * 32;
 constexpr int GV_MAX_STAGES = 12;
-constexpr int GV_SLOTS = 4;                       // partial-sum slots (4 KB each) between consumers and epilogue warp
+constexpr int GV_MAX_SLOTS = 8;                   // row blocks whose K-partials (4 KB each) are parked before a reduction round
 constexpr int GV_TOK = 8;                         // tokens per pass = MMA N
 
 struct GemvParams {
@@ -53,11 +52,10 @@ struct GemvParams {
     int row_blocks;   // ceil(N / 16)
     int nrb;          // row blocks per CTA = ceil(row_blocks / gridDim.x)
     int stages;       // ring depth
-    int inflight;     // tiles requested ahead of the last one that has landed (paces the prefetch)
+    int nslots;       // row blocks per reduction round (partial-sum slots in shared memory)
     float clip_val;
     int pdl;
     int one_box;      // the tensor map is 4-D (word, row, segment, layer): one 16 KB box per tile
-    int dbg;          // experiment switches (TB200_GEMV_DBG): 1 skip MMAs, 2 skip x load+quantisation, 4 skip epilogue stores
     bool xvec;
     long long* trace;   // debug: per-CTA globaltimer stamps (tb200_debug_set_trace), normally null
     // tensor-parallel gather fused into the epilogue: when n_peers > 0 the output element is stored into every
@@ -131,21 +129,20 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;         // SWIZZLE_128B boxes: 1024-B aligned
     uint8_t* gbase = smem_dyn + (base - smem_u32(smem_dyn));
-    // layout: ring[stages][16 KB] | image[nks*4096*M] | slots[2][8 warps][32] uint4 | sx | red_f | red_i | barriers | scale | bias
+    // layout: ring[stages][16 KB] | image[nks*4096*M] | slots[nslots][8 warps][32] uint4 | sx | sumq | red_f | red_i | barriers | scale | bias
     const uint32_t sRing = base;
     uint32_t* xq = reinterpret_cast<uint32_t*>(gbase + p.stages * GV_TILE_BYTES);
     uint4* slots = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(xq) + (size_t)p.nks * 4096 * p.M);
-    float* sh_sx = reinterpret_cast<float*>(slots + GV_SLOTS * GV_CTHREADS);
-    float* red_f = sh_sx + GV_TOK;                                        // [8 tokens][8 warps]
+    float* sh_sx = reinterpret_cast<float*>(slots + (size_t)p.nslots * GV_CTHREADS);
+    int* sh_sumq = reinterpret_cast<int*>(sh_sx + GV_TOK);
+    float* red_f = reinterpret_cast<float*>(sh_sumq + GV_TOK);             // [8 tokens][8 warps]
     int* red_i = reinterpret_cast<int*>(red_f + GV_TOK * GV_CWARPS);      // [8 tokens][8 warps]
     uint64_t* bars = reinterpret_cast<uint64_t*>(red_i + GV_TOK * GV_CWARPS);
-    float* sh_scale = reinterpret_cast<float*>(bars + 2 * GV_MAX_STAGES + 2 * GV_SLOTS);   // [nrb][16] this CTA's rows
+    float* sh_scale = reinterpret_cast<float*>(bars + 2 * GV_MAX_STAGES);   // [nrb][16] this CTA's rows
     float* sh_bias = sh_scale + p.nrb * GV_ROWS;
     const uint32_t sBar = smem_u32(bars);
     auto bar_full = [&](int s) { return sBar + 8u * s; };
     auto bar_empty = [&](int s) { return sBar + 8u * (GV_MAX_STAGES + s); };
-    auto slot_full = [&](int s) { return sBar + 8u * (2 * GV_MAX_STAGES + s); };
-    auto slot_empty = [&](int s) { return sBar + 8u * (2 * GV_MAX_STAGES + GV_SLOTS + s); };
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int layer = blockIdx.y;
@@ -156,10 +153,6 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
         for (int s = 0; s < p.stages; ++s) {
             mbar_init(bar_full(s), 1);
             mbar_init(bar_empty(s), GV_CWARPS);
-        }
-        for (int s = 0; s < GV_SLOTS; ++s) {
-            mbar_init(slot_full(s), GV_CWARPS);
-            mbar_init(slot_empty(s), 1);
         }
         mbar_fence_init();
     }
@@ -172,118 +165,46 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
         // behind a ring-full of weight traffic: let the consumers issue their x loads first.
         if (!p.pdl) asm volatile("bar.sync 2, %0;" ::"n"(GV_CTHREADS + 32) : "memory");
         if (lane == 0) {
-            int s = 0; uint32_t ph = 0;
-            int idx = 0, ls = 0; uint32_t lph = 0;     // (ls, lph): stage and phase of tile idx - inflight
+            int s = 0; uint32_t ph = 0; int idx = 0;
             for (int rb = blockIdx.x; rb < p.row_blocks; rb += gridDim.x) {
                 for (int ks = 0; ks < p.nks; ++ks, ++idx) {
-                    // Pacing: at most `inflight` tiles outstanding per SM.  Requesting the whole share at once parks
-                    // ~12 MB in the memory system and the (small, latency-critical) activation loads of the kernel
-                    // that is running queue behind it.
-                    if (idx >= p.inflight) {
-                        mbar_wait(bar_full(ls), lph);
-                        if (++ls == p.stages) { ls = 0; lph ^= 1u; }
-                    }
-                    mbar_wait(bar_empty(s), ph ^ 1u);
+                    if (idx >= p.stages) mbar_wait(bar_empty(s), ph ^ 1u);     // first pass over the ring: stages are free
                     mbar_arrive_expect_tx(bar_full(s), GV_TILE_BYTES);
                     if (p.one_box) {
                         tma_load_4d(sRing + s * GV_TILE_BYTES, &map_w, bar_full(s), 0, rb * GV_ROWS, ks * GV_CWARPS, layer);
-                    } else
+                    } else {
 #pragma unroll
-                    for (int sg = 0; sg < GV_CWARPS; ++sg)
-                        tma_load_3d(sRing + s * GV_TILE_BYTES + sg * (GV_ROWS * GV_SEG), &map_w, bar_full(s),
-                                    ks * (GV_SLICE / 4) + sg * (GV_SEG / 4), rb * GV_ROWS, layer);
+                        for (int sg = 0; sg < GV_CWARPS; ++sg)
+                            tma_load_3d(sRing + s * GV_TILE_BYTES + sg * (GV_ROWS * GV_SEG), &map_w, bar_full(s),
+                                        ks * (GV_SLICE / 4) + sg * (GV_SEG / 4), rb * GV_ROWS, layer);
+                    }
                     if (++s == p.stages) { s = 0; ph ^= 1u; }
                 }
             }
-            GV_STAMP(10);
         }
-        return;
-    }
-
-    if (warp == GV_WARP_EPILOGUE) {
-        // ===================== epilogue warp: sums the 8 K-partials of a row block, scale/bias/clip, store ===========
-        {   // this CTA's per-row scale and bias are weights: fetched before the dependency wait
-            const float* scale_g = p.scale ? p.scale + layer * p.stride_sb : nullptr;
-            const float* bias_g = p.bias ? p.bias + layer * p.stride_sb : nullptr;
-            for (int i = lane; i < p.nrb * GV_ROWS; i += 32) {
-                const int64_t row = ((int64_t)blockIdx.x + (int64_t)(i >> 4) * gridDim.x) * GV_ROWS + (i & 15);
-                sh_scale[i] = (scale_g && row < p.N) ? scale_g[row] : 1.0f;
-                sh_bias[i] = (bias_g && row < p.N) ? bias_g[row] : 0.0f;
-            }
-        }
-        if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
-        __syncwarp();
-        OT* out = reinterpret_cast<OT*>(p.out) + layer * p.stride_out;
-        const int g = lane >> 2, t = lane & 3;
-        float sx[2] = {0.0f, 0.0f}; int sumq[2] = {0, 0};
-        bool have_tok = false, wrote_peer = false;
-        int rbi = 0;
-        for (int rb = blockIdx.x; rb < p.row_blocks && !(p.dbg & 16); rb += gridDim.x, ++rbi) {
-            const int slot = rbi % GV_SLOTS;
-            mbar_wait(slot_full(slot), (uint32_t)(rbi / GV_SLOTS) & 1u);
-            if (lane == 0 && rb + (int)gridDim.x >= p.row_blocks) GV_STAMP(11);     // last row block handed over
-            if (!have_tok) {      // the consumers' prologue is complete: per-token scale and sum of codes
-                if (lane == 0) GV_STAMP(9);
-#pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int tok = 2 * t + e;
-                    if (tok < M) {
-                        if (FUSED) {
-                            sx[e] = sh_sx[tok];
-                            int v = 0;
-#pragma unroll
-                            for (int w = 0; w < GV_CWARPS; ++w) v += red_i[tok * GV_CWARPS + w];
-                            sumq[e] = v;
-                        } else {
-                            sx[e] = p.sx_in[layer * p.stride_s + tok];
-                            sumq[e] = p.sumq_in[layer * p.stride_s + tok];
-                        }
-                    }
-                }
-                have_tok = true;
-            }
-            const uint4* sl = slots + slot * GV_CTHREADS + lane;
-            int v0 = 0, v1 = 0, v2 = 0, v3 = 0;
-#pragma unroll
-            for (int w = 0; w < GV_CWARPS; ++w) {
-                const uint4 u = sl[w * 32];
-                v0 += (int)u.x; v1 += (int)u.y; v2 += (int)u.z; v3 += (int)u.w;
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(slot_empty(slot));
-            if (lane == 0 && rb + (int)gridDim.x >= p.row_blocks) GV_STAMP(12);     // last partials summed
-            // accumulator fragment: v0 (row g, tok 2t), v1 (row g, tok 2t+1), v2 (row g+8, tok 2t), v3 (row g+8, tok 2t+1)
-            const int vv[4] = {v0, v1, v2, v3};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int rl = g + 8 * (q >> 1), e = q & 1, tok = 2 * t + e;
-                const int64_t row = (int64_t)rb * GV_ROWS + rl;
-                if (row < p.N && tok < M && !(p.dbg & 4)) {
-                    const int a = vv[q] - sumq[e];
-                    if (p.acc_out && layer == 0) p.acc_out[(int64_t)tok * p.N + row] = a;
-                    const float tv = __fmul_rn((float)a, sx[e]);
-                    const float y = epilogue(tv, sh_scale[rbi * GV_ROWS + rl], sh_bias[rbi * GV_ROWS + rl], p.clip_val);
-                    const OT yv = from_f32<OT>(y);
-                    if (p.n_peers == 0) {
-                        out[(int64_t)tok * p.ldo + row] = yv;
-                    } else {
-#pragma unroll 1
-                        for (int r = 0; r < p.n_peers; ++r)     // one small store per peer over NVLink (P2P-mapped memory)
-                            reinterpret_cast<OT*>(p.peers[r])[(int64_t)tok * p.ldo + row] = yv;
-                        wrote_peer = true;
-                    }
-                }
-            }
-        }
-        if (wrote_peer) __threadfence_system();      // peer stores are visible system-wide before the grid completes
-        if (lane == 0) GV_STAMP(15);
         return;
     }
 
     // ===================== consumers =====================
     const int ct = threadIdx.x;                       // 0..255
     const int g = lane >> 2, t = lane & 3;
-    if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");   // x comes from the previous kernel
+    // this CTA's per-row scale and bias (weights: independent of the previous kernel): the loads are issued
+    // now, the values are parked in shared memory once the activations have been requested
+    float sb_scale[2], sb_bias[2];
+    {
+        const float* scale_g = p.scale ? p.scale + layer * p.stride_sb : nullptr;
+        const float* bias_g = p.bias ? p.bias + layer * p.stride_sb : nullptr;
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int i = ct + u * GV_CTHREADS;
+            const int64_t row = ((int64_t)blockIdx.x + (int64_t)(i >> 4) * gridDim.x) * GV_ROWS + (i & 15);
+            const bool ok = i < p.nrb * GV_ROWS && row < p.N;
+            sb_scale[u] = (scale_g && ok) ? scale_g[row] : 1.0f;
+            sb_bias[u] = (bias_g && ok) ? bias_g[row] : 0.0f;
+        }
+    }
+    // x comes from the previous kernel
+    if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     if (ct == 0) GV_STAMP(1);
     bool released = p.pdl != 0;                       // producer already running under PDL
     auto release_producer = [&]() {
@@ -299,7 +220,7 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
 #pragma unroll
         for (int mb = 0; mb < GV_TOK / TB; ++mb) {
             const int m0 = mb * TB;
-            if (m0 >= M || (p.dbg & 2)) break;
+            if (m0 >= M) break;
             Raw16<XT> raw[TB];
             float amax[TB];
 #pragma unroll
@@ -326,9 +247,7 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
                     if (lane == 0) red_f[(m0 + tb) * GV_CWARPS + warp] = __uint_as_float(a);
                 }
             }
-            if (ct == 0 && m0 == 0) GV_STAMP(2);     // activations arrived
             consumer_bar();
-            if (ct == 0 && m0 == 0) GV_STAMP(6);     // every warp's activations arrived
             float inv[TB];
 #pragma unroll
             for (int tb = 0; tb < TB; ++tb) {
@@ -397,9 +316,18 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
         }
     }
     release_producer();
-    if (ct == 0) GV_STAMP(3);     // quantised image written
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int i = ct + u * GV_CTHREADS;
+        if (i < p.nrb * GV_ROWS) { sh_scale[i] = sb_scale[u]; sh_bias[i] = sb_bias[u]; }
+    }
+    for (int i = ct + 2 * GV_CTHREADS; i < p.nrb * GV_ROWS; i += GV_CTHREADS) {   // > 32 row blocks per CTA
+        const int64_t row = ((int64_t)blockIdx.x + (int64_t)(i >> 4) * gridDim.x) * GV_ROWS + (i & 15);
+        sh_scale[i] = (p.scale && row < p.N) ? p.scale[layer * p.stride_sb + row] : 1.0f;
+        sh_bias[i] = (p.bias && row < p.N) ? p.bias[layer * p.stride_sb + row] : 0.0f;
+    }
     consumer_bar();               // activation image (and sh_sx) complete
-    if (ct == 0) GV_STAMP(7);
+    if (ct == 0) GV_STAMP(3);
 
     // B fragments of this warp's K segment: 32 registers, loaded once when K <= 4096
     const uint4* xqv = reinterpret_cast<const uint4*>(xq);
@@ -412,7 +340,7 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
                 bq[pp][i] = g < M ? xqv[xq_vec(ks * GV_CWARPS + warp, pp, i, g, t, M)] : make_uint4(0u, 0u, 0u, 0u);
     };
     load_b(0);
-    if (FUSED) {                  // per-token sum of codes: needed by the epilogue warp only, off the critical path
+    if (FUSED) {                  // per-token sum of codes: needed by the epilogue only, off the critical path
 #pragma unroll
         for (int m = 0; m < GV_TOK; ++m)
             if (m < M) {
@@ -420,13 +348,18 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
                 if (lane == 0) red_i[m * GV_CWARPS + warp] = v;
             }
     }
-    if (ct == 0) GV_STAMP(8);
 
     // Main loop, software-pipelined: the packed rows of tile i+1 are fetched into registers (and its ring stage
     // released) between the two halves of the MMAs of tile i.
     const uint32_t sSeg = warp * (GV_ROWS * GV_SEG) + g * GV_SEG;
     const uint32_t phys0 = ((2 * t) ^ g) << 4, phys1 = ((2 * t + 1) ^ g) << 4;   // SWIZZLE_128B: chunk ^= row & 7
-    const int ntiles = p.nks * ((p.row_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x);
+    // loop-invariant launch parameters pinned in registers (otherwise every use is a constant-bank load on the
+    // critical path of a loop that runs only a handful of times)
+    auto pin = [](int v) { int r; asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v)); return r; };
+    const int nks_r = pin(p.nks), stages_r = pin(p.stages), nslots_r = pin(p.nslots);
+    const int my_rbs = pin((p.row_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x);
+    const int ntiles = pin(nks_r * my_rbs);
+    const bool recycle = ntiles > stages_r;           // stages are handed back to the producer only when the ring wraps
     int s = 0; uint32_t ph = 0;
     uint4 wlo[2], whi[2], nlo[2], nhi[2];
     auto fetch = [&](uint4 (&lo)[2], uint4 (&hi)[2]) {
@@ -436,9 +369,11 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
         hi[0] = *reinterpret_cast<const uint4*>(seg + 8 * GV_SEG + phys0);
         lo[1] = *reinterpret_cast<const uint4*>(seg + phys1);
         hi[1] = *reinterpret_cast<const uint4*>(seg + 8 * GV_SEG + phys1);
-        __syncwarp();
-        if (lane == 0 && !(p.dbg & 8)) mbar_arrive(bar_empty(s));            // the tile lives in registers now
-        if (++s == p.stages) { s = 0; ph ^= 1u; }
+        if (recycle) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_empty(s));            // the tile lives in registers now
+        }
+        if (++s == stages_r) { s = 0; ph ^= 1u; }
     };
     auto mma_half = [&](int (&acc)[4][4], const uint4& lo, const uint4& hi, const uint4 (&b)[4]) {
 #pragma unroll
@@ -452,23 +387,82 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
             imma_16832(acc[i], lo.z & mk, hi.z & mk, lo.w & mk, hi.w & mk, b[i].z, b[i].w);
         }
     };
+    // Reduction round: the K-partials of up to nslots row blocks are parked in shared memory; after a barrier warp w
+    // sums the eight partials of row blocks w, w+8, ... of the round and runs the fused epilogue for them.
+    OT* out = reinterpret_cast<OT*>(p.out) + layer * p.stride_out;
+    bool wrote_peer = false;
+    auto reduce_round = [&](int rbi0, int count) {
+        consumer_bar();
+        int sumq[2]; float sxv[2];                // this lane's two tokens (2t, 2t+1)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int tok = 2 * t + e;
+            sumq[e] = 0; sxv[e] = 0.0f;
+            if (tok < M) {
+                sxv[e] = sh_sx[tok];
+                if (FUSED) {
+                    const int4 r0 = *reinterpret_cast<const int4*>(red_i + tok * GV_CWARPS);
+                    const int4 r1 = *reinterpret_cast<const int4*>(red_i + tok * GV_CWARPS + 4);
+                    sumq[e] = r0.x + r0.y + r0.z + r0.w + r1.x + r1.y + r1.z + r1.w;
+                } else {
+                    sumq[e] = sh_sumq[tok];
+                }
+            }
+        }
+        for (int j = warp; j < count; j += GV_CWARPS) {
+            const uint4* sl = slots + (size_t)j * GV_CTHREADS + lane;
+            int vv[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int w = 0; w < GV_CWARPS; ++w) {
+                const uint4 u = sl[w * 32];
+                vv[0] += (int)u.x; vv[1] += (int)u.y; vv[2] += (int)u.z; vv[3] += (int)u.w;
+            }
+            // accumulator fragment: vv0 (row g, tok 2t), vv1 (row g, tok 2t+1), vv2 (row g+8, tok 2t), vv3 (row g+8, tok 2t+1)
+            const int rbi = rbi0 + j;
+            const int64_t rb = (int64_t)blockIdx.x + (int64_t)rbi * gridDim.x;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int rl = g + 8 * (q >> 1), tok = 2 * t + (q & 1);
+                const int64_t row = rb * GV_ROWS + rl;
+                if (row < p.N && tok < M) {
+                    const int a = vv[q] - sumq[q & 1];
+                    if (p.acc_out && layer == 0) p.acc_out[(int64_t)tok * p.N + row] = a;
+                    const float tv = __fmul_rn((float)a, sxv[q & 1]);
+                    const float y = epilogue(tv, sh_scale[rbi * GV_ROWS + rl], sh_bias[rbi * GV_ROWS + rl], p.clip_val);
+                    const OT yv = from_f32<OT>(y);
+                    if (p.n_peers == 0) {
+                        out[(int64_t)tok * p.ldo + row] = yv;
+                    } else {
+#pragma unroll 1
+                        for (int r = 0; r < p.n_peers; ++r)     // one small store per peer over NVLink (P2P-mapped memory)
+                            reinterpret_cast<OT*>(p.peers[r])[(int64_t)tok * p.ldo + row] = yv;
+                        wrote_peer = true;
+                    }
+                }
+            }
+        }
+    };
+    if (!FUSED && ct < M) {       // pre-quantised activations: scale and sum of codes come from the quantiser kernel
+        sh_sx[ct] = p.sx_in[layer * p.stride_s + ct];
+        sh_sumq[ct] = p.sumq_in[layer * p.stride_s + ct];
+    }
+
     int acc[4][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int q = 0; q < 4; ++q) acc[i][q] = 0;
     if (ntiles > 0) fetch(wlo, whi);
-    int ks = 0, rbi = 0;
+    int ks = 0, rbi = 0, round0 = 0;
 #pragma unroll 1
     for (int it = 0; it < ntiles; ++it) {
-        if (!(p.dbg & 1)) mma_half(acc, wlo[0], whi[0], bq[0]);
+        mma_half(acc, wlo[0], whi[0], bq[0]);
         if (it + 1 < ntiles) fetch(nlo, nhi);
-        if (!(p.dbg & 1)) mma_half(acc, wlo[1], whi[1], bq[1]);
-        if (p.dbg & 1) acc[0][0] += (int)(wlo[0].x ^ whi[0].y ^ wlo[1].z ^ whi[1].w);
+        mma_half(acc, wlo[1], whi[1], bq[1]);
 #pragma unroll
         for (int pp = 0; pp < 2; ++pp) { wlo[pp] = nlo[pp]; whi[pp] = nhi[pp]; }
-        if (++ks == p.nks) {
-            // recombine fields (exact: set i is a multiple of 4^i) and hand this warp's K-partials to the epilogue warp
+        if (++ks == nks_r) {
+            // recombine fields (exact: set i is a multiple of 4^i) and park this warp's K-partials
             uint4 v;
             v.x = (uint32_t)(acc[0][0] + (acc[1][0] >> 2) + (acc[2][0] >> 4) + (acc[3][0] >> 6));
             v.y = (uint32_t)(acc[0][1] + (acc[1][1] >> 2) + (acc[2][1] >> 4) + (acc[3][1] >> 6));
@@ -478,21 +472,19 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
             for (int i = 0; i < 4; ++i)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) acc[i][q] = 0;
-            const int slot = rbi % GV_SLOTS;
-            if (p.dbg & 16) { if (v.x == 0x12345u) slots[0] = v; } else {
-            if (rbi >= GV_SLOTS) mbar_wait(slot_empty(slot), (uint32_t)(rbi / GV_SLOTS - 1) & 1u);
-            slots[slot * GV_CTHREADS + warp * 32 + lane] = v;
-            __syncwarp();
-            if (lane == 0) mbar_arrive(slot_full(slot));
-            }
-            if (ct == 0 && rbi == 0) GV_STAMP(4);
-            if (ct == 0 && rbi == 1) GV_STAMP(13);
-            if (ct == 0 && rbi == 2) GV_STAMP(14);
+            slots[(size_t)(rbi - round0) * GV_CTHREADS + warp * 32 + lane] = v;
             ks = 0; ++rbi;
+            if (rbi - round0 == nslots_r || rbi == my_rbs) {
+                if (ct == 0 && rbi == my_rbs) GV_STAMP(5);
+                reduce_round(round0, rbi - round0);
+                round0 = rbi;
+                if (rbi < my_rbs) consumer_bar();     // the slots are rewritten by the next round
+            }
         }
-        if (p.nks > 1) load_b(ks);
+        if (nks_r > 1) load_b(ks);
     }
-    if (ct == 0) GV_STAMP(5);
+    if (wrote_peer) __threadfence_system();      // peer stores are visible system-wide before the grid completes
+    if (ct == 0) GV_STAMP(15);
 }
 
 // ---- parity aid: the activation quantisation of the fused prologue, written out densely (sx_out / qx_out of tb200_gemv)
@@ -598,35 +590,36 @@ static int get_weight_map(const uint8_t* packed, int64_t ld, int64_t N, int64_t 
 
 int gemv_nks(int64_t K) { return (int)((K + 4095) / 4096); }
 
-static size_t gemv_smem(int m, int nks, int stages, int nrb) {
-    return 1024 + (size_t)stages * GV_TILE_BYTES + (size_t)nks * 4096 * m + (size_t)GV_SLOTS * GV_CTHREADS * 16 +
-           GV_TOK * 4 + 2 * GV_TOK * GV_CWARPS * 4 + (2 * GV_MAX_STAGES + 2 * GV_SLOTS) * 8 + (size_t)nrb * GV_ROWS * 8 + 64;
+static size_t gemv_smem(int m, int nks, int stages, int nslots, int nrb) {
+    return 1024 + (size_t)stages * GV_TILE_BYTES + (size_t)nks * 4096 * m + (size_t)nslots * GV_CTHREADS * 16 +
+           2 * GV_TOK * 4 + 2 * GV_TOK * GV_CWARPS * 4 + 2 * GV_MAX_STAGES * 8 + (size_t)nrb * GV_ROWS * 8 + 64;
 }
-// Ring depth: the CTA's whole share of the weights when it fits (then every load is issued before the kernel
-// waits for its predecessor).  Two CTAs per SM must fit (this layer's and, under programmatic dependent
-// launch, the next layer's): 2 x (smem + 1 KB reserved) <= 228 KB.  Falls back to one CTA per SM for large K*M.
-static int gemv_pick_stages(int m, int nks, int nrb) {
+// Ring depth and reduction slots.  Preferred: the CTA's whole share of the weights in the ring (then every load is
+// issued before the kernel waits for its predecessor) and one slot per row block (one reduction round).  Two CTAs per
+// SM must fit (this layer's and, under programmatic dependent launch, the next layer's): 2 x (smem + 1 KB reserved)
+// <= 228 KB; large K*M falls back to one CTA per SM.
+static bool gemv_pick(int m, int nks, int nrb, int* stages, int* nslots) {
     const int tiles = nrb * nks;
     const int want = tiles < GV_MAX_STAGES ? tiles : GV_MAX_STAGES;
-    for (int s = want; s >= 2; --s)
-        if (gemv_smem(m, nks, s, nrb) <= 113 * 1024) return s;
-    for (int s = want; s >= 1; --s)
-        if (gemv_smem(m, nks, s, nrb) <= 227 * 1024) return s;
-    return 0;
+    const int smax = nrb < GV_MAX_SLOTS ? nrb : GV_MAX_SLOTS;
+    const size_t limits[2] = {113 * 1024, 227 * 1024};
+    for (int l = 0; l < 2; ++l)
+        for (int st = want; st >= (want < 2 ? want : 2); --st)
+            for (int ns = smax; ns >= (smax < 2 ? smax : 2); --ns)
+                if (gemv_smem(m, nks, st, ns, nrb) <= limits[l]) { *stages = st; *nslots = ns; return true; }
+    if (gemv_smem(m, nks, 1, 1, nrb) <= limits[1]) { *stages = 1; *nslots = 1; return true; }
+    return false;
 }
 
 template <typename XT, typename OT, bool FUSED, bool VEC>
 static int launch_gemv(const CUtensorMap& map, GemvParams p, int layers, cudaStream_t s) {
     const int ctas = p.row_blocks < sm_count() ? p.row_blocks : sm_count();
     p.nrb = (p.row_blocks + ctas - 1) / ctas;
-    p.stages = gemv_pick_stages(p.M, p.nks, p.nrb);
-    static const int inflight_env = getenv("TB200_GEMV_INFLIGHT") ? atoi(getenv("TB200_GEMV_INFLIGHT")) : 0;
-    p.inflight = inflight_env > 0 ? inflight_env : GV_MAX_STAGES;
-    static const int dbg_env = getenv("TB200_GEMV_DBG") ? atoi(getenv("TB200_GEMV_DBG")) : 0;
-    p.dbg = dbg_env;
-    if (p.inflight > p.stages) p.inflight = p.stages;
-    TB_REQUIRE(p.stages >= 1, "gemv: K=%lld N=%lld is too large for the shared-memory activation image", (long long)p.K, (long long)p.N);
-    const size_t smem = gemv_smem(p.M, p.nks, p.stages, p.nrb);
+    TB_REQUIRE(gemv_pick(p.M, p.nks, p.nrb, &p.stages, &p.nslots),
+               "gemv: K=%lld N=%lld is too large for the shared-memory activation image", (long long)p.K, (long long)p.N);
+    size_t smem = gemv_smem(p.M, p.nks, p.stages, p.nslots, p.nrb);
+    static const int solo_env = getenv("TB200_GEMV_SOLO") ? atoi(getenv("TB200_GEMV_SOLO")) : 0;
+    if (solo_env && smem < 120 * 1024) smem = 120 * 1024;     // experiment: one CTA per SM
     auto kern = gemv_mma_kernel<XT, OT, FUSED, VEC>;
     static size_t configured = 0;   // per instantiation
     if (smem > configured) {

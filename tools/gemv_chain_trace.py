@@ -28,11 +28,10 @@ with torch.cuda.stream(s):
     for _ in range(3): gr.replay()
 torch.cuda.synchronize()
 t = trace.cpu().numpy().reshape(T, 148, 64).astype(np.float64)
-names = {0: "start", 10: "tma_issued", 1: "wait_return", 2: "x_arrived(w0)", 6: "x_arrived(all)", 3: "quantised(w0)", 7: "image_done",
-         8: "b_loaded", 4: "tile0_done(w0)", 9: "epi_first_slot", 13: "tile1_done(w0)", 14: "tile2_done(w0)", 5: "consumers_done(w0)", 11: "epi_last_slot_full", 12: "epi_last_summed", 15: "end"}
+names = {0: "start", 1: "wait_return", 3: "image_done", 5: "mma_done(w0)", 15: "end"}
 base = t[0, :, 0][t[0, :, 0] > 0].min()
 for k in range(T):
-    print(f"--- kernel {k}: globaltimer ns relative to first traced kernel's first CTA start | clock64 relative to own CTA start (median, max)")
+    print(f"--- kernel {k}: clock64 relative to own CTA start | globaltimer ns relative to first traced kernel's first CTA start")
     for slot, n in names.items():
         col = t[k, :, 16 + slot]; ok = col > 0
         if ok.any():
@@ -42,9 +41,5 @@ for k in range(T):
                 gt = t[k, :, slot][t[k, :, slot] > 0] - base
                 gts = f"gt min {gt.min():8.0f} med {np.median(gt):8.0f} max {gt.max():8.0f}"
             print(f"  {n:20s} clk min {ck.min():8.0f} med {np.median(ck):8.0f} max {ck.max():8.0f} | {gts}")
-    for w, off in (("warp0", 32), ("warp5", 40)):
-        c = t[k, :, off:off + 6]
-        d = np.diff(c, axis=1)
-        print(f"  tile1 {w}: loop_top->half1_issued->fetched->half2_issued->slot_stored->loop_end (median clk):", np.median(d, axis=0), " loop_top rel start:", np.median(c[:, 0] - t[k, :, 16]))
 ends = [t[k, :, 15].max() - base for k in range(T)]
 print("kernel end-to-end period (ns):", np.diff(ends))
