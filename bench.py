@@ -280,7 +280,7 @@ def run_b200(args):
             e1.record(stream)
             stream.synchronize()
             t = e0.elapsed_time(e1) * 1e-3 / (reps * R)          # seconds per layer
-            nl = 1 if M <= 8 else 1 + (M + 7) // 8
+            nl = 1 if M <= 8 else (1 + (M + 7) // 8 if M <= 16 else 2)
             per_case.append({"K": K, "N": N, "M": M, "us_per_layer": t * 1e6, "launches_per_layer": nl,
                              "gbs": algorithmic_bytes(K, N, M) / t / 1e9,
                              "frac_hbm_measured": algorithmic_bytes(K, N, M) / t / 1e9 / pk["hbm_gbs"],

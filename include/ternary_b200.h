@@ -140,6 +140,7 @@ int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K, int64_t l
  * mma.sync.m16n8k32 (u8 x s8) integer dot products, fused epilogue.  K <= 20480. */
 #define TB200_GEMV_MAX_M 32
 #define TB200_GEMV_FUSED_M 8 /* tokens per pass over the weights; up to here tb200_linear_forward is ONE launch */
+#define TB200_LINEAR_GEMV_M 16 /* tb200_linear_forward: largest M served by GEMV passes, above it the tcgen05 GEMM */
 /* flags bit 0: programmatic dependent launch.  The kernel prefetches its packed weights
  * before waiting for the previous kernel in the stream (which normally produces x); the
  * caller asserts that the previous kernel does NOT write `packed`. */
@@ -184,7 +185,7 @@ int tb200_gemm_i8(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_
                   void* out, int out_dtype, int64_t ldo,
                   int32_t* acc_out, void* stream);
 
-/* Whole layer by token count: M <= 8 tb200_gemv (fused quantisation, one launch); M <= 32 quantise
+/* Whole layer by token count: M <= 8 tb200_gemv (fused quantisation, one launch); M <= 16 quantise
  * (layout 1) + tb200_gemv_q; larger M quantise (layout 1) + tb200_gemm_i8.
  * workspace: tb200_linear_workspace(M,K) bytes, 256-byte aligned. */
 size_t tb200_linear_workspace(int64_t M, int64_t K);

@@ -229,7 +229,8 @@ extern "C" int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K
     TB_REQUIRE(layout != 2 || ldq % 4096 == 0, "quant_act_i8: layout 2 needs ldq = 4096*ceil(K/4096)");
     const size_t es = dtype_size(dtype);
     const bool vec_ok = ((uintptr_t)x % 16 == 0) && ((ldx * es) % 16 == 0);
-    if ((ldq >> 4) <= 32 * GC) {
+    // few rows: one CTA per row (the warp-per-row kernel would leave most SMs idle and is latency-bound per row)
+    if ((ldq >> 4) <= 32 * GC && M >= 4 * (int64_t)sm_count()) {
         TB_DISPATCH_DTYPE(dtype, T,
             (quant_act_kernel<T><<<(unsigned)((M + QW - 1) / QW), QW * 32, 0, (cudaStream_t)stream>>>(
                 (const T*)x, M, K, ldx, q_x, ldq, s_x, sum_qx, layout, vec_ok)));

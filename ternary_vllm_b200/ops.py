@@ -264,7 +264,7 @@ def _workspace(M: int, K: int, device) -> torch.Tensor:
 def ternary_matmul(x: torch.Tensor, pw: torch.Tensor, scale, bias, clip_val: float, out_dtype=None, out=None) -> torch.Tensor:
     """``ops.ternary_matmul(x, pw, scale, bias, clip_val)`` (impl/tf/moondream/ternary.py:279-281):
     ``clip((x @ unpack(pw)^T) * scale + bias, +-clip_val)`` for ``x [..., K]`` and ``pw [N, ld]``.
-    M <= 32 tokens run the HBM-bound GEMV, larger M the tcgen05 kind::i8 GEMM."""
+    M <= 16 tokens run the HBM-bound GEMV (8 tokens per pass), larger M the tcgen05 kind::i8 GEMM."""
     _cuda(x, pw, scale, bias)
     K = x.shape[-1]
     N = pw.shape[0]
