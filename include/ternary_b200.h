@@ -175,6 +175,18 @@ int tb200_gemv_grouped(const void* x, int x_dtype, int64_t M, int64_t K, int64_t
                        void* out, int out_dtype, int64_t ldo, int64_t stride_out,
                        int count, int flags, void* stream);
 
+/* Streaming decode over a LIST of `count` layers of identical shape (M <= 32 tokens each): a per-layer activation
+ * quantiser launch followed by ONE persistent kernel that keeps the TMA weight stream running across layer boundaries
+ * (csrc/gemv_stream.cu).  Same arguments as tb200_gemv_grouped plus acc_out (optional, i32 [M,N], layer 0 only) and
+ * a 256-byte aligned workspace of tb200_gemv_stream_workspace(M, K, count) bytes.  count = 1 serves a single layer
+ * with 9..32 tokens in one pass over the weights.  Returns TB200_ENOTSUP when K*M exceeds the shared-memory image. */
+size_t tb200_gemv_stream_workspace(int64_t M, int64_t K, int count);
+int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                      const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                      const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                      void* out, int out_dtype, int64_t ldo, int64_t stride_out,
+                      int count, int32_t* acc_out, void* workspace, void* stream);
+
 /* Prefill shape: tcgen05.mma kind::i8, TMEM accumulators.  Takes PRE-QUANTISED activations
  * from tb200_quant_act_i8(kperm=1): q_x int8 [M, ldq], s_x [M], sum_qx [M].
  * Requires ldq % 16 == 0, ld_packed % 16 == 0, 16-byte aligned base pointers. */

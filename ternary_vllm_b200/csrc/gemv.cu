@@ -554,7 +554,7 @@ static std::mutex g_map_mu;
 static MapEntry g_maps[64];
 static int g_map_next = 0;
 
-static int get_weight_map(const uint8_t* packed, int64_t ld, int64_t N, int64_t stride, int layers, CUtensorMap* out, int* one_box) {
+int get_weight_map(const uint8_t* packed, int64_t ld, int64_t N, int64_t stride, int layers, CUtensorMap* out, int* one_box) {
     std::lock_guard<std::mutex> lk(g_map_mu);
     for (auto& e : g_maps)
         if (e.used && e.key.ptr == packed && e.key.ld == ld && e.key.N == N && e.key.stride == stride && e.key.layers == layers) {

@@ -1,0 +1,617 @@
+// gemv_stream.cu — persistent, warp-specialised decode GEMV over a LIST of layers (M <= 32 tokens).
+//
+// The single-layer kernel (gemv.cu) is latency-bound: activation prologue -> dot products -> reduction run one
+// after the other inside every CTA, and a 4096 x 11008 layer is only 1.7 us of HBM time.  This kernel keeps HBM
+// busy across layer boundaries instead.  One CTA per SM walks the global list of 16-row blocks of ALL layers
+// (block u = layer * row_blocks + rb, CTA b takes u = b, b + grid, ...: balanced to one block over the whole
+// list) with specialised warps that never wait for each other's phase:
+//   * warp 8  (1 thread): streams the packed weight tiles (16 rows x 1024 B, SWIZZLE_128B) through a ring of
+//     shared-memory stages with TMA, continuously across layers;
+//   * warp 9  (1 thread): brings the int8 activation image of the next layer (written once per layer by
+//     quant_image_kernel below, not by every CTA) into shared memory with cp.async.bulk while the MMA warps are
+//     still on the previous layer;
+//   * warps 0-7: warp w owns the w-th 128-byte K segment of every row: 4 LDS.128 of packed weights per tile, in-place
+//     field masks (4 LOP3 per 16 weights) and mma.sync.m16n8k32.u8.s8 against up to four groups of 8 tokens; the
+//     K-partials of a row block are parked in a ring of shared-memory slots;
+//   * warps 10-13: sum the eight partials of a slot and run the fused epilogue (-sum_qx, s_x * scale, bias, clip,
+//     store) off the critical path of the MMA warps.
+// Integer accumulators are the same as the single-layer kernel's (bit-exact); the epilogue arithmetic is identical.
+// Reference semantics: ScaledTernaryLinear.forward (binary/modules.py:101-109), ops.ternary_matmul
+// (impl/tf/moondream/ternary.py:279-281).
+#include <cstdlib>
+#include "tma.cuh"
+
+namespace tb200 {
+
+int get_weight_map(const uint8_t* packed, int64_t ld, int64_t N, int64_t stride, int layers, CUtensorMap* out, int* one_box);
+int gemv_nks(int64_t K);
+
+constexpr int SV_ROWS = 16;
+constexpr int SV_SEG = 128;
+constexpr int SV_TILE_BYTES = 16 * 1024;
+constexpr int SV_MMA_WARPS = 8;
+constexpr int SV_AUX_WARPS = 4;
+constexpr int SV_WARP_TILES = 8;       // tile producer
+constexpr int SV_WARP_IMAGE = 9;       // image producer
+constexpr int SV_WARP_AUX0 = 10;
+constexpr int SV_THREADS = (SV_WARP_AUX0 + SV_AUX_WARPS) * 32;   // 448
+constexpr int SV_MAX_STAGES = 12;
+constexpr int SV_MAX_SLOTS = 4;
+constexpr int SV_MAX_IMG = 2;
+constexpr int SV_TAIL = 256;           // blob tail: s_x[32] f32 | sum_qx[32] i32
+
+struct StreamParams {
+    const uint8_t* blob; int64_t blob_stride;      // per layer: activation image | s_x[32] | sum_qx[32]
+    const float* scale; const float* bias; int64_t stride_sb;
+    void* out; int64_t ldo; int64_t stride_out; int out_dtype;
+    int32_t* acc_out;
+    int64_t N;
+    int M, Mg, nks, row_blocks, layers;
+    int stages, nslots, nimg;
+    uint32_t img_bytes, grp_bytes;
+    float clip_val;
+    int one_box;
+};
+
+__device__ __forceinline__ void imma_s(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// uint4 index inside one token group's image: see gemv.cu (xq_vec); Mg = token stride
+__device__ __forceinline__ int img_vec(int sg, int pp, int i, int n, int t, int Mg) {
+    return ((((sg * 2 + pp) * 4 + i) * Mg + n) << 2) + t;
+}
+
+// NG = groups of 8 tokens; BREG = the B fragments of the whole layer live in registers (NG == 1, K <= 4096)
+template <int NG, bool BREG>
+__global__ void __launch_bounds__(SV_THREADS, 1)
+gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams p) {
+    extern __shared__ uint8_t smem_dyn[];
+    const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+    uint8_t* gbase = smem_dyn + (base - smem_u32(smem_dyn));
+    // ring[stages][16 KB] | image[nimg][img_bytes] | slots[nslots][NG][8 warps][32] uint4 | barriers
+    const uint32_t sRing = base;
+    const uint32_t img_pitch = (p.img_bytes + 127u) & ~127u;
+    uint8_t* img0 = gbase + (size_t)p.stages * SV_TILE_BYTES;
+    uint4* slots = reinterpret_cast<uint4*>(img0 + (size_t)p.nimg * img_pitch);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(slots + (size_t)p.nslots * NG * 256);
+    const uint32_t sBar = smem_u32(bars);
+    auto bar_full = [&](int s) { return sBar + 8u * s; };
+    auto bar_empty = [&](int s) { return sBar + 8u * (SV_MAX_STAGES + s); };
+    auto bar_ifull = [&](int b) { return sBar + 8u * (2 * SV_MAX_STAGES + b); };
+    auto bar_iempty = [&](int b) { return sBar + 8u * (2 * SV_MAX_STAGES + SV_MAX_IMG + b); };
+    auto bar_sfull = [&](int q) { return sBar + 8u * (2 * SV_MAX_STAGES + 2 * SV_MAX_IMG + q); };
+    auto bar_sempty = [&](int q) { return sBar + 8u * (2 * SV_MAX_STAGES + 2 * SV_MAX_IMG + SV_MAX_SLOTS + q); };
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int G = gridDim.x, b = blockIdx.x;
+    const int RB = p.row_blocks;
+    const int total = p.layers * RB;                       // row blocks of all layers
+    const int my_groups = total > b ? (total - b + G - 1) / G : 0;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&map_w);
+        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), SV_MMA_WARPS); }
+        for (int i = 0; i < p.nimg; ++i) { mbar_init(bar_ifull(i), 1); mbar_init(bar_iempty(i), SV_MMA_WARPS); }
+        for (int q = 0; q < p.nslots; ++q) { mbar_init(bar_sfull(q), SV_MMA_WARPS); mbar_init(bar_sempty(q), 1); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    asm volatile("griddepcontrol.launch_dependents;");
+
+    if (warp == SV_WARP_TILES) {
+        // ===================== weight tiles: independent of any previous kernel =====================
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0;
+            for (int u = b; u < total; u += G) {
+                const int l = u / RB, rb = u - l * RB;
+                for (int ks = 0; ks < p.nks; ++ks) {
+                    mbar_wait(bar_empty(s), ph ^ 1u);
+                    mbar_arrive_expect_tx(bar_full(s), SV_TILE_BYTES);
+                    if (p.one_box) {
+                        tma_load_4d(sRing + s * SV_TILE_BYTES, &map_w, bar_full(s), 0, rb * SV_ROWS, ks * 8, l);
+                    } else {
+#pragma unroll
+                        for (int sg = 0; sg < 8; ++sg)
+                            tma_load_3d(sRing + s * SV_TILE_BYTES + sg * (SV_ROWS * SV_SEG), &map_w, bar_full(s),
+                                        ks * 256 + sg * 32, rb * SV_ROWS, l);
+                    }
+                    if (++s == p.stages) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == SV_WARP_IMAGE) {
+        // ===================== activation images (written by the preceding quantiser kernel) =====================
+        if (lane == 0) {
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            int cur = -1, j = 0;
+            for (int u = b; u < total; u += G) {
+                const int l = u / RB;
+                if (l == cur) continue;
+                cur = l;
+                const int ib = j % p.nimg;
+                const uint32_t par = (uint32_t)(j / p.nimg) & 1u;
+                mbar_wait(bar_iempty(ib), par ^ 1u);
+                mbar_arrive_expect_tx(bar_ifull(ib), p.img_bytes);
+                const uint8_t* src = p.blob + (int64_t)l * p.blob_stride;
+                const uint32_t dst = smem_u32(img0) + ib * img_pitch;
+                // chunks of <= 32 KB keep each bulk request small enough to interleave with the weight stream
+                for (uint32_t off = 0; off < p.img_bytes; off += 32768u) {
+                    const uint32_t n = p.img_bytes - off < 32768u ? p.img_bytes - off : 32768u;
+                    bulk_g2s(dst + off, src + off, n, bar_ifull(ib));
+                }
+                ++j;
+            }
+        }
+    } else if (warp < SV_MMA_WARPS) {
+        // ===================== dot products =====================
+        const int g = lane >> 2, t = lane & 3;
+        const uint32_t sSeg = warp * (SV_ROWS * SV_SEG) + g * SV_SEG;
+        const uint32_t phys0 = ((2 * t) ^ g) << 4, phys1 = ((2 * t + 1) ^ g) << 4;
+        const int nks = p.nks, stages = p.stages, nslots = p.nslots, nimg = p.nimg, Mg = p.Mg;
+        int ntok[NG];                                   // tokens of each group
+#pragma unroll
+        for (int q = 0; q < NG; ++q) { const int r = p.M - 8 * q; ntok[q] = r < 0 ? 0 : (r > 8 ? 8 : r); }
+        int s = 0; uint32_t ph = 0;
+        uint4 wlo[2], whi[2], nlo[2], nhi[2];
+        auto fetch = [&](uint4 (&lo)[2], uint4 (&hi)[2]) {
+            mbar_wait(bar_full(s), ph);
+            const uint8_t* seg = gbase + s * SV_TILE_BYTES + sSeg;
+            lo[0] = *reinterpret_cast<const uint4*>(seg + phys0);
+            hi[0] = *reinterpret_cast<const uint4*>(seg + 8 * SV_SEG + phys0);
+            lo[1] = *reinterpret_cast<const uint4*>(seg + phys1);
+            hi[1] = *reinterpret_cast<const uint4*>(seg + 8 * SV_SEG + phys1);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_empty(s));            // the tile lives in registers now
+            if (++s == stages) { s = 0; ph ^= 1u; }
+        };
+        int acc[NG][4][4];
+#pragma unroll
+        for (int q = 0; q < NG; ++q)
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) acc[q][i][e] = 0;
+        uint4 bq[2][4];                                  // BREG: B fragments of the layer
+        const uint4* img = nullptr;
+        int cur = -1, j = 0, ib = 0, slot_no = 0;
+        const int ntiles = my_groups * nks;
+        if (ntiles > 0) fetch(wlo, whi);
+        int u = b, ks = 0, l = 0;
+        // one half (pp) of a tile: 8 (BREG / NG == 1) or 8 * NG MMAs
+        auto half = [&](const uint4& lo, const uint4& hi, int pp, int ksl) {
+            if (BREG) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t mk = 0x03030303u << (2 * i);
+                    imma_s(acc[0][i], lo.x & mk, hi.x & mk, lo.y & mk, hi.y & mk, bq[pp][i].x, bq[pp][i].y);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t mk = 0x03030303u << (2 * i);
+                    imma_s(acc[0][i], lo.z & mk, hi.z & mk, lo.w & mk, hi.w & mk, bq[pp][i].z, bq[pp][i].w);
+                }
+            } else if (NG <= 2) {
+                uint4 bv[NG][4];
+#pragma unroll
+                for (int q = 0; q < NG; ++q)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        bv[q][i] = g < ntok[q] ? img[q * (p.grp_bytes >> 4) + img_vec(ksl * 8 + warp, pp, i, g, t, Mg)]
+                                               : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t mk = 0x03030303u << (2 * i);
+                    const uint32_t a0 = lo.x & mk, a1 = hi.x & mk, a2 = lo.y & mk, a3 = hi.y & mk;
+#pragma unroll
+                    for (int q = 0; q < NG; ++q) imma_s(acc[q][i], a0, a1, a2, a3, bv[q][i].x, bv[q][i].y);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t mk = 0x03030303u << (2 * i);
+                    const uint32_t a0 = lo.z & mk, a1 = hi.z & mk, a2 = lo.w & mk, a3 = hi.w & mk;
+#pragma unroll
+                    for (int q = 0; q < NG; ++q) imma_s(acc[q][i], a0, a1, a2, a3, bv[q][i].z, bv[q][i].w);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 bv[NG];
+#pragma unroll
+                    for (int q = 0; q < NG; ++q)
+                        bv[q] = g < ntok[q] ? img[q * (p.grp_bytes >> 4) + img_vec(ksl * 8 + warp, pp, i, g, t, Mg)]
+                                            : make_uint4(0u, 0u, 0u, 0u);
+                    const uint32_t mk = 0x03030303u << (2 * i);
+                    {
+                        const uint32_t a0 = lo.x & mk, a1 = hi.x & mk, a2 = lo.y & mk, a3 = hi.y & mk;
+#pragma unroll
+                        for (int q = 0; q < NG; ++q) imma_s(acc[q][i], a0, a1, a2, a3, bv[q].x, bv[q].y);
+                    }
+                    {
+                        const uint32_t a0 = lo.z & mk, a1 = hi.z & mk, a2 = lo.w & mk, a3 = hi.w & mk;
+#pragma unroll
+                        for (int q = 0; q < NG; ++q) imma_s(acc[q][i], a0, a1, a2, a3, bv[q].z, bv[q].w);
+                    }
+                }
+            }
+        };
+#pragma unroll 1
+        for (int it = 0; it < ntiles; ++it) {
+            if (ks == 0) {
+                l = u / RB;
+                if (l != cur) {                          // first row block of a new layer: its image must have landed
+                    cur = l;
+                    ib = j % nimg;
+                    mbar_wait(bar_ifull(ib), (uint32_t)(j / nimg) & 1u);
+                    img = reinterpret_cast<const uint4*>(img0 + ib * img_pitch);
+                    if (BREG) {
+#pragma unroll
+                        for (int pp = 0; pp < 2; ++pp)
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                bq[pp][i] = g < ntok[0] ? img[img_vec(warp, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_iempty(ib));      // the image buffer can take the next layer
+                    }
+                    ++j;
+                }
+            }
+            half(wlo[0], whi[0], 0, ks);
+            if (it + 1 < ntiles) fetch(nlo, nhi);
+            half(wlo[1], whi[1], 1, ks);
+#pragma unroll
+            for (int pp = 0; pp < 2; ++pp) { wlo[pp] = nlo[pp]; whi[pp] = nhi[pp]; }
+            if (++ks == nks) {
+                // recombine the four fields (exact: set i is a multiple of 4^i) and park this warp's K-partials
+                const int sq = slot_no % nslots;
+                mbar_wait(bar_sempty(sq), ((uint32_t)(slot_no / nslots) & 1u) ^ 1u);
+#pragma unroll
+                for (int q = 0; q < NG; ++q) {
+                    uint4 v;
+                    v.x = (uint32_t)(acc[q][0][0] + (acc[q][1][0] >> 2) + (acc[q][2][0] >> 4) + (acc[q][3][0] >> 6));
+                    v.y = (uint32_t)(acc[q][0][1] + (acc[q][1][1] >> 2) + (acc[q][2][1] >> 4) + (acc[q][3][1] >> 6));
+                    v.z = (uint32_t)(acc[q][0][2] + (acc[q][1][2] >> 2) + (acc[q][2][2] >> 4) + (acc[q][3][2] >> 6));
+                    v.w = (uint32_t)(acc[q][0][3] + (acc[q][1][3] >> 2) + (acc[q][2][3] >> 4) + (acc[q][3][3] >> 6));
+                    slots[(size_t)(sq * NG + q) * 256 + warp * 32 + lane] = v;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc[q][i][e] = 0;
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_sfull(sq));
+                ++slot_no;
+                ks = 0;
+                u += G;
+                if (!BREG && (u >= total || u / RB != cur)) {            // last row block of this layer for this CTA
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_iempty(ib));
+                }
+            }
+        }
+    } else {
+        // ===================== reduction of the K-partials + fused epilogue =====================
+        const int a = warp - SV_WARP_AUX0;
+        const int g = lane >> 2, t = lane & 3;
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        int cur = -1;
+        float sxv[NG][2]; int sumq[NG][2];
+#pragma unroll
+        for (int q = 0; q < NG; ++q) { sxv[q][0] = sxv[q][1] = 0.0f; sumq[q][0] = sumq[q][1] = 0; }
+        // slot buffer a belongs to aux warp a (a parity wait must never be more than one phase ahead of its barrier)
+        for (int sn = a; a < p.nslots && sn < my_groups; sn += p.nslots) {
+            const int u = b + sn * G;
+            const int l = u / RB, rb = u - l * RB;
+            // everything that comes from global memory is requested before the wait for the partial sums
+            const int64_t row0 = (int64_t)rb * SV_ROWS + g, row1 = row0 + 8;
+            const float* sc = p.scale ? p.scale + (int64_t)l * p.stride_sb : nullptr;
+            const float* bi = p.bias ? p.bias + (int64_t)l * p.stride_sb : nullptr;
+            const float sc0 = (sc && row0 < p.N) ? sc[row0] : 1.0f, sc1 = (sc && row1 < p.N) ? sc[row1] : 1.0f;
+            const float bi0 = (bi && row0 < p.N) ? bi[row0] : 0.0f, bi1 = (bi && row1 < p.N) ? bi[row1] : 0.0f;
+            if (l != cur) {
+                cur = l;
+                const uint8_t* tail = p.blob + (int64_t)l * p.blob_stride + p.img_bytes;
+                const float* sx = reinterpret_cast<const float*>(tail);
+                const int* sq = reinterpret_cast<const int*>(tail + 128);
+#pragma unroll
+                for (int q = 0; q < NG; ++q)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int tok = 8 * q + 2 * t + e;
+                        sxv[q][e] = tok < p.M ? sx[tok] : 0.0f;
+                        sumq[q][e] = tok < p.M ? sq[tok] : 0;
+                    }
+            }
+            const int sq_i = a;
+            mbar_wait(bar_sfull(sq_i), (uint32_t)(sn / p.nslots) & 1u);
+#pragma unroll
+            for (int q = 0; q < NG; ++q) {
+                const uint4* sl = slots + (size_t)(sq_i * NG + q) * 256 + lane;
+                int vv[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int w = 0; w < SV_MMA_WARPS; ++w) {
+                    const uint4 v = sl[w * 32];
+                    vv[0] += (int)v.x; vv[1] += (int)v.y; vv[2] += (int)v.z; vv[3] += (int)v.w;
+                }
+                // fragment: vv0 (row g, tok 2t), vv1 (row g, tok 2t+1), vv2 (row g+8, tok 2t), vv3 (row g+8, tok 2t+1)
+#pragma unroll
+                for (int e4 = 0; e4 < 4; ++e4) {
+                    const int e = e4 & 1, hi = e4 >> 1;
+                    const int tok = 8 * q + 2 * t + e;
+                    const int64_t row = hi ? row1 : row0;
+                    if (row < p.N && tok < p.M) {
+                        const int av = vv[e4] - sumq[q][e];
+                        if (p.acc_out && l == 0) p.acc_out[(int64_t)tok * p.N + row] = av;
+                        const float tv = __fmul_rn((float)av, sxv[q][e]);
+                        const float y = epilogue(tv, hi ? sc1 : sc0, hi ? bi1 : bi0, p.clip_val);
+                        const int64_t o = (int64_t)l * p.stride_out + (int64_t)tok * p.ldo + row;
+                        if (p.out_dtype == TB200_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(y);
+                        else if (p.out_dtype == TB200_F16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(y);
+                        else reinterpret_cast<float*>(p.out)[o] = y;
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_sempty(sq_i));
+        }
+    }
+}
+
+// ---- activation quantiser writing the per-layer blob: image (token groups of 8, see img_vec) | s_x | sum_qx ----
+// One CTA per (token, layer).  Same arithmetic as tb200_quant_act_i8 (quant.cu).
+template <typename T>
+__global__ void __launch_bounds__(256)
+quant_image_kernel(const T* __restrict__ x, int64_t ldx, int64_t stride_x, int64_t K, int M, int Mg, int nks,
+                   uint8_t* __restrict__ blob, int64_t blob_stride, uint32_t img_bytes, uint32_t grp_bytes, bool vec_ok) {
+    __shared__ float sh_max[8];
+    __shared__ int sh_sum[8];
+    asm volatile("griddepcontrol.launch_dependents;");            // the GEMV may start streaming weights now
+    asm volatile("griddepcontrol.wait;" ::: "memory");            // the previous kernel may still be reading the blob
+    const int m = blockIdx.x, layer = blockIdx.y;
+    const T* xr = x + (int64_t)layer * stride_x + (int64_t)m * ldx;
+    uint8_t* bl = blob + (int64_t)layer * blob_stride;
+    uint32_t* image = reinterpret_cast<uint32_t*>(bl + (size_t)(m >> 3) * grp_bytes);
+    const int n = m & 7;
+    const int groups = nks * 256;
+    constexpr int QC = 2;                                  // groups per thread kept in registers between the passes (K <= 8192)
+    const bool cached = nks <= QC;
+    float vc[QC][16];
+    auto load16 = [&](int gi, float (&v)[16]) {
+        if (vec_ok && 16 * (int64_t)gi + 16 <= K) {
+            const uint4* q = reinterpret_cast<const uint4*>(xr + 16 * (int64_t)gi);
+#pragma unroll
+            for (int jv = 0; jv < (int)sizeof(T); ++jv) {
+                const uint4 u4 = q[jv];
+                const T* e = reinterpret_cast<const T*>(&u4);
+#pragma unroll
+                for (int tt = 0; tt < 16 / (int)sizeof(T); ++tt) v[jv * (16 / (int)sizeof(T)) + tt] = to_f32(e[tt]);
+            }
+        } else {
+#pragma unroll
+            for (int tt = 0; tt < 16; ++tt) {
+                const int64_t k = 16 * (int64_t)gi + tt;
+                v[tt] = k < K ? to_f32(xr[k]) : 0.0f;
+            }
+        }
+    };
+    float amax = 0.0f;
+    if (cached) {
+#pragma unroll
+        for (int c = 0; c < QC; ++c)
+            if (c < nks) load16(threadIdx.x + 256 * c, vc[c]);
+#pragma unroll
+        for (int c = 0; c < QC; ++c)
+            if (c < nks) {
+#pragma unroll
+                for (int tt = 0; tt < 16; ++tt) amax = fmaxf(amax, fabsf(vc[c][tt]));
+            }
+    } else {
+        for (int gi = threadIdx.x; 16 * (int64_t)gi < K; gi += 256) {
+            float v[16];
+            load16(gi, v);
+#pragma unroll
+            for (int tt = 0; tt < 16; ++tt) amax = fmaxf(amax, fabsf(v[tt]));
+        }
+    }
+    amax = warp_max(amax);
+    if ((threadIdx.x & 31) == 0) sh_max[threadIdx.x >> 5] = amax;
+    __syncthreads();
+    amax = sh_max[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) amax = fmaxf(amax, sh_max[i]);
+    const float s = amax > 0.0f ? __fdiv_rn(amax, 127.0f) : 1.0f;
+    const float inv = amax > 0.0f ? __fdiv_rn(127.0f, amax) : 1.0f;
+    int lsum = 0;
+    auto emit = [&](int gi, const float (&v)[16]) {
+        int qv[16];
+#pragma unroll
+        for (int tt = 0; tt < 16; ++tt) {
+            float r = __fmul_rn(v[tt], inv);
+            r = fminf(fmaxf(r, -127.0f), 127.0f);
+            qv[tt] = __float_as_int(__fadd_rn(r, 12582912.0f)) - 0x4B400000;
+            lsum += qv[tt];
+        }
+        const int c = gi >> 2, jw = gi & 3, lc = c & 7;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {     // word i = elements i, 4+i, 8+i, 12+i (field i of bytes 0..3 of packed word gi)
+            const uint32_t w = (uint32_t)(qv[i] & 0xff) | ((uint32_t)(qv[4 + i] & 0xff) << 8) |
+                               ((uint32_t)(qv[8 + i] & 0xff) << 16) | ((uint32_t)(qv[12 + i] & 0xff) << 24);
+            image[img_vec(c >> 3, lc & 1, i, n, lc >> 1, Mg) * 4 + jw] = w;
+        }
+    };
+    if (cached) {
+#pragma unroll
+        for (int c = 0; c < QC; ++c)
+            if (c < nks) emit(threadIdx.x + 256 * c, vc[c]);
+    } else {
+        for (int gi = threadIdx.x; gi < groups; gi += 256) {
+            float v[16];
+            load16(gi, v);
+            emit(gi, v);
+        }
+    }
+    lsum = warp_sum(lsum);
+    if ((threadIdx.x & 31) == 0) sh_sum[threadIdx.x >> 5] = lsum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tsum = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) tsum += sh_sum[i];
+        reinterpret_cast<float*>(bl + img_bytes)[m] = s;
+        reinterpret_cast<int*>(bl + img_bytes + 128)[m] = tsum;
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------
+struct StreamGeom { int Mg, ng, nks; uint32_t grp_bytes, img_bytes; int64_t blob_stride; };
+static StreamGeom stream_geom(int64_t M, int64_t K) {
+    StreamGeom gm;
+    gm.Mg = (int)(M < 8 ? M : 8);
+    gm.ng = (int)((M + 7) / 8);
+    gm.nks = gemv_nks(K);
+    gm.grp_bytes = (uint32_t)(gm.nks * 4096 * gm.Mg);
+    gm.img_bytes = gm.grp_bytes * (uint32_t)gm.ng;
+    gm.blob_stride = ((int64_t)gm.img_bytes + SV_TAIL + 255) / 256 * 256;
+    return gm;
+}
+static size_t stream_smem(const StreamGeom& gm, int stages, int nslots, int nimg) {
+    const size_t img_pitch = ((size_t)gm.img_bytes + 127) & ~(size_t)127;
+    return 1024 + (size_t)stages * SV_TILE_BYTES + nimg * img_pitch + (size_t)nslots * gm.ng * 4096 +
+           (2 * SV_MAX_STAGES + 2 * SV_MAX_IMG + 2 * SV_MAX_SLOTS) * 8 + 64;
+}
+// ring depth first (bytes in flight), then a second image buffer, then more slots
+static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslots, int* nimg) {
+    const size_t limit = 227 * 1024;
+    static const int st_env = getenv("TB200_STREAM_STAGES") ? atoi(getenv("TB200_STREAM_STAGES")) : 0;
+    const int want_st = st_env > 0 ? st_env : 8;
+    const int min_st = gm.nks < 3 ? 3 : (gm.nks < SV_MAX_STAGES ? gm.nks : SV_MAX_STAGES);
+    for (int img = breg ? 1 : 2; img >= 1; --img)
+        for (int st = want_st; st >= min_st; --st)
+            for (int ns = (gm.ng > 2 ? 2 : SV_MAX_SLOTS); ns >= 2; --ns)
+                if (stream_smem(gm, st, ns, img) <= limit) { *stages = st; *nslots = ns; *nimg = img; return true; }
+    return false;
+}
+
+bool gemv_stream_fits(int64_t M, int64_t K) {
+    if (M < 1 || M > TB200_GEMV_MAX_M) return false;
+    const StreamGeom gm = stream_geom(M, K);
+    int a, b2, c;
+    return stream_pick(gm, gm.ng == 1 && gm.nks == 1, &a, &b2, &c);
+}
+
+template <int NG, bool BREG>
+static int launch_stream(const CUtensorMap& map, const StreamParams& p, size_t smem, int ctas, bool pdl, cudaStream_t s) {
+    auto kern = gemv_stream_kernel<NG, BREG>;
+    static size_t configured = 0;
+    if (smem > configured) {
+        TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)ctas, 1, 1);
+    cfg.blockDim = dim3(SV_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    TB_CUDA(cudaLaunchKernelEx(&cfg, kern, map, p));
+    TB_LAUNCH_CHECK();
+    return TB200_OK;
+}
+
+int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                     const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                     const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                     void* out, int out_dtype, int64_t ldo, int64_t stride_out,
+                     int32_t* acc_out, int layers, void* workspace, cudaStream_t s) {
+    const StreamGeom gm = stream_geom(M, K);
+    const bool breg = gm.ng == 1 && gm.nks == 1;
+    StreamParams p = {};
+    if (!stream_pick(gm, breg, &p.stages, &p.nslots, &p.nimg)) {
+        set_error("gemv_stream: M=%lld K=%lld does not fit the shared-memory activation image", (long long)M, (long long)K);
+        return TB200_ENOTSUP;
+    }
+    CUtensorMap map;
+    int one_box = 0;
+    int rc = get_weight_map(packed, ld_packed, N, stride_packed, layers, &map, &one_box);
+    if (rc) return rc;
+    // 1. activations -> int8 image per layer (one CTA per token and layer)
+    uint8_t* blob = (uint8_t*)workspace;
+    const size_t xs = dtype_size(x_dtype);
+    const bool vec_ok = ((uintptr_t)x % 16 == 0) && ((ldx * xs) % 16 == 0) && ((stride_x * xs) % 16 == 0);
+    {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)M, (unsigned)layers, 1);
+        cfg.blockDim = dim3(256, 1, 1);
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        TB_DISPATCH_DTYPE(x_dtype, T,
+            TB_CUDA(cudaLaunchKernelEx(&cfg, quant_image_kernel<T>, (const T*)x, ldx, stride_x, K, (int)M, gm.Mg, gm.nks,
+                                       blob, gm.blob_stride, gm.img_bytes, gm.grp_bytes, vec_ok)));
+        TB_LAUNCH_CHECK();
+    }
+    // 2. the persistent GEMV
+    p.blob = blob; p.blob_stride = gm.blob_stride;
+    p.scale = scale; p.bias = bias; p.stride_sb = stride_sb;
+    p.out = out; p.ldo = ldo; p.stride_out = stride_out; p.out_dtype = out_dtype;
+    p.acc_out = acc_out;
+    p.N = N; p.M = (int)M; p.Mg = gm.Mg; p.nks = gm.nks;
+    p.row_blocks = (int)((N + SV_ROWS - 1) / SV_ROWS);
+    p.layers = layers;
+    p.img_bytes = gm.img_bytes; p.grp_bytes = gm.grp_bytes;
+    p.clip_val = fabsf(clip_val);
+    p.one_box = one_box;
+    const int64_t total = (int64_t)p.row_blocks * layers;
+    const int ctas = (int)(total < sm_count() ? total : sm_count());
+    const size_t smem = stream_smem(gm, p.stages, p.nslots, p.nimg);
+    switch (gm.ng) {
+        case 1: return breg ? launch_stream<1, true>(map, p, smem, ctas, true, s) : launch_stream<1, false>(map, p, smem, ctas, true, s);
+        case 2: return launch_stream<2, false>(map, p, smem, ctas, true, s);
+        case 3: return launch_stream<3, false>(map, p, smem, ctas, true, s);
+        default: return launch_stream<4, false>(map, p, smem, ctas, true, s);
+    }
+}
+
+}  // namespace tb200
+
+using namespace tb200;
+
+extern "C" size_t tb200_gemv_stream_workspace(int64_t M, int64_t K, int count) {
+    if (M < 1 || K < 1 || count < 1) return 256;
+    const StreamGeom gm = stream_geom(M, K);
+    return (size_t)gm.blob_stride * (size_t)count + 256;
+}
+
+extern "C" int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                                 const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                                 const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                                 void* out, int out_dtype, int64_t ldo, int64_t stride_out,
+                                 int count, int32_t* acc_out, void* workspace, void* stream) {
+    TB_DEVICE_OR_RETURN();
+    if (M == 0 || N == 0 || count == 0) return TB200_OK;
+    TB_REQUIRE(x && packed && out && workspace, "gemv_stream: null pointer");
+    TB_REQUIRE(M >= 1 && M <= TB200_GEMV_MAX_M, "gemv_stream: M=%lld out of range [1,%d]", (long long)M, TB200_GEMV_MAX_M);
+    TB_REQUIRE(K > 0 && N > 0 && ldx >= K && ldo >= N, "gemv_stream: bad shape M=%lld K=%lld N=%lld", (long long)M, (long long)K, (long long)N);
+    TB_REQUIRE(dtype_ok(x_dtype) && dtype_ok(out_dtype), "gemv_stream: bad dtype");
+    const int64_t kc = (K + 63) / 64;
+    TB_REQUIRE(ld_packed % 16 == 0 && ld_packed >= kc * 16, "gemv_stream: ld_packed=%lld must be a multiple of 16 and >= %lld",
+               (long long)ld_packed, (long long)(kc * 16));
+    TB_REQUIRE((uintptr_t)packed % 16 == 0 && stride_packed % 16 == 0, "gemv_stream: packed weights must be 16-byte aligned");
+    TB_REQUIRE((uintptr_t)workspace % 256 == 0, "gemv_stream: workspace must be 256-byte aligned");
+    TB_REQUIRE(count >= 1 && count <= 65535, "gemv_stream: bad layer count %d", count);
+    return gemv_stream_impl(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N, scale, bias, stride_sb,
+                            clip_val, out, out_dtype, ldo, stride_out, acc_out, count, workspace, (cudaStream_t)stream);
+}

@@ -290,5 +290,40 @@ def ternary_matmul(x: torch.Tensor, pw: torch.Tensor, scale, bias, clip_val: flo
     return out.reshape(*x.shape[:-1], N)
 
 
+def gemv_stream(xs, packed, scale, bias, clip_val, out=None, out_dtype=None, debug=False, workspace=None):
+    """Streaming decode over a list of layers in one persistent launch (``tb200_gemv_stream``).
+    ``xs [R, M, K]`` (or ``[M, K]`` shared by all layers), ``packed [R, N, ld]``, ``scale``/``bias`` ``[R, N]`` or None
+    -> ``out [R, M, N]``.  ``debug`` also returns the integer accumulators of layer 0."""
+    _cuda(xs, packed, scale, bias)
+    assert packed.dim() == 3 and packed.dtype == torch.uint8 and packed.stride(2) == 1
+    R, N, _ = packed.shape
+    shared_x = xs.dim() == 2
+    assert xs.stride(-1) == 1
+    M, K = xs.shape[-2], xs.shape[-1]
+    out_dtype = out_dtype or xs.dtype
+    if out is None:
+        out = torch.empty((R, M, N), dtype=out_dtype, device=xs.device)
+    assert out.shape == (R, M, N) and out.stride(2) == 1
+    if scale is not None:
+        assert scale.dtype == torch.float32 and scale.shape == (R, N) and scale.stride(1) == 1
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.shape == (R, N) and bias.stride(1) == 1
+    stride_sb = scale.stride(0) if scale is not None else (bias.stride(0) if bias is not None else 0)
+    if scale is not None and bias is not None:
+        assert scale.stride(0) == bias.stride(0)
+    need = L.lib().tb200_gemv_stream_workspace(M, K, R)
+    if workspace is None:
+        workspace = torch.empty((need,), dtype=torch.uint8, device=xs.device)
+    assert workspace.numel() >= need
+    acc = torch.empty((M, N), dtype=torch.int32, device=xs.device) if debug else None
+    with torch.cuda.device(xs.device):
+        L.check(L.lib().tb200_gemv_stream(xs.data_ptr(), _dt(xs), M, K, xs.stride(-2), 0 if shared_x else xs.stride(0),
+                                          packed.data_ptr(), packed.stride(1), packed.stride(0), N,
+                                          _ptr(scale), _ptr(bias), stride_sb, float(clip_val),
+                                          out.data_ptr(), _DT[out.dtype], out.stride(1), out.stride(0), R,
+                                          _ptr(acc), workspace.data_ptr(), _stream(xs)), "gemv_stream")
+    return (out, acc) if debug else out
+
+
 def launch_count() -> int:
     return int(L.lib().tb200_launch_count())

@@ -54,5 +54,16 @@ for M in Ms:
                                            scale.data_ptr(), bias.data_ptr(), N, 100.0, out.data_ptr(), L.TB200_BF16, N, M * N,
                                            R, 0, torch.cuda.current_stream().cuda_stream), "grouped")
         res["grouped 1 launch"] = timeit(grouped) / R
+    ws = torch.empty(lib.tb200_gemv_stream_workspace(M, K, R), dtype=torch.uint8, device=dev)
+    try:
+        res["stream 2 launches"] = timeit(lambda: ops.gemv_stream(xs, packed, scale, bias, 100.0, out=out, workspace=ws)) / R
+        gr2 = torch.cuda.CUDAGraph()
+        s2 = torch.cuda.Stream()
+        with torch.cuda.stream(s2):
+            with torch.cuda.graph(gr2, stream=s2):
+                ops.gemv_stream(xs, packed, scale, bias, 100.0, out=out, workspace=ws)
+        res["stream graph"] = timeit(gr2.replay) / R
+    except Exception as e:
+        print("stream:", e)
     for k, t in res.items():
         print(f"K={K} N={N} M={M} R={R} {k:20s} {t*1e6:8.2f} us/layer {bytes_layer/t/1e9:8.1f} GB/s")

@@ -27,6 +27,20 @@ if case == "gemv":
         for r in range(R):
             ops.gemv(x, packed[r], scale, bias, 100.0, pdl=True, out=out)
     torch.cuda.synchronize()
+elif case == "stream":
+    M = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    K, N, R = 4096, 11008, 25
+    ld = ops.packed_pitch(K)
+    packed = torch.empty(R, N, ld, dtype=torch.uint8, device=dev)
+    for r in range(R):
+        packed[r] = ops.quantize_pack(torch.randn(N, K, generator=g, device=dev).clip_(-1, 1), "ternary")
+    scale = torch.full((R, N), 1 / math.sqrt(K), device=dev)
+    bias = torch.randn(R, N, generator=g, device=dev)
+    xs = torch.randn(R, M, K, generator=g, device=dev, dtype=torch.bfloat16)
+    out = torch.empty(R, M, N, device=dev, dtype=torch.bfloat16)
+    for _ in range(3):
+        ops.gemv_stream(xs, packed, scale, bias, 100.0, out=out)
+    torch.cuda.synchronize()
 elif case == "grouped":
     from ternary_vllm_b200 import _lib as L
     M = int(sys.argv[2]) if len(sys.argv) > 2 else 1
