@@ -13,7 +13,7 @@
 //   * warps 0-7: warp w owns the w-th 128-byte K segment of every row: 4 LDS.128 of packed weights per tile, in-place
 //     field masks (4 LOP3 per 16 weights) and mma.sync.m16n8k32.u8.s8 against up to four groups of 8 tokens; the
 //     K-partials of a row block are parked in a ring of shared-memory slots;
-//   * warps 10-13: sum the eight partials of a slot and run the fused epilogue (-sum_qx, s_x * scale, bias, clip,
+//   * warps 10-11: sum the eight partials of a slot and run the fused epilogue (-sum_qx, s_x * scale, bias, clip,
 //     store) off the critical path of the MMA warps.
 // Integer accumulators are the same as the single-layer kernel's (bit-exact); the epilogue arithmetic is identical.
 // Reference semantics: ScaledTernaryLinear.forward (binary/modules.py:101-109), ops.ternary_matmul
@@ -30,7 +30,7 @@ constexpr int SV_ROWS = 16;
 constexpr int SV_SEG = 128;
 constexpr int SV_TILE_BYTES = 16 * 1024;
 constexpr int SV_MMA_WARPS = 8;
-constexpr int SV_AUX_WARPS = 4;
+constexpr int SV_AUX_WARPS = 2;       // nslots is a multiple of this: every slot buffer has exactly one consumer warp
 constexpr int SV_WARP_TILES = 8;       // tile producer
 constexpr int SV_WARP_IMAGE = 9;       // image producer
 constexpr int SV_WARP_AUX0 = 10;
@@ -180,10 +180,14 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 for (int e = 0; e < 4; ++e) acc[q][i][e] = 0;
         uint4 bq[2][4];                                  // BREG: B fragments of the layer
         const uint4* img = nullptr;
-        int cur = -1, j = 0, ib = 0, slot_no = 0;
         const int ntiles = my_groups * nks;
         if (ntiles > 0) fetch(wlo, whi);
-        int u = b, ks = 0, l = 0;
+        // position in the global row-block list, advanced without divisions: u = l * RB + rb, step G = Gq * RB + Gr
+        const int Gq = G / RB, Gr = G - Gq * RB;
+        int l = b / RB, rb = b - l * RB;
+        int cur = -1, ks = 0, it = 0;
+        int ib = 0, ib_cur = 0; uint32_t ipar = 0;       // image buffer ring
+        int sq = 0; uint32_t spar = 0;                   // partial-sum slot ring
         // one half (pp) of a tile: 8 (BREG / NG == 1) or 8 * NG MMAs
         auto half = [&](const uint4& lo, const uint4& hi, int pp, int ksl) {
             if (BREG) {
@@ -241,36 +245,31 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 }
             }
         };
-#pragma unroll 1
-        for (int it = 0; it < ntiles; ++it) {
-            if (ks == 0) {
-                l = u / RB;
-                if (l != cur) {                          // first row block of a new layer: its image must have landed
-                    cur = l;
-                    ib = j % nimg;
-                    mbar_wait(bar_ifull(ib), (uint32_t)(j / nimg) & 1u);
-                    img = reinterpret_cast<const uint4*>(img0 + ib * img_pitch);
-                    if (BREG) {
+        // one tile: A fragments in (lo, hi); the next tile's fragments are fetched into (nl, nh) between the halves
+        auto step = [&](uint4 (&lo)[2], uint4 (&hi)[2], uint4 (&nl)[2], uint4 (&nh)[2]) {
+            if (ks == 0 && l != cur) {                   // first row block of a new layer: its image must have landed
+                cur = l;
+                ib_cur = ib;
+                mbar_wait(bar_ifull(ib), ipar);
+                img = reinterpret_cast<const uint4*>(img0 + ib * img_pitch);
+                if (BREG) {
 #pragma unroll
-                        for (int pp = 0; pp < 2; ++pp)
+                    for (int pp = 0; pp < 2; ++pp)
 #pragma unroll
-                            for (int i = 0; i < 4; ++i)
-                                bq[pp][i] = g < ntok[0] ? img[img_vec(warp, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(bar_iempty(ib));      // the image buffer can take the next layer
-                    }
-                    ++j;
+                        for (int i = 0; i < 4; ++i)
+                            bq[pp][i] = g < ntok[0] ? img[img_vec(warp, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_iempty(ib));      // the image buffer can take the next layer
                 }
+                if (++ib == nimg) { ib = 0; ipar ^= 1u; }
             }
-            half(wlo[0], whi[0], 0, ks);
-            if (it + 1 < ntiles) fetch(nlo, nhi);
-            half(wlo[1], whi[1], 1, ks);
-#pragma unroll
-            for (int pp = 0; pp < 2; ++pp) { wlo[pp] = nlo[pp]; whi[pp] = nhi[pp]; }
+            half(lo[0], hi[0], 0, ks);
+            if (++it < ntiles) fetch(nl, nh);
+            half(lo[1], hi[1], 1, ks);
             if (++ks == nks) {
                 // recombine the four fields (exact: set i is a multiple of 4^i) and park this warp's K-partials
-                const int sq = slot_no % nslots;
-                mbar_wait(bar_sempty(sq), ((uint32_t)(slot_no / nslots) & 1u) ^ 1u);
+                ks = 0;
+                mbar_wait(bar_sempty(sq), spar ^ 1u);
 #pragma unroll
                 for (int q = 0; q < NG; ++q) {
                     uint4 v;
@@ -286,14 +285,20 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_sfull(sq));
-                ++slot_no;
-                ks = 0;
-                u += G;
-                if (!BREG && (u >= total || u / RB != cur)) {            // last row block of this layer for this CTA
+                if (++sq == nslots) { sq = 0; spar ^= 1u; }
+                l += Gq; rb += Gr;
+                if (rb >= RB) { rb -= RB; ++l; }
+                if (!BREG && (it >= ntiles || l != cur)) {              // last row block of this layer for this CTA
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_iempty(ib));
+                    if (lane == 0) mbar_arrive(bar_iempty(ib_cur));
                 }
             }
+        };
+#pragma unroll 1
+        while (it < ntiles) {
+            step(wlo, whi, nlo, nhi);
+            if (it >= ntiles) break;
+            step(nlo, nhi, wlo, whi);
         }
     } else {
         // ===================== reduction of the K-partials + fused epilogue =====================
@@ -304,16 +309,36 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
         float sxv[NG][2]; int sumq[NG][2];
 #pragma unroll
         for (int q = 0; q < NG; ++q) { sxv[q][0] = sxv[q][1] = 0.0f; sumq[q][0] = sumq[q][1] = 0; }
-        // slot buffer a belongs to aux warp a (a parity wait must never be more than one phase ahead of its barrier)
-        for (int sn = a; a < p.nslots && sn < my_groups; sn += p.nslots) {
+        // aux warp a takes row blocks a, a + 2, ...: slot buffer q is only ever waited on by warp q % 2, in phase order
+        // (a parity wait must never be more than one phase ahead of its barrier).
+        // scale/bias of a row block are read once per launch (cold: DRAM latency), so the loads for this warp's NEXT
+        // slot are issued before the current one is reduced.
+        auto load_sb = [&](int sn, float (&v)[4]) {
+            v[0] = v[1] = 1.0f; v[2] = v[3] = 0.0f;
+            if (sn < my_groups) {
+                const int u = b + sn * G;
+                const int l = u / RB, rb = u - l * RB;
+                const int64_t row0 = (int64_t)rb * SV_ROWS + g, row1 = row0 + 8;
+                if (p.scale) {
+                    const float* sc = p.scale + (int64_t)l * p.stride_sb;
+                    if (row0 < p.N) v[0] = sc[row0];
+                    if (row1 < p.N) v[1] = sc[row1];
+                }
+                if (p.bias) {
+                    const float* bi = p.bias + (int64_t)l * p.stride_sb;
+                    if (row0 < p.N) v[2] = bi[row0];
+                    if (row1 < p.N) v[3] = bi[row1];
+                }
+            }
+        };
+        float sbn[4];
+        load_sb(a, sbn);
+        for (int sn = a; sn < my_groups; sn += SV_AUX_WARPS) {
             const int u = b + sn * G;
             const int l = u / RB, rb = u - l * RB;
-            // everything that comes from global memory is requested before the wait for the partial sums
             const int64_t row0 = (int64_t)rb * SV_ROWS + g, row1 = row0 + 8;
-            const float* sc = p.scale ? p.scale + (int64_t)l * p.stride_sb : nullptr;
-            const float* bi = p.bias ? p.bias + (int64_t)l * p.stride_sb : nullptr;
-            const float sc0 = (sc && row0 < p.N) ? sc[row0] : 1.0f, sc1 = (sc && row1 < p.N) ? sc[row1] : 1.0f;
-            const float bi0 = (bi && row0 < p.N) ? bi[row0] : 0.0f, bi1 = (bi && row1 < p.N) ? bi[row1] : 0.0f;
+            const float sc0 = sbn[0], sc1 = sbn[1], bi0 = sbn[2], bi1 = sbn[3];
+            load_sb(sn + SV_AUX_WARPS, sbn);
             if (l != cur) {
                 cur = l;
                 const uint8_t* tail = p.blob + (int64_t)l * p.blob_stride + p.img_bytes;
@@ -328,7 +353,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                         sumq[q][e] = tok < p.M ? sq[tok] : 0;
                     }
             }
-            const int sq_i = a;
+            const int sq_i = sn % p.nslots;
             mbar_wait(bar_sfull(sq_i), (uint32_t)(sn / p.nslots) & 1u);
 #pragma unroll
             for (int q = 0; q < NG; ++q) {
@@ -493,7 +518,7 @@ static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslot
     const int min_st = gm.nks < 3 ? 3 : (gm.nks < SV_MAX_STAGES ? gm.nks : SV_MAX_STAGES);
     for (int img = breg ? 1 : 2; img >= 1; --img)
         for (int st = want_st; st >= min_st; --st)
-            for (int ns = (gm.ng > 2 ? 2 : SV_MAX_SLOTS); ns >= 2; --ns)
+            for (int ns = (gm.ng > 2 ? 2 : SV_MAX_SLOTS); ns >= 2; ns -= SV_AUX_WARPS)
                 if (stream_smem(gm, st, ns, img) <= limit) { *stages = st; *nslots = ns; *nimg = img; return true; }
     return false;
 }
