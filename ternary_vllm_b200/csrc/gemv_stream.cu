@@ -30,13 +30,10 @@ constexpr int SV_ROWS = 16;
 constexpr int SV_SEG = 128;
 constexpr int SV_TILE_BYTES = 16 * 1024;
 constexpr int SV_MMA_WARPS = 8;
-constexpr int SV_AUX_WARPS = 2;       // nslots is a multiple of this: every slot buffer has exactly one consumer warp
-constexpr int SV_WARP_TILES = 8;       // tile producer
-constexpr int SV_WARP_IMAGE = 9;       // image producer
-constexpr int SV_WARP_AUX0 = 10;
-constexpr int SV_THREADS = (SV_WARP_AUX0 + SV_AUX_WARPS) * 32;   // 448
+// warp roles for TEAMS teams of 8 MMA warps: [0, 8T) MMA | 8T tile producer | 8T+1 image producer | 8T+2.. aux
+constexpr int sv_threads(int teams, int aux) { return (8 * teams + 2 + aux) * 32; }
 constexpr int SV_MAX_STAGES = 12;
-constexpr int SV_MAX_SLOTS = 4;
+constexpr int SV_MAX_SLOTS = 8;
 constexpr int SV_MAX_IMG = 2;
 constexpr int SV_TAIL = 256;           // blob tail: s_x[32] f32 | sum_qx[32] i32
 
@@ -51,6 +48,7 @@ struct StreamParams {
     uint32_t img_bytes, grp_bytes;
     float clip_val;
     int one_box;
+    int dbg;          // experiments: bit 0 skips the MMAs (memory-stream ceiling of the kernel)
 };
 
 __device__ __forceinline__ void imma_s(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
@@ -69,8 +67,10 @@ __device__ __forceinline__ int img_vec(int sg, int pp, int i, int n, int t, int 
 }
 
 // NG = groups of 8 tokens; BREG = the B fragments of the whole layer live in registers (NG == 1, K <= 4096)
-template <int NG, bool BREG>
-__global__ void __launch_bounds__(SV_THREADS, 1)
+// TEAMS = 2: two teams of 8 MMA warps take alternate row blocks (4 warps per scheduler hide the LOP3 -> IMMA latency
+// that bounds the 8-warp version; used for NG == 1, where 96 registers per thread suffice)
+template <int NG, bool BREG, int TEAMS, int AUX>
+__global__ void __launch_bounds__(sv_threads(TEAMS, AUX), 1)
 gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams p) {
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
@@ -98,13 +98,14 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_w);
         for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), SV_MMA_WARPS); }
-        for (int i = 0; i < p.nimg; ++i) { mbar_init(bar_ifull(i), 1); mbar_init(bar_iempty(i), SV_MMA_WARPS); }
+        for (int i = 0; i < p.nimg; ++i) { mbar_init(bar_ifull(i), 1); mbar_init(bar_iempty(i), SV_MMA_WARPS * TEAMS); }
         for (int q = 0; q < p.nslots; ++q) { mbar_init(bar_sfull(q), SV_MMA_WARPS); mbar_init(bar_sempty(q), 1); }
         mbar_fence_init();
     }
     __syncthreads();
     asm volatile("griddepcontrol.launch_dependents;");
 
+    constexpr int SV_WARP_TILES = 8 * TEAMS, SV_WARP_IMAGE = 8 * TEAMS + 1, SV_WARP_AUX0 = 8 * TEAMS + 2;
     if (warp == SV_WARP_TILES) {
         // ===================== weight tiles: independent of any previous kernel =====================
         if (lane == 0) {
@@ -149,10 +150,11 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 ++j;
             }
         }
-    } else if (warp < SV_MMA_WARPS) {
+    } else if (warp < SV_MMA_WARPS * TEAMS) {
         // ===================== dot products =====================
         const int g = lane >> 2, t = lane & 3;
-        const uint32_t sSeg = warp * (SV_ROWS * SV_SEG) + g * SV_SEG;
+        const int team = warp >> 3, wseg = warp & 7;       // K segment of this warp
+        const uint32_t sSeg = wseg * (SV_ROWS * SV_SEG) + g * SV_SEG;
         const uint32_t phys0 = ((2 * t) ^ g) << 4, phys1 = ((2 * t + 1) ^ g) << 4;
         const int nks = p.nks, stages = p.stages, nslots = p.nslots, nimg = p.nimg, Mg = p.Mg;
         int ntok[NG];                                   // tokens of each group
@@ -160,8 +162,8 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
         for (int q = 0; q < NG; ++q) { const int r = p.M - 8 * q; ntok[q] = r < 0 ? 0 : (r > 8 ? 8 : r); }
         int s = 0; uint32_t ph = 0;
         uint4 wlo[2], whi[2], nlo[2], nhi[2];
-        auto fetch = [&](uint4 (&lo)[2], uint4 (&hi)[2]) {
-            mbar_wait(bar_full(s), ph);
+        auto fetch = [&](uint4 (&lo)[2], uint4 (&hi)[2], uint32_t ready) {
+            if (!ready) mbar_wait(bar_full(s), ph);
             const uint8_t* seg = gbase + s * SV_TILE_BYTES + sSeg;
             lo[0] = *reinterpret_cast<const uint4*>(seg + phys0);
             hi[0] = *reinterpret_cast<const uint4*>(seg + 8 * SV_SEG + phys0);
@@ -181,7 +183,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
         uint4 bq[2][4];                                  // BREG: B fragments of the layer
         const uint4* img = nullptr;
         const int ntiles = my_groups * nks;
-        if (ntiles > 0) fetch(wlo, whi);
+        if (TEAMS == 1 && ntiles > 0) fetch(wlo, whi, 0u);
         // position in the global row-block list, advanced without divisions: u = l * RB + rb, step G = Gq * RB + Gr
         const int Gq = G / RB, Gr = G - Gq * RB;
         int l = b / RB, rb = b - l * RB;
@@ -190,6 +192,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
         int sq = 0; uint32_t spar = 0;                   // partial-sum slot ring
         // one half (pp) of a tile: 8 (BREG / NG == 1) or 8 * NG MMAs
         auto half = [&](const uint4& lo, const uint4& hi, int pp, int ksl) {
+            if (p.dbg & 1) { acc[0][0][0] += (int)(lo.x ^ hi.y); return; }
             if (BREG) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -207,7 +210,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 for (int q = 0; q < NG; ++q)
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
-                        bv[q][i] = g < ntok[q] ? img[q * (p.grp_bytes >> 4) + img_vec(ksl * 8 + warp, pp, i, g, t, Mg)]
+                        bv[q][i] = g < ntok[q] ? img[q * (p.grp_bytes >> 4) + img_vec(ksl * 8 + wseg, pp, i, g, t, Mg)]
                                                : make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -229,7 +232,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                     uint4 bv[NG];
 #pragma unroll
                     for (int q = 0; q < NG; ++q)
-                        bv[q] = g < ntok[q] ? img[q * (p.grp_bytes >> 4) + img_vec(ksl * 8 + warp, pp, i, g, t, Mg)]
+                        bv[q] = g < ntok[q] ? img[q * (p.grp_bytes >> 4) + img_vec(ksl * 8 + wseg, pp, i, g, t, Mg)]
                                             : make_uint4(0u, 0u, 0u, 0u);
                     const uint32_t mk = 0x03030303u << (2 * i);
                     {
@@ -257,14 +260,15 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                     for (int pp = 0; pp < 2; ++pp)
 #pragma unroll
                         for (int i = 0; i < 4; ++i)
-                            bq[pp][i] = g < ntok[0] ? img[img_vec(warp, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
+                            bq[pp][i] = g < ntok[0] ? img[img_vec(wseg, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar_iempty(ib));      // the image buffer can take the next layer
                 }
                 if (++ib == nimg) { ib = 0; ipar ^= 1u; }
             }
+            const uint32_t ready = mbar_test(bar_full(s), ph);      // next tile's stage, tested ahead of its use
             half(lo[0], hi[0], 0, ks);
-            if (++it < ntiles) fetch(nl, nh);
+            if (++it < ntiles) fetch(nl, nh, ready);
             half(lo[1], hi[1], 1, ks);
             if (++ks == nks) {
                 // recombine the four fields (exact: set i is a multiple of 4^i) and park this warp's K-partials
@@ -277,7 +281,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                     v.y = (uint32_t)(acc[q][0][1] + (acc[q][1][1] >> 2) + (acc[q][2][1] >> 4) + (acc[q][3][1] >> 6));
                     v.z = (uint32_t)(acc[q][0][2] + (acc[q][1][2] >> 2) + (acc[q][2][2] >> 4) + (acc[q][3][2] >> 6));
                     v.w = (uint32_t)(acc[q][0][3] + (acc[q][1][3] >> 2) + (acc[q][2][3] >> 4) + (acc[q][3][3] >> 6));
-                    slots[(size_t)(sq * NG + q) * 256 + warp * 32 + lane] = v;
+                    slots[(size_t)(sq * NG + q) * 256 + wseg * 32 + lane] = v;
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -294,51 +298,117 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 }
             }
         };
+        if constexpr (TEAMS == 1) {
 #pragma unroll 1
-        while (it < ntiles) {
-            step(wlo, whi, nlo, nhi);
-            if (it >= ntiles) break;
-            step(nlo, nhi, wlo, whi);
+            while (it < ntiles) {
+                step(wlo, whi, nlo, nhi);
+                if (it >= ntiles) break;
+                step(nlo, nhi, wlo, whi);
+            }
+        } else {
+            // Two teams: every team walks the whole row-block list (layer changes, ring and slot positions) but computes
+            // only its own row blocks (gi & 1 == team); no cross-tile register prefetch, the other team's warps cover
+            // the latencies.
+            (void)step;
+#pragma unroll 1
+            for (int gi = 0; gi < my_groups; ++gi) {
+                if (l != cur) {
+                    cur = l;
+                    ib_cur = ib;
+                    mbar_wait(bar_ifull(ib), ipar);
+                    img = reinterpret_cast<const uint4*>(img0 + ib * img_pitch);
+                    if (BREG) {
+#pragma unroll
+                        for (int pp = 0; pp < 2; ++pp)
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                bq[pp][i] = g < ntok[0] ? img[img_vec(wseg, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_iempty(ib));
+                    }
+                    if (++ib == nimg) { ib = 0; ipar ^= 1u; }
+                }
+                if ((gi & 1) == team) {
+#pragma unroll 1
+                    for (int k2 = 0; k2 < nks; ++k2) {
+                        fetch(wlo, whi, 0u);
+                        half(wlo[0], whi[0], 0, k2);
+                        half(wlo[1], whi[1], 1, k2);
+                    }
+                    mbar_wait(bar_sempty(sq), spar ^ 1u);
+                    uint4 v;
+                    v.x = (uint32_t)(acc[0][0][0] + (acc[0][1][0] >> 2) + (acc[0][2][0] >> 4) + (acc[0][3][0] >> 6));
+                    v.y = (uint32_t)(acc[0][0][1] + (acc[0][1][1] >> 2) + (acc[0][2][1] >> 4) + (acc[0][3][1] >> 6));
+                    v.z = (uint32_t)(acc[0][0][2] + (acc[0][1][2] >> 2) + (acc[0][2][2] >> 4) + (acc[0][3][2] >> 6));
+                    v.w = (uint32_t)(acc[0][0][3] + (acc[0][1][3] >> 2) + (acc[0][2][3] >> 4) + (acc[0][3][3] >> 6));
+                    slots[(size_t)(sq * NG) * 256 + wseg * 32 + lane] = v;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc[0][i][e] = 0;
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_sfull(sq));
+                } else {
+                    s += nks;                                            // the other team's tiles
+                    while (s >= stages) { s -= stages; ph ^= 1u; }
+                }
+                if (++sq == nslots) { sq = 0; spar ^= 1u; }
+                l += Gq; rb += Gr;
+                if (rb >= RB) { rb -= RB; ++l; }
+                if (!BREG && (gi + 1 == my_groups || l != cur)) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_iempty(ib_cur));
+                }
+            }
         }
     } else {
         // ===================== reduction of the K-partials + fused epilogue =====================
+        // Aux warp a takes row blocks a, a + AUX, ...; nslots is a multiple of AUX, so slot buffer q is only ever waited
+        // on by warp q % AUX, in phase order (a parity wait must never be more than one phase ahead of its barrier).
         const int a = warp - SV_WARP_AUX0;
         const int g = lane >> 2, t = lane & 3;
         asm volatile("griddepcontrol.wait;" ::: "memory");
-        int cur = -1;
-        float sxv[NG][2]; int sumq[NG][2];
-#pragma unroll
-        for (int q = 0; q < NG; ++q) { sxv[q][0] = sxv[q][1] = 0.0f; sumq[q][0] = sumq[q][1] = 0; }
-        // aux warp a takes row blocks a, a + 2, ...: slot buffer q is only ever waited on by warp q % 2, in phase order
-        // (a parity wait must never be more than one phase ahead of its barrier).
-        // scale/bias of a row block are read once per launch (cold: DRAM latency), so the loads for this warp's NEXT
-        // slot are issued before the current one is reduced.
-        auto load_sb = [&](int sn, float (&v)[4]) {
+        // position of this warp's current row block and of the one it prefetches for, advanced without divisions
+        const int step = AUX * G;
+        const int Sq = step / RB, Sr = step - Sq * RB;
+        struct Pos { int l, rb; };
+        auto advance = [&](Pos& q) { q.l += Sq; q.rb += Sr; if (q.rb >= RB) { q.rb -= RB; ++q.l; } };
+        Pos cp, np;
+        { const int u = b + a * G; cp.l = u / RB; cp.rb = u - cp.l * RB; }
+        np = cp;
+        // scale/bias of a row block are read once per launch (cold in L2): the loads for this warp's NEXT row block are
+        // issued before the current one is reduced
+        auto load_sb = [&](const Pos& q, bool valid, float (&v)[4]) {
             v[0] = v[1] = 1.0f; v[2] = v[3] = 0.0f;
-            if (sn < my_groups) {
-                const int u = b + sn * G;
-                const int l = u / RB, rb = u - l * RB;
-                const int64_t row0 = (int64_t)rb * SV_ROWS + g, row1 = row0 + 8;
+            if (valid) {
+                const int64_t row0 = (int64_t)q.rb * SV_ROWS + g, row1 = row0 + 8;
                 if (p.scale) {
-                    const float* sc = p.scale + (int64_t)l * p.stride_sb;
+                    const float* sc = p.scale + (int64_t)q.l * p.stride_sb;
                     if (row0 < p.N) v[0] = sc[row0];
                     if (row1 < p.N) v[1] = sc[row1];
                 }
                 if (p.bias) {
-                    const float* bi = p.bias + (int64_t)l * p.stride_sb;
+                    const float* bi = p.bias + (int64_t)q.l * p.stride_sb;
                     if (row0 < p.N) v[2] = bi[row0];
                     if (row1 < p.N) v[3] = bi[row1];
                 }
             }
         };
+        int cur = -1;
+        float sxv[NG][2]; int sumq[NG][2];
+#pragma unroll
+        for (int q = 0; q < NG; ++q) { sxv[q][0] = sxv[q][1] = 0.0f; sumq[q][0] = sumq[q][1] = 0; }
         float sbn[4];
-        load_sb(a, sbn);
-        for (int sn = a; sn < my_groups; sn += SV_AUX_WARPS) {
-            const int u = b + sn * G;
-            const int l = u / RB, rb = u - l * RB;
-            const int64_t row0 = (int64_t)rb * SV_ROWS + g, row1 = row0 + 8;
+        load_sb(np, a < my_groups, sbn);
+        int sq_i = a % p.nslots; uint32_t spar = (uint32_t)(a / p.nslots) & 1u;     // AUX <= nslots: a / nslots == 0
+        const bool store_acc = p.acc_out != nullptr;
+#pragma unroll 1
+        for (int sn = a; sn < my_groups; sn += AUX) {
+            const int l = cp.l;
+            const int64_t row0 = (int64_t)cp.rb * SV_ROWS + g, row1 = row0 + 8;
             const float sc0 = sbn[0], sc1 = sbn[1], bi0 = sbn[2], bi1 = sbn[3];
-            load_sb(sn + SV_AUX_WARPS, sbn);
+            advance(np);
+            load_sb(np, sn + AUX < my_groups, sbn);
             if (l != cur) {
                 cur = l;
                 const uint8_t* tail = p.blob + (int64_t)l * p.blob_stride + p.img_bytes;
@@ -353,37 +423,44 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                         sumq[q][e] = tok < p.M ? sq[tok] : 0;
                     }
             }
-            const int sq_i = sn % p.nslots;
-            mbar_wait(bar_sfull(sq_i), (uint32_t)(sn / p.nslots) & 1u);
+            mbar_wait(bar_sfull(sq_i), spar);
+            int vv[NG][4];
 #pragma unroll
             for (int q = 0; q < NG; ++q) {
                 const uint4* sl = slots + (size_t)(sq_i * NG + q) * 256 + lane;
-                int vv[4] = {0, 0, 0, 0};
+                vv[q][0] = vv[q][1] = vv[q][2] = vv[q][3] = 0;
 #pragma unroll
                 for (int w = 0; w < SV_MMA_WARPS; ++w) {
                     const uint4 v = sl[w * 32];
-                    vv[0] += (int)v.x; vv[1] += (int)v.y; vv[2] += (int)v.z; vv[3] += (int)v.w;
+                    vv[q][0] += (int)v.x; vv[q][1] += (int)v.y; vv[q][2] += (int)v.z; vv[q][3] += (int)v.w;
                 }
-                // fragment: vv0 (row g, tok 2t), vv1 (row g, tok 2t+1), vv2 (row g+8, tok 2t), vv3 (row g+8, tok 2t+1)
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_sempty(sq_i));      // the partial sums live in registers: the slot is free again
+            sq_i += AUX;
+            if (sq_i >= p.nslots) { sq_i -= p.nslots; spar ^= 1u; }
+            // fragment: vv0 (row g, tok 2t), vv1 (row g, tok 2t+1), vv2 (row g+8, tok 2t), vv3 (row g+8, tok 2t+1)
+            const int64_t obase = (int64_t)l * p.stride_out;
+#pragma unroll
+            for (int q = 0; q < NG; ++q) {
 #pragma unroll
                 for (int e4 = 0; e4 < 4; ++e4) {
                     const int e = e4 & 1, hi = e4 >> 1;
                     const int tok = 8 * q + 2 * t + e;
                     const int64_t row = hi ? row1 : row0;
                     if (row < p.N && tok < p.M) {
-                        const int av = vv[e4] - sumq[q][e];
-                        if (p.acc_out && l == 0) p.acc_out[(int64_t)tok * p.N + row] = av;
+                        const int av = vv[q][e4] - sumq[q][e];
+                        if (store_acc && l == 0) p.acc_out[(int64_t)tok * p.N + row] = av;
                         const float tv = __fmul_rn((float)av, sxv[q][e]);
                         const float y = epilogue(tv, hi ? sc1 : sc0, hi ? bi1 : bi0, p.clip_val);
-                        const int64_t o = (int64_t)l * p.stride_out + (int64_t)tok * p.ldo + row;
+                        const int64_t o = obase + (int64_t)tok * p.ldo + row;
                         if (p.out_dtype == TB200_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(y);
                         else if (p.out_dtype == TB200_F16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(y);
                         else reinterpret_cast<float*>(p.out)[o] = y;
                     }
                 }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_sempty(sq_i));
+            advance(cp);
         }
     }
 }
@@ -518,7 +595,7 @@ static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslot
     const int min_st = gm.nks < 3 ? 3 : (gm.nks < SV_MAX_STAGES ? gm.nks : SV_MAX_STAGES);
     for (int img = breg ? 1 : 2; img >= 1; --img)
         for (int st = want_st; st >= min_st; --st)
-            for (int ns = (gm.ng > 2 ? 2 : SV_MAX_SLOTS); ns >= 2; ns -= SV_AUX_WARPS)
+            for (int ns = (gm.ng > 2 ? 2 : gm.ng == 2 ? 4 : 8); ns >= (gm.ng == 1 ? 4 : 2); ns -= (gm.ng == 1 ? 4 : 2))   // multiples of the aux-warp count
                 if (stream_smem(gm, st, ns, img) <= limit) { *stages = st; *nslots = ns; *nimg = img; return true; }
     return false;
 }
@@ -530,9 +607,9 @@ bool gemv_stream_fits(int64_t M, int64_t K) {
     return stream_pick(gm, gm.ng == 1 && gm.nks == 1, &a, &b2, &c);
 }
 
-template <int NG, bool BREG>
+template <int NG, bool BREG, int TEAMS, int AUX>
 static int launch_stream(const CUtensorMap& map, const StreamParams& p, size_t smem, int ctas, bool pdl, cudaStream_t s) {
-    auto kern = gemv_stream_kernel<NG, BREG>;
+    auto kern = gemv_stream_kernel<NG, BREG, TEAMS, AUX>;
     static size_t configured = 0;
     if (smem > configured) {
         TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -540,7 +617,7 @@ static int launch_stream(const CUtensorMap& map, const StreamParams& p, size_t s
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas, 1, 1);
-    cfg.blockDim = dim3(SV_THREADS, 1, 1);
+    cfg.blockDim = dim3(sv_threads(TEAMS, AUX), 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
@@ -599,14 +676,21 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     p.img_bytes = gm.img_bytes; p.grp_bytes = gm.grp_bytes;
     p.clip_val = fabsf(clip_val);
     p.one_box = one_box;
+    static const int dbg_env = getenv("TB200_STREAM_DBG") ? atoi(getenv("TB200_STREAM_DBG")) : 0;
+    p.dbg = dbg_env;
     const int64_t total = (int64_t)p.row_blocks * layers;
     const int ctas = (int)(total < sm_count() ? total : sm_count());
     const size_t smem = stream_smem(gm, p.stages, p.nslots, p.nimg);
     switch (gm.ng) {
-        case 1: return breg ? launch_stream<1, true>(map, p, smem, ctas, true, s) : launch_stream<1, false>(map, p, smem, ctas, true, s);
-        case 2: return launch_stream<2, false>(map, p, smem, ctas, true, s);
-        case 3: return launch_stream<3, false>(map, p, smem, ctas, true, s);
-        default: return launch_stream<4, false>(map, p, smem, ctas, true, s);
+        case 1: {
+            static const int teams = getenv("TB200_STREAM_TEAMS") ? atoi(getenv("TB200_STREAM_TEAMS")) : 2;
+            if (teams == 2)
+                return breg ? launch_stream<1, true, 2, 4>(map, p, smem, ctas, true, s) : launch_stream<1, false, 2, 4>(map, p, smem, ctas, true, s);
+            return breg ? launch_stream<1, true, 1, 4>(map, p, smem, ctas, true, s) : launch_stream<1, false, 1, 4>(map, p, smem, ctas, true, s);
+        }
+        case 2: return launch_stream<2, false, 1, 2>(map, p, smem, ctas, true, s);
+        case 3: return launch_stream<3, false, 1, 2>(map, p, smem, ctas, true, s);
+        default: return launch_stream<4, false, 1, 2>(map, p, smem, ctas, true, s);
     }
 }
 

@@ -8,7 +8,7 @@ dev = torch.device("cuda:0")
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 N = int(sys.argv[2]) if len(sys.argv) > 2 else 11008
 Ms = [int(a) for a in sys.argv[3].split(",")] if len(sys.argv) > 3 else [1]
-R = max(8, int(math.ceil(2.2 * 126e6 / (N * K / 4))))
+R = int(os.environ.get("TB200_PROBE_R", 0)) or max(8, int(math.ceil(2.2 * 126e6 / (N * K / 4))))
 g = torch.Generator(device=dev).manual_seed(0)
 ld = ops.packed_pitch(K)
 packed = torch.empty(R, N, ld, dtype=torch.uint8, device=dev)
