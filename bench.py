@@ -168,7 +168,9 @@ def run_reference(args):
 METRIC = "packed-ternary decode GEMV sweep, algorithmic HBM bytes / time"
 CONFIG_N1 = {"workload": "configs[1] decode GEMV sweep: ternary Linear 4096x4096 and 4096x11008, batch 1/8/32, "
                          "bf16 activations, ring of distinct layers per case",
-             "l2_policy": "inputs larger than L2 (ring of 64 x 4.2 MB / 32 x 11.3 MB packed layers per case)"}
+             "l2_policy": "inputs larger than L2 (ring of 67 x 4.2 MB / 64 x 11.3 MB distinct packed layers per case, "
+                          "every layer read once per step)",
+             "api": "tb200_gemv_stream: one call per sweep case over its ring of layers"}
 CONFIG_TP = {"workload": "configs[4] 7B-class decoder projections 4096x11008, 11008x4096, 4096x32000 (lm_head), "
                          "N-sharded across ranks, decode batch 1/8/32, all-gather of the output shards",
              "l2_policy": "inputs larger than L2 (ring of distinct layers per shape)"}
@@ -194,12 +196,10 @@ class Ring:
 
 def run_b200(args):
     import torch
-    import torch.distributed as dist
     import ternary_vllm_b200 as tb
     from ternary_vllm_b200 import ops, _lib as L
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
         from bench_tp import run_tp
@@ -211,21 +211,30 @@ def run_b200(args):
 
     rings = {}
     for (K, N) in SHAPES:
-        R = max(8, int(math.ceil(2.2 * L2_BYTES / (N * K / 4))))
+        R = max(RING_MIN, int(math.ceil(2.2 * L2_BYTES / (N * K / 4))))
         rings[(K, N)] = Ring(K, N, R, dev, seed=K + N)
     cases = [(K, N, M) for (K, N) in SHAPES for M in BATCHES]
-    xs = {c: torch.randn(c[2], c[0], device=dev, dtype=torch.bfloat16) for c in cases}
+    g = torch.Generator(device=dev).manual_seed(99)
+    xs = {c: torch.randn(rings[c[:2]].R, c[2], c[0], generator=g, device=dev, dtype=torch.bfloat16) for c in cases}
     outs = {c: torch.empty(rings[c[:2]].R, c[2], c[1], device=dev, dtype=torch.bfloat16) for c in cases}
+    wss = {c: torch.empty(lib.tb200_gemv_stream_workspace(c[2], c[0], rings[c[:2]].R), dtype=torch.uint8, device=dev) for c in cases}
 
-    def launch_case(c, pdl=True):
+    def launch_case(c):
+        """One decode pass of case c over its ring of layers: tb200_gemv_stream (activation quantiser launch + ONE
+        persistent GEMV launch for the whole ring)."""
+        ring = rings[c[:2]]
+        ops.gemv_stream(xs[c], ring.packed, ring.scale, ring.bias, 100.0, out=outs[c], workspace=wss[c])
+
+    def launch_chain(c):
+        """The same ring as a chain of per-layer calls (what a model's sequential layers do): tb200_gemv with
+        programmatic dependent launch up to 8 tokens, tb200_linear_forward above."""
         K, N, M = c
         ring = rings[(K, N)]
-        x, out = xs[c], outs[c]
         for r in range(ring.R):
-            if M <= 8:     # fused activation quantisation, programmatic dependent launch between layers
-                ops.gemv(x, ring.packed[r], ring.scale[r], ring.bias[r], 100.0, pdl=pdl, out=out[r])
-            else:          # tb200_linear_forward: quantise once + GEMV on int8 activations
-                ops.ternary_matmul(x, ring.packed[r], ring.scale[r], ring.bias[r], 100.0, out=out[r])
+            if M <= 8:
+                ops.gemv(xs[c][r], ring.packed[r], ring.scale[r], ring.bias[r], 100.0, pdl=True, out=outs[c][r])
+            else:
+                ops.ternary_matmul(xs[c][r], ring.packed[r], ring.scale[r], ring.bias[r], 100.0, out=outs[c][r])
 
     def launch_step():
         for c in cases:
@@ -234,10 +243,29 @@ def run_b200(args):
     step_bytes = sum(algorithmic_bytes(*c) * rings[c[:2]].R for c in cases)
     step_tokens = sum(c[2] * rings[c[:2]].R for c in cases)
 
-    # ---- capture one step as a CUDA graph (launch-bound otherwise: kernels are ~1-3 us) ----
+    def timed_graph(fn, stream, reps, warm=3):
+        fn()
+        stream.synchronize()
+        n0 = ops.launch_count()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=stream):
+            fn()
+        launches = ops.launch_count() - n0
+        for _ in range(warm):
+            gr.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        stream.synchronize()
+        e0.record(stream)
+        for _ in range(reps):
+            gr.replay()
+        e1.record(stream)
+        stream.synchronize()
+        return e0.elapsed_time(e1) * 1e-3 / reps, launches, gr
+
+    # ---- one step = all six cases, captured as one CUDA graph ----
     stream = torch.cuda.Stream(dev)
     with torch.cuda.stream(stream):
-        launch_step()                                    # warm: cudaFuncSetAttribute etc. outside capture
+        launch_step()
         stream.synchronize()
         n0 = ops.launch_count()
         graph = torch.cuda.CUDAGraph()
@@ -260,39 +288,32 @@ def run_b200(args):
         ms = ev0.elapsed_time(ev1)
     value = step_bytes * args.steps / (ms * 1e-3) / 1e9
 
-    # ---- per-case device numbers (each case alone, graph of its ring) ----
+    # ---- per-case device numbers: the streaming call, and the per-layer chain next to it ----
     per_case = []
     with torch.cuda.stream(stream):
         for c in cases:
             K, N, M = c
             R = rings[(K, N)].R
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g, stream=stream):
-                launch_case(c)
-            for _ in range(3):
-                g.replay()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            reps = 20
-            stream.synchronize()
-            e0.record(stream)
-            for _ in range(reps):
-                g.replay()
-            e1.record(stream)
-            stream.synchronize()
-            t = e0.elapsed_time(e1) * 1e-3 / (reps * R)          # seconds per layer
-            nl = 1 if M <= 8 else (1 + (M + 7) // 8 if M <= 16 else 2)
-            per_case.append({"K": K, "N": N, "M": M, "us_per_layer": t * 1e6, "launches_per_layer": nl,
-                             "gbs": algorithmic_bytes(K, N, M) / t / 1e9,
-                             "frac_hbm_measured": algorithmic_bytes(K, N, M) / t / 1e9 / pk["hbm_gbs"],
-                             "tokens_per_s": M / t})
-    dom = [p for p in per_case if p["N"] == 11008 and p["M"] == 1][0]
-    roofline = {"bound": "hbm", "kernel": "gemv_mma_kernel<bf16,bf16,NT=1,FUSED> on 4096x11008, M=1 (PDL chain of distinct layers)",
+            t_call, nl, _ = timed_graph(lambda: launch_case(c), stream, 20)
+            t_chain, nlc, _ = timed_graph(lambda: launch_chain(c), stream, 5)
+            t = t_call / R
+            b = algorithmic_bytes(K, N, M)
+            per_case.append({"K": K, "N": N, "M": M, "layers": R, "us_per_layer": t * 1e6, "us_per_call": t_call * 1e6,
+                             "launches_per_call": nl, "gbs": b / t / 1e9, "frac_hbm_measured": b / t / 1e9 / pk["hbm_gbs"],
+                             "tokens_per_s": M / t,
+                             "chain": {"us_per_layer": t_chain / R * 1e6, "launches_per_layer": nlc / R,
+                                       "gbs": b / (t_chain / R) / 1e9,
+                                       "api": "one call per layer (tb200_gemv + PDL up to 8 tokens, tb200_linear_forward above)"}})
+    dom = [p_ for p_ in per_case if p_["N"] == 11008 and p_["M"] == 1][0]
+    roofline = {"bound": "hbm",
+                "kernel": "gemv_stream_kernel<NG=1,BREG,TEAMS=2> (+ quant_image_kernel) on %d layers of 4096x11008, M=1" % dom["layers"],
                 "achieved": dom["gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": dom["gbs"] / pk["hbm_gbs"],
                 "peak_source": pk["source"], "frac_of_spec_8TBs": dom["gbs"] / 8000.0,
-                "algorithmic_bytes_per_launch": algorithmic_bytes(4096, 11008, 1),
-                "avg_launch_us": dom["us_per_layer"], "traffic": TRAFFIC_BYTES}
+                "algorithmic_bytes_per_launch": algorithmic_bytes(4096, 11008, 1) * dom["layers"],
+                "avg_launch_us": dom["us_per_call"], "traffic": TRAFFIC_BYTES,
+                "chain_of_single_layer_launches_gbs": dom["chain"]["gbs"]}
 
-    # ---- e2e: host buffers through the C ABI, one call per layer ----
+    # ---- e2e: host buffers through the C ABI ----
     e2e = run_e2e(args, lib, dev, rings, cases, step_bytes)
 
     # ---- tcgen05 prefill GEMM (configs[2]) ----
@@ -320,39 +341,41 @@ def run_b200(args):
     print(json.dumps(line))
 
 
-TRAFFIC_BYTES = 11408384    # dram__bytes_read+write per launch of the dominant kernel (profiles/r1_gemv_mma.summary.txt)
+RING_MIN = 64               # layers per ring (>= 2.2 x L2 in packed bytes for both shapes)
+TRAFFIC_BYTES = None        # dram__bytes_read+write per launch of the dominant kernel, filled from profiles/ (see below)
 
 
 def run_e2e(args, lib, dev, rings, cases, step_bytes):
+    """The sweep through the host-buffer C-ABI call: per case one tb200_gemv_stream_host (H2D of all activations of
+    the ring, quantiser + persistent GEMV, D2H of all outputs)."""
     import torch
     from ternary_vllm_b200 import _lib as L
     stream = torch.cuda.current_stream(dev)
-    hx = {c: torch.randn(c[2], c[0], dtype=torch.bfloat16).pin_memory() for c in cases}
-    hy = {c: torch.empty(c[2], c[1], dtype=torch.bfloat16).pin_memory() for c in cases}
-    dx = {c: torch.empty(c[2], c[0], dtype=torch.bfloat16, device=dev) for c in cases}
-    dy = {c: torch.empty(c[2], c[1], dtype=torch.bfloat16, device=dev) for c in cases}
-    ws = torch.empty(1 << 20, dtype=torch.uint8, device=dev)
-    h2d = sum(c[2] * c[0] * 2 * rings[c[:2]].R for c in cases)
-    d2h = sum(c[2] * c[1] * 2 * rings[c[:2]].R for c in cases)
+    R = {c: rings[c[:2]].R for c in cases}
+    hx = {c: torch.randn(R[c], c[2], c[0], dtype=torch.bfloat16).pin_memory() for c in cases}
+    hy = {c: torch.empty(R[c], c[2], c[1], dtype=torch.bfloat16).pin_memory() for c in cases}
+    dx = {c: torch.empty(R[c], c[2], c[0], dtype=torch.bfloat16, device=dev) for c in cases}
+    dy = {c: torch.empty(R[c], c[2], c[1], dtype=torch.bfloat16, device=dev) for c in cases}
+    ws = {c: torch.empty(lib.tb200_gemv_stream_workspace(c[2], c[0], R[c]), dtype=torch.uint8, device=dev) for c in cases}
+    h2d = sum(hx[c].numel() * 2 for c in cases)
+    d2h = sum(hy[c].numel() * 2 for c in cases)
 
     def step():
         s = stream.cuda_stream
         for c in cases:
             K, N, M = c
             ring = rings[(K, N)]
-            ld = ring.packed.stride(1)
-            for r in range(ring.R):
-                rc = lib.tb200_linear_forward_host(hx[c].data_ptr(), L.TB200_BF16, M, K, ring.packed[r].data_ptr(), ld, N,
-                                                   ring.scale[r].data_ptr(), ring.bias[r].data_ptr(), 100.0,
-                                                   hy[c].data_ptr(), L.TB200_BF16, dx[c].data_ptr(), dy[c].data_ptr(),
-                                                   ws.data_ptr(), s)
-                if rc:
-                    L.check(rc, "linear_forward_host")
+            rc = lib.tb200_gemv_stream_host(hx[c].data_ptr(), L.TB200_BF16, M, K, ring.packed.data_ptr(), ring.packed.stride(1),
+                                            ring.packed.stride(0), N, ring.scale.data_ptr(), ring.bias.data_ptr(), N, 100.0,
+                                            hy[c].data_ptr(), L.TB200_BF16, R[c], dx[c].data_ptr(), dy[c].data_ptr(),
+                                            ws[c].data_ptr(), s)
+            if rc:
+                L.check(rc, "gemv_stream_host")
         stream.synchronize()          # the caller reads hy after every step
 
     for _ in range(3):
         step()
-    steps = max(3, min(args.steps, 10))
+    steps = max(3, min(args.steps, 20))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -365,7 +388,8 @@ def run_e2e(args, lib, dev, rings, cases, step_bytes):
     ms = max(e0.elapsed_time(e1), wall * 1e3)
     return {"value": step_bytes * steps / (ms * 1e-3) / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d,
             "d2h_bytes_per_step": d2h, "steps": steps, "ms_per_step": ms / steps,
-            "api": "tb200_linear_forward_host (pinned host x -> device, kernel, device -> pinned host y), one call per layer"}
+            "api": "tb200_gemv_stream_host per sweep case (pinned host x -> device, quantiser + persistent GEMV over the "
+                   "ring, device -> pinned host y)"}
 
 
 VIT_SHAPES = [(1024, 3072), (1024, 1024), (1024, 4096), (4096, 1024)]     # configs[3]: ViT-L/14 QKV, proj, fc1, fc2; M = 32 x 257

@@ -187,6 +187,15 @@ int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t K, int64_t 
                       void* out, int out_dtype, int64_t ldo, int64_t stride_out,
                       int count, int32_t* acc_out, void* workspace, void* stream);
 
+/* tb200_gemv_stream with HOST activations x_host [count, M, K] and outputs out_host [count, M, N] (dense, pinned):
+ * one H2D copy, the two launches, one D2H copy, in order on `stream`.  dev_x / dev_out: device staging buffers of the
+ * same sizes.  The end-to-end form of a decode step over a list of layers (bench.py `e2e`). */
+int tb200_gemv_stream_host(const void* x_host, int x_dtype, int64_t M, int64_t K,
+                           const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                           const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                           void* out_host, int out_dtype, int count,
+                           void* dev_x, void* dev_out, void* workspace, void* stream);
+
 /* Prefill shape: tcgen05.mma kind::i8, TMEM accumulators.  Takes PRE-QUANTISED activations
  * from tb200_quant_act_i8(kperm=1): q_x int8 [M, ldq], s_x [M], sum_qx [M].
  * Requires ldq % 16 == 0, ld_packed % 16 == 0, 16-byte aligned base pointers. */

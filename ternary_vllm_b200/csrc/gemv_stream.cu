@@ -30,8 +30,8 @@ constexpr int SV_ROWS = 16;
 constexpr int SV_SEG = 128;
 constexpr int SV_TILE_BYTES = 16 * 1024;
 constexpr int SV_MMA_WARPS = 8;
-// warp roles for TEAMS teams of 8 MMA warps: [0, 8T) MMA | 8T tile producer | 8T+1 image producer | 8T+2.. aux
-constexpr int sv_threads(int teams, int aux) { return (8 * teams + 2 + aux) * 32; }
+// warp roles: [0, 8) MMA | 8 tile producer | 9 image producer | 10.. aux
+constexpr int sv_threads(int aux) { return (8 + 2 + aux) * 32; }
 constexpr int SV_MAX_STAGES = 12;
 constexpr int SV_MAX_SLOTS = 8;
 constexpr int SV_MAX_IMG = 2;
@@ -67,10 +67,11 @@ __device__ __forceinline__ int img_vec(int sg, int pp, int i, int n, int t, int 
 }
 
 // NG = groups of 8 tokens; BREG = the B fragments of the whole layer live in registers (NG == 1, K <= 4096)
-// TEAMS = 2: two teams of 8 MMA warps take alternate row blocks (4 warps per scheduler hide the LOP3 -> IMMA latency
-// that bounds the 8-warp version; used for NG == 1, where 96 registers per thread suffice)
+// TEAMS = 2 (NG == 1 only): two teams of 4 MMA warps take alternate row blocks, every warp owning TWO 128-byte K
+// segments: the per-row-block work of a warp (barriers, recombination, slot hand-off) is amortised over twice the MMAs
+// and only four K-partials per output meet in shared memory.
 template <int NG, bool BREG, int TEAMS, int AUX>
-__global__ void __launch_bounds__(sv_threads(TEAMS, AUX), 1)
+__global__ void __launch_bounds__(sv_threads(AUX), 1)
 gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams p) {
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
@@ -89,6 +90,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
     auto bar_sfull = [&](int q) { return sBar + 8u * (2 * SV_MAX_STAGES + 2 * SV_MAX_IMG + q); };
     auto bar_sempty = [&](int q) { return sBar + 8u * (2 * SV_MAX_STAGES + 2 * SV_MAX_IMG + SV_MAX_SLOTS + q); };
 
+    constexpr int WPT = SV_MMA_WARPS / TEAMS;              // MMA warps per tile (team size)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int G = gridDim.x, b = blockIdx.x;
     const int RB = p.row_blocks;
@@ -97,15 +99,15 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_w);
-        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), SV_MMA_WARPS); }
-        for (int i = 0; i < p.nimg; ++i) { mbar_init(bar_ifull(i), 1); mbar_init(bar_iempty(i), SV_MMA_WARPS * TEAMS); }
-        for (int q = 0; q < p.nslots; ++q) { mbar_init(bar_sfull(q), SV_MMA_WARPS); mbar_init(bar_sempty(q), 1); }
+        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), WPT); }
+        for (int i = 0; i < p.nimg; ++i) { mbar_init(bar_ifull(i), 1); mbar_init(bar_iempty(i), SV_MMA_WARPS); }
+        for (int q = 0; q < p.nslots; ++q) { mbar_init(bar_sfull(q), WPT); mbar_init(bar_sempty(q), 1); }
         mbar_fence_init();
     }
     __syncthreads();
     asm volatile("griddepcontrol.launch_dependents;");
 
-    constexpr int SV_WARP_TILES = 8 * TEAMS, SV_WARP_IMAGE = 8 * TEAMS + 1, SV_WARP_AUX0 = 8 * TEAMS + 2;
+    constexpr int SV_WARP_TILES = 8, SV_WARP_IMAGE = 9, SV_WARP_AUX0 = 10;
     if (warp == SV_WARP_TILES) {
         // ===================== weight tiles: independent of any previous kernel =====================
         if (lane == 0) {
@@ -113,7 +115,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
             for (int u = b; u < total; u += G) {
                 const int l = u / RB, rb = u - l * RB;
                 for (int ks = 0; ks < p.nks; ++ks) {
-                    mbar_wait(bar_empty(s), ph ^ 1u);
+                    mbar_wait_relaxed(bar_empty(s), ph ^ 1u);
                     mbar_arrive_expect_tx(bar_full(s), SV_TILE_BYTES);
                     if (p.one_box) {
                         tma_load_4d(sRing + s * SV_TILE_BYTES, &map_w, bar_full(s), 0, rb * SV_ROWS, ks * 8, l);
@@ -138,7 +140,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 cur = l;
                 const int ib = j % p.nimg;
                 const uint32_t par = (uint32_t)(j / p.nimg) & 1u;
-                mbar_wait(bar_iempty(ib), par ^ 1u);
+                mbar_wait_relaxed(bar_iempty(ib), par ^ 1u);
                 mbar_arrive_expect_tx(bar_ifull(ib), p.img_bytes);
                 const uint8_t* src = p.blob + (int64_t)l * p.blob_stride;
                 const uint32_t dst = smem_u32(img0) + ib * img_pitch;
@@ -150,10 +152,11 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 ++j;
             }
         }
-    } else if (warp < SV_MMA_WARPS * TEAMS) {
+    } else if (warp < SV_MMA_WARPS) {
         // ===================== dot products =====================
         const int g = lane >> 2, t = lane & 3;
-        const int team = warp >> 3, wseg = warp & 7;       // K segment of this warp
+        const int team = warp / WPT, wq = warp % WPT;       // TEAMS == 2: segments 2*wq, 2*wq+1
+        const int wseg = TEAMS == 1 ? warp : 2 * wq;        // (first) K segment of this warp
         const uint32_t sSeg = wseg * (SV_ROWS * SV_SEG) + g * SV_SEG;
         const uint32_t phys0 = ((2 * t) ^ g) << 4, phys1 = ((2 * t + 1) ^ g) << 4;
         const int nks = p.nks, stages = p.stages, nslots = p.nslots, nimg = p.nimg, Mg = p.Mg;
@@ -192,7 +195,9 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
         int sq = 0; uint32_t spar = 0;                   // partial-sum slot ring
         // one half (pp) of a tile: 8 (BREG / NG == 1) or 8 * NG MMAs
         auto half = [&](const uint4& lo, const uint4& hi, int pp, int ksl) {
-            if (p.dbg & 1) { acc[0][0][0] += (int)(lo.x ^ hi.y); return; }
+#ifdef TB200_STREAM_NOMMA
+            acc[0][0][0] += (int)(lo.x ^ hi.y); return;
+#endif
             if (BREG) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -306,10 +311,32 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 step(nlo, nhi, wlo, whi);
             }
         } else {
-            // Two teams: every team walks the whole row-block list (layer changes, ring and slot positions) but computes
-            // only its own row blocks (gi & 1 == team); no cross-tile register prefetch, the other team's warps cover
-            // the latencies.
+            // Two teams of four warps: every team walks the whole row-block list (layer changes, ring and slot positions)
+            // but computes only its own row blocks (gi & 1 == team).
             (void)step;
+            uint32_t ready = 0;                          // early test of the stage of this team's next tile
+            uint4 b2[2][2][4];                           // BREG: B fragments of both segments
+            auto seg_half = [&](const uint4& lo, const uint4& hi, int j, int pp, int ksl) {
+#ifdef TB200_STREAM_NOMMA
+                acc[0][0][0] += (int)(lo.x ^ hi.y); return;
+#endif
+                uint4 bv[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (BREG) bv[i] = b2[j][pp][i];
+                    else bv[i] = g < ntok[0] ? img[img_vec(ksl * 8 + wseg + j, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t mk = 0x03030303u << (2 * i);
+                    imma_s(acc[0][i], lo.x & mk, hi.x & mk, lo.y & mk, hi.y & mk, bv[i].x, bv[i].y);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t mk = 0x03030303u << (2 * i);
+                    imma_s(acc[0][i], lo.z & mk, hi.z & mk, lo.w & mk, hi.w & mk, bv[i].z, bv[i].w);
+                }
+            };
 #pragma unroll 1
             for (int gi = 0; gi < my_groups; ++gi) {
                 if (l != cur) {
@@ -319,29 +346,53 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                     img = reinterpret_cast<const uint4*>(img0 + ib * img_pitch);
                     if (BREG) {
 #pragma unroll
-                        for (int pp = 0; pp < 2; ++pp)
+                        for (int j = 0; j < 2; ++j)
 #pragma unroll
-                            for (int i = 0; i < 4; ++i)
-                                bq[pp][i] = g < ntok[0] ? img[img_vec(wseg, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
+                            for (int pp = 0; pp < 2; ++pp)
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+                                    b2[j][pp][i] = g < ntok[0] ? img[img_vec(wseg + j, pp, i, g, t, Mg)] : make_uint4(0u, 0u, 0u, 0u);
                         __syncwarp();
                         if (lane == 0) mbar_arrive(bar_iempty(ib));
                     }
                     if (++ib == nimg) { ib = 0; ipar ^= 1u; }
                 }
                 if ((gi & 1) == team) {
+                    const uint32_t sready = mbar_test(bar_sempty(sq), spar ^ 1u);     // consumed after the MMAs
 #pragma unroll 1
                     for (int k2 = 0; k2 < nks; ++k2) {
-                        fetch(wlo, whi, 0u);
-                        half(wlo[0], whi[0], 0, k2);
-                        half(wlo[1], whi[1], 1, k2);
+                        if (!ready) mbar_wait(bar_full(s), ph);
+                        const uint8_t* seg = gbase + s * SV_TILE_BYTES + sSeg;
+                        uint4 alo[2][2], ahi[2][2];
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) {
+                            const uint8_t* sj = seg + j * (SV_ROWS * SV_SEG);
+                            alo[j][0] = *reinterpret_cast<const uint4*>(sj + phys0);
+                            ahi[j][0] = *reinterpret_cast<const uint4*>(sj + 8 * SV_SEG + phys0);
+                            alo[j][1] = *reinterpret_cast<const uint4*>(sj + phys1);
+                            ahi[j][1] = *reinterpret_cast<const uint4*>(sj + 8 * SV_SEG + phys1);
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_empty(s));
+                        if (++s == stages) { s = 0; ph ^= 1u; }
+                        {   // test the stage of this team's NEXT tile now, use the answer after the MMAs
+                            int s2 = s; uint32_t ph2 = ph;
+                            if (k2 + 1 == nks) { s2 += nks; while (s2 >= stages) { s2 -= stages; ph2 ^= 1u; } }
+                            ready = mbar_test(bar_full(s2), ph2);
+                        }
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) {
+                            seg_half(alo[j][0], ahi[j][0], j, 0, k2);
+                            seg_half(alo[j][1], ahi[j][1], j, 1, k2);
+                        }
                     }
-                    mbar_wait(bar_sempty(sq), spar ^ 1u);
+                    if (!sready) mbar_wait(bar_sempty(sq), spar ^ 1u);
                     uint4 v;
                     v.x = (uint32_t)(acc[0][0][0] + (acc[0][1][0] >> 2) + (acc[0][2][0] >> 4) + (acc[0][3][0] >> 6));
                     v.y = (uint32_t)(acc[0][0][1] + (acc[0][1][1] >> 2) + (acc[0][2][1] >> 4) + (acc[0][3][1] >> 6));
                     v.z = (uint32_t)(acc[0][0][2] + (acc[0][1][2] >> 2) + (acc[0][2][2] >> 4) + (acc[0][3][2] >> 6));
                     v.w = (uint32_t)(acc[0][0][3] + (acc[0][1][3] >> 2) + (acc[0][2][3] >> 4) + (acc[0][3][3] >> 6));
-                    slots[(size_t)(sq * NG) * 256 + wseg * 32 + lane] = v;
+                    slots[(size_t)(sq * NG) * 256 + wq * 32 + lane] = v;
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -398,17 +449,28 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
         float sxv[NG][2]; int sumq[NG][2];
 #pragma unroll
         for (int q = 0; q < NG; ++q) { sxv[q][0] = sxv[q][1] = 0.0f; sumq[q][0] = sumq[q][1] = 0; }
-        float sbn[4];
-        load_sb(np, a < my_groups, sbn);
+        // Under a saturated read stream every load waits behind ~20 MB of queued tile traffic (microseconds), so the
+        // scale/bias values are requested SV_FIFO row blocks of this warp ahead and kept in a register FIFO.
+        constexpr int SV_FIFO = 4;
+        float sbf[SV_FIFO][4];
+#pragma unroll
+        for (int d = 0; d < SV_FIFO; ++d) {
+            load_sb(np, a + d * AUX < my_groups, sbf[d]);
+            advance(np);
+        }
         int sq_i = a % p.nslots; uint32_t spar = (uint32_t)(a / p.nslots) & 1u;     // AUX <= nslots: a / nslots == 0
         const bool store_acc = p.acc_out != nullptr;
 #pragma unroll 1
-        for (int sn = a; sn < my_groups; sn += AUX) {
+        for (int sn0 = a; sn0 < my_groups; sn0 += SV_FIFO * AUX) {
+#pragma unroll
+          for (int d = 0; d < SV_FIFO; ++d) {
+            const int sn = sn0 + d * AUX;
+            if (sn >= my_groups) break;
             const int l = cp.l;
             const int64_t row0 = (int64_t)cp.rb * SV_ROWS + g, row1 = row0 + 8;
-            const float sc0 = sbn[0], sc1 = sbn[1], bi0 = sbn[2], bi1 = sbn[3];
+            const float sc0 = sbf[d][0], sc1 = sbf[d][1], bi0 = sbf[d][2], bi1 = sbf[d][3];
+            load_sb(np, sn + SV_FIFO * AUX < my_groups, sbf[d]);
             advance(np);
-            load_sb(np, sn + AUX < my_groups, sbn);
             if (l != cur) {
                 cur = l;
                 const uint8_t* tail = p.blob + (int64_t)l * p.blob_stride + p.img_bytes;
@@ -423,14 +485,14 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                         sumq[q][e] = tok < p.M ? sq[tok] : 0;
                     }
             }
-            mbar_wait(bar_sfull(sq_i), spar);
+            mbar_wait_relaxed(bar_sfull(sq_i), spar);
             int vv[NG][4];
 #pragma unroll
             for (int q = 0; q < NG; ++q) {
                 const uint4* sl = slots + (size_t)(sq_i * NG + q) * 256 + lane;
                 vv[q][0] = vv[q][1] = vv[q][2] = vv[q][3] = 0;
 #pragma unroll
-                for (int w = 0; w < SV_MMA_WARPS; ++w) {
+                for (int w = 0; w < WPT; ++w) {
                     const uint4 v = sl[w * 32];
                     vv[q][0] += (int)v.x; vv[q][1] += (int)v.y; vv[q][2] += (int)v.z; vv[q][3] += (int)v.w;
                 }
@@ -461,6 +523,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                 }
             }
             advance(cp);
+          }
         }
     }
 }
@@ -617,7 +680,7 @@ static int launch_stream(const CUtensorMap& map, const StreamParams& p, size_t s
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas, 1, 1);
-    cfg.blockDim = dim3(sv_threads(TEAMS, AUX), 1, 1);
+    cfg.blockDim = dim3(sv_threads(AUX), 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
@@ -685,7 +748,7 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
         case 1: {
             static const int teams = getenv("TB200_STREAM_TEAMS") ? atoi(getenv("TB200_STREAM_TEAMS")) : 2;
             if (teams == 2)
-                return breg ? launch_stream<1, true, 2, 4>(map, p, smem, ctas, true, s) : launch_stream<1, false, 2, 4>(map, p, smem, ctas, true, s);
+                return breg ? launch_stream<1, true, 2, 2>(map, p, smem, ctas, true, s) : launch_stream<1, false, 2, 2>(map, p, smem, ctas, true, s);
             return breg ? launch_stream<1, true, 1, 4>(map, p, smem, ctas, true, s) : launch_stream<1, false, 1, 4>(map, p, smem, ctas, true, s);
         }
         case 2: return launch_stream<2, false, 1, 2>(map, p, smem, ctas, true, s);
@@ -723,4 +786,25 @@ extern "C" int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t 
     TB_REQUIRE(count >= 1 && count <= 65535, "gemv_stream: bad layer count %d", count);
     return gemv_stream_impl(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N, scale, bias, stride_sb,
                             clip_val, out, out_dtype, ldo, stride_out, acc_out, count, workspace, (cudaStream_t)stream);
+}
+
+// End-to-end with HOST activations / outputs for a list of layers (weights resident on the device): one H2D copy of
+// all activations, the streaming GEMV, one D2H copy of all outputs, in order on `stream`.  x_host [count, M, K] and
+// out_host [count, M, N] are dense and should be pinned; dev_x / dev_out are device staging buffers of the same sizes.
+extern "C" int tb200_gemv_stream_host(const void* x_host, int x_dtype, int64_t M, int64_t K,
+                                      const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                                      const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                                      void* out_host, int out_dtype, int count,
+                                      void* dev_x, void* dev_out, void* workspace, void* stream) {
+    TB_DEVICE_OR_RETURN();
+    if (M == 0 || N == 0 || count == 0) return TB200_OK;
+    TB_REQUIRE(x_host && out_host && dev_x && dev_out, "gemv_stream_host: null pointer");
+    TB_REQUIRE(dtype_ok(x_dtype) && dtype_ok(out_dtype), "gemv_stream_host: bad dtype");
+    cudaStream_t s = (cudaStream_t)stream;
+    TB_CUDA(cudaMemcpyAsync(dev_x, x_host, (size_t)count * M * K * dtype_size(x_dtype), cudaMemcpyHostToDevice, s));
+    int rc = tb200_gemv_stream(dev_x, x_dtype, M, K, K, M * K, packed, ld_packed, stride_packed, N, scale, bias, stride_sb,
+                               clip_val, dev_out, out_dtype, N, M * N, count, nullptr, workspace, stream);
+    if (rc) return rc;
+    TB_CUDA(cudaMemcpyAsync(out_host, dev_out, (size_t)count * M * N * dtype_size(out_dtype), cudaMemcpyDeviceToHost, s));
+    return TB200_OK;
 }

@@ -31,6 +31,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         if (++spins > 20000000u) __trap();
     }
 }
+// wait of a warp that is off the critical path (producers, epilogue warps): back off between polls so that the
+// spin does not take issue slots from the warps doing the dot products on the same scheduler
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0, spins = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (done) break;
+        __nanosleep(64);
+        if (++spins > 20000000u) __trap();
+    }
+}
 // one non-blocking test: issue early, consume the result later (hides the ~70-clock PHASECHK + branch latency)
 __device__ __forceinline__ uint32_t mbar_test(uint32_t bar, uint32_t parity) {
     uint32_t done;

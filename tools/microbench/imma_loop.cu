@@ -43,6 +43,44 @@ __global__ void __launch_bounds__(512) k(int* out, long long* cyc, uint32_t seed
             wlo[pp] = *reinterpret_cast<const uint4*>(seg + phys);
             whi[pp] = *reinterpret_cast<const uint4*>(seg + 1024 + phys);
         }
+        if (V == 5 || V == 6) {
+            // pinned schedule: all masks of a batch first (distinct registers), then the batch's IMMAs back to back
+            auto vand = [](uint32_t a, uint32_t m) { uint32_t r; asm volatile("and.b32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(m)); return r; };
+#pragma unroll
+            for (int pp = 0; pp < 2; ++pp) {
+                if (V == 5) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t m[4][4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const uint32_t mk = 0x03030303u << (2 * i);
+                            m[i][0] = vand(h ? wlo[pp].z : wlo[pp].x, mk); m[i][1] = vand(h ? whi[pp].z : whi[pp].x, mk);
+                            m[i][2] = vand(h ? wlo[pp].w : wlo[pp].y, mk); m[i][3] = vand(h ? whi[pp].w : whi[pp].y, mk);
+                        }
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            imma(acc[i], m[i][0], m[i][1], m[i][2], m[i][3], h ? bq[pp][i].z : bq[pp][i].x, h ? bq[pp][i].w : bq[pp][i].y);
+                    }
+                } else {
+                    uint32_t m[2][4][4];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const uint32_t mk = 0x03030303u << (2 * i);
+                            m[h][i][0] = vand(h ? wlo[pp].z : wlo[pp].x, mk); m[h][i][1] = vand(h ? whi[pp].z : whi[pp].x, mk);
+                            m[h][i][2] = vand(h ? wlo[pp].w : wlo[pp].y, mk); m[h][i][3] = vand(h ? whi[pp].w : whi[pp].y, mk);
+                        }
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            imma(acc[i + 4 * h], m[h][i][0], m[h][i][1], m[h][i][2], m[h][i][3], h ? bq[pp][i].z : bq[pp][i].x, h ? bq[pp][i].w : bq[pp][i].y);
+                }
+            }
+            continue;
+        }
 #pragma unroll
         for (int pp = 0; pp < 2; ++pp) {
 #pragma unroll
@@ -82,12 +120,14 @@ template <int V> void run(const char* name, int threads) {
     cudaFree(out); cudaFree(cyc);
 }
 int main() {
-    for (int th : {128, 256, 512}) {
+    for (int th : {256, 384, 512}) {
         run<0>("full (LDS+LOP+IMMA)", th);
         run<1>("no LOP3", th);
         run<2>("no IMMA (LOP+XOR)", th);
         run<3>("full + try_wait", th);
         run<4>("full, 8 acc sets", th);
+        run<5>("pinned batches of 4", th);
+        run<6>("pinned batches of 8, 8 acc", th);
     }
     printf("status: %s\n", cudaGetErrorString(cudaGetLastError()));
     return 0;
