@@ -285,6 +285,7 @@ extern "C" int tb200_gemm_i8(const int8_t* q_x, int64_t ldq, const float* s_x, c
     p.out = out; p.ldo = ldo; p.acc_out = acc_out;
     p.M = M; p.N = N; p.K = K; p.clip_val = fabsf(clip_val);
     p.m_tiles = p.n_tiles = p.k_blocks = 0;
+    p.layers = 1; p.stride_act_rows = 0; p.stride_sb = 0; p.stride_out = 0;
     { const char* e = getenv("TB200_GEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
     cudaStream_t s = (cudaStream_t)stream;
     static int use_ts = -1;

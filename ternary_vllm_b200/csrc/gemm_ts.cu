@@ -17,7 +17,7 @@
 //   * accumulators are double-buffered in TMEM (2 x BT columns); the epilogue warps read them with
 //     tcgen05.ld, apply -sum_qx, s_x*scale, bias, clip, and hand 32-token x 128-channel chunks to TMA
 //     stores through a double-buffered shared-memory staging tile (2-byte scattered stores cost 60 us).
-// TMEM budget at BT=192: 2*192 (D) + 2*64 (A) = 512 columns.
+// TMEM budget at BT=192: 2*192 (D) + 2*64 (A) = 512 columns; at BT<=64: 2*BT (D) + 6*64 (A).
 #include <stdlib.h>
 #include <type_traits>
 #include "umma.cuh"
@@ -30,15 +30,17 @@ constexpr int TS_KS = TS_BK / 128;   // activation sub-tiles per stage
 constexpr int TS_EXP_SETS = 2;       // expander warp sets (4 warps each) taking k-blocks round-robin
 constexpr int TS_THREADS = 256 + 128 * TS_EXP_SETS;   // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8.. expanders
 constexpr int TS_P_BYTES = TS_ROWS * (TS_BK / 4);   // 8 KB packed weights per stage (64 bytes per row)
-constexpr int TS_NSA = 2;            // A tiles in TMEM
 constexpr int TS_A_COLS = TS_BK / 4; // 64 columns per A tile
 
 template <int BT, int OSZ = 4> struct TsCfg {
     static constexpr int B_BYTES = BT * TS_BK;
     static constexpr int STAGE_BYTES = B_BYTES + TS_P_BYTES;
-    static constexpr int STAGES = BT >= 192 ? 3 : BT >= 128 ? 4 : BT >= 64 ? 6 : 8;   // 160 -> 4 stages of 48 KB
+    static constexpr int STAGES = BT >= 192 ? 3 : BT >= 128 ? 4 : BT >= 64 ? 6 : BT >= 32 ? 12 : 8;   // 160 -> 4 stages of 48 KB
     static constexpr int D_COLS = 2 * BT;
-    static constexpr int NEED = D_COLS + TS_NSA * TS_A_COLS;
+    // A tiles in TMEM: the expand -> MMA -> retire -> reuse loop of a slot is ~2000 clocks long, so skinny token tiles
+    // (which finish a k-block's MMAs quickly and have TMEM columns to spare) keep six of them in flight
+    static constexpr int NSA = BT <= 32 ? 6 : BT <= 64 ? 4 : 2;
+    static constexpr int NEED = D_COLS + NSA * TS_A_COLS;
     static constexpr int TMEM_COLS = NEED <= 32 ? 32 : NEED <= 64 ? 64 : NEED <= 128 ? 128 : NEED <= 256 ? 256 : 512;
     static_assert(NEED <= 512, "TMEM budget");
     static constexpr int SX_BYTES = 2 * BT * 8;
@@ -56,6 +58,8 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                const __grid_constant__ CUtensorMap map_out, const UmmaParams p) {
     using Cfg = TsCfg<BT, (int)sizeof(OT)>;
     constexpr int NS = Cfg::STAGES;
+    constexpr int TS_NSA = Cfg::NSA;
+    static_assert(NS > TS_NSA, "a stage's done barrier must not wrap before its A slot is reused");
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
     uint8_t* gbase = smem_dyn + (base - smem_u32(smem_dyn));
@@ -83,7 +87,8 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
     if (CL > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
     const int cluster_id = blockIdx.x / CL, num_clusters = gridDim.x / CL;
     const int n_groups = (p.n_tiles + CL - 1) / CL;
-    const int total_tiles = p.m_tiles * n_groups;           // super-tiles: CL weight tiles x one token tile
+    const int tiles_per_layer = p.m_tiles * n_groups;       // super-tiles: CL weight tiles x one token tile
+    const int total_tiles = tiles_per_layer * p.layers;
     constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1u);
 
     if (warp == 0 && lane == 0) {
@@ -119,22 +124,23 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;
             for (int t = cluster_id; t < total_tiles; t += num_clusters) {
-                const int n_group = t / p.m_tiles, m_tile = t - n_group * p.m_tiles;
+                const int layer = t / tiles_per_layer, tl = t - layer * tiles_per_layer;
+                const int n_group = tl / p.m_tiles, m_tile = tl - n_group * p.m_tiles;
                 const int n_tile = n_group * CL + (int)cta_rank;
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
                     mbar_wait(bar_done(s), ph ^ 1u);
                     mbar_arrive_expect_tx(bar_pfull(s), TS_P_BYTES);
-                    tma_load_2d(sP + s * TS_P_BYTES, &map_pw, bar_pfull(s), kb * (TS_BK / 4), n_tile * TS_ROWS);
+                    tma_load_3d(sP + s * TS_P_BYTES, &map_pw, bar_pfull(s), kb * (TS_BK / 4), n_tile * TS_ROWS, layer);
                     mbar_arrive_expect_tx(bar_ready(s), Cfg::B_BYTES);
 #pragma unroll
                     for (int j = 0; j < TS_KS; ++j) {
                         const uint32_t dst = sB + s * Cfg::B_BYTES + j * (BT * 128);
                         if (CL == 1) {
-                            tma_load_2d(dst, &map_act, bar_ready(s), kb * TS_BK + j * 128, m_tile * BT);
+                            tma_load_3d(dst, &map_act, bar_ready(s), kb * TS_BK + j * 128, m_tile * BT, layer);
                         } else {   // my 1/CL slice of the token tile, delivered to every CTA of the cluster
                             constexpr int SL = BT / CL;
-                            tma_load_2d_mc(dst + cta_rank * (SL * 128), &map_act, bar_ready(s),
-                                           kb * TS_BK + j * 128, m_tile * BT + (int)cta_rank * SL, kMask);
+                            tma_load_3d_mc(dst + cta_rank * (SL * 128), &map_act, bar_ready(s),
+                                           kb * TS_BK + j * 128, m_tile * BT + (int)cta_rank * SL, layer, kMask);
                         }
                     }
                     if (++s == NS) { s = 0; ph ^= 1u; }
@@ -143,7 +149,36 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // CL == 1: the whole warp runs the loop (uniform code, see umma_i8_ts_warp); clusters keep the single-thread form
+        if (CL == 1) {
+            constexpr uint32_t idesc = umma_idesc_i8(TS_ROWS, BT);
+            int s = 0; uint32_t ph = 0; int a = 0; int it = 0;
+            for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
+                const int buf = it & 1;
+                mbar_wait(bar_tempty(buf), (((uint32_t)it >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BT);
+                for (int kb = 0; kb < p.k_blocks; ++kb) {
+                    mbar_wait(bar_ready(s), ph);
+                    tc_fence_after();
+                    const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
+                    if (!(p.dbg & 4)) {
+#pragma unroll
+                        for (int j = 0; j < TS_KS; ++j) {
+                            const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                umma_i8_ts_warp(d_tmem, a_tmem + (uint32_t)(j * 32 + k * 8), bdesc + 2u * k, idesc,
+                                                (kb | j | k) ? 1u : 0u);
+                        }
+                    }
+                    umma_commit_warp(bar_done(s));
+                    if (kb == p.k_blocks - 1) umma_commit_warp(bar_tfull(buf));
+                    if (++s == NS) { s = 0; ph ^= 1u; }
+                    if (++a == TS_NSA) a = 0;
+                }
+            }
+        } else if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_i8(TS_ROWS, BT);
             int s = 0; uint32_t ph = 0; int a = 0; int it = 0;
             for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
@@ -165,11 +200,10 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                                            (kb | j | k) ? 1u : 0u);
                         }
                     }
-                    if (CL == 1) umma_commit(bar_done(s));
-                    else         umma_commit_mc(bar_done(s), kMask);   // frees the stage in every CTA of the cluster
+                    umma_commit_mc(bar_done(s), kMask);   // frees the stage in every CTA of the cluster
                     if (kb == p.k_blocks - 1) umma_commit(bar_tfull(buf));
                     if (++s == NS) { s = 0; ph ^= 1u; }
-                    a ^= 1;
+                    if (++a == TS_NSA) a = 0;
                 }
             }
         }
@@ -177,23 +211,28 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         // ===================== epilogue =====================
         const int q = warp & 3;
         const int et = threadIdx.x - 128;
-        OT* out = reinterpret_cast<OT*>(p.out);
+        OT* out_base = reinterpret_cast<OT*>(p.out);
         int it = 0, chunk_no = 0;
         if (et == 0 && p.tma_out) tma_prefetch_desc(&map_out);
         for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
             const int buf = it & 1;
-            const int n_group = t / p.m_tiles, m_tile = t - n_group * p.m_tiles;
+            const int layer = t / tiles_per_layer, tl = t - layer * tiles_per_layer;
+            const int n_group = tl / p.m_tiles, m_tile = tl - n_group * p.m_tiles;
             const int n_tile = n_group * CL + (int)cta_rank;
             const int64_t m0 = (int64_t)m_tile * BT;
             const int64_t n = (int64_t)n_tile * TS_ROWS + q * 32 + lane;
+            const float* s_x_l = p.s_x + layer * p.stride_act_rows;
+            const int32_t* sum_qx_l = p.sum_qx + layer * p.stride_act_rows;
+            OT* out = out_base + layer * p.stride_out;
+            const bool acc_on = p.acc_out != nullptr && layer == 0;
             for (int j = et; j < BT; j += 128) {
                 const int64_t m = m0 + j;
-                sx_sm[buf * BT + j] = m < p.M ? p.s_x[m] : 0.0f;
-                sq_sm[buf * BT + j] = m < p.M ? p.sum_qx[m] : 0;
+                sx_sm[buf * BT + j] = m < p.M ? s_x_l[m] : 0.0f;
+                sq_sm[buf * BT + j] = m < p.M ? sum_qx_l[m] : 0;
             }
             asm volatile("bar.sync 1, 128;" ::: "memory");
-            const float sc = (n < p.N && p.scale) ? p.scale[n] : 1.0f;
-            const float bi = (n < p.N && p.bias) ? p.bias[n] : 0.0f;
+            const float sc = (n < p.N && p.scale) ? p.scale[layer * p.stride_sb + n] : 1.0f;
+            const float bi = (n < p.N && p.bias) ? p.bias[layer * p.stride_sb + n] : 0.0f;
             mbar_wait(bar_tfull(buf), ((uint32_t)it >> 1) & 1u);
             tc_fence_after();
             constexpr int CH = BT >= 32 ? 32 : 16;
@@ -228,13 +267,13 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         const uint32_t addr = stg + (uint32_t)((j * TS_ROWS + q * 32 + lane) * sizeof(OT));
                         if (sizeof(OT) == 4) asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(to_f32(yv)) : "memory");
                         else asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(*reinterpret_cast<const unsigned short*>(&yv)) : "memory");
-                        if (p.acc_out && n < p.N && m0 + c0 + j < p.M) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
+                        if (acc_on && n < p.N && m0 + c0 + j < p.M) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
                     }
                     fence_proxy_async();
                     asm volatile("bar.sync 1, 128;" ::: "memory");
                     if (et == 0) {
-                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                                     ::"l"(&map_out), "r"(stg), "r"(n_tile * TS_ROWS), "r"((int)(m0 + c0)) : "memory");
+                        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                                     ::"l"(&map_out), "r"(stg), "r"(n_tile * TS_ROWS), "r"((int)(m0 + c0)), "r"(layer) : "memory");
                         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     }
                     ++chunk_no;
@@ -248,7 +287,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         const float tv = __fmul_rn((float)a, sxv[j]);
                         const OT yv = from_f32<OT>(epilogue(tv, sc, bi, p.clip_val));
                         if (j < valid) {
-                            if (p.acc_out) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
+                            if (acc_on) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
                             orow[(int64_t)j * p.ldo] = yv;
                         }
                     }
@@ -265,7 +304,6 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         const int q = warp & 3;                       // TMEM lane quarter; thread = weight row q*32 + lane
         const int row = q * 32 + lane;
         const int set = (warp - 8) >> 2;              // this warp set expands k-blocks set, set+SETS, ...
-        static_assert(TS_NSA == 2, "slot bookkeeping below assumes two A slots");
         int s = 0; uint32_t ph = 0;                   // ring position of the current k-block
         int s2 = 0; uint32_t ph2 = 0;                 // ring position of the k-block TS_NSA earlier (A-slot reuse)
         int a = 0, turn = 0; long long kbc = 0;
@@ -312,7 +350,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                 }
                 if (++s == NS) { s = 0; ph ^= 1u; }
                 if (kbc >= TS_NSA) { if (++s2 == NS) { s2 = 0; ph2 ^= 1u; } }
-                a ^= 1;
+                if (++a == TS_NSA) a = 0;
             }
         }
     }
@@ -330,26 +368,32 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
 }
 
 template <typename OT, int BT, int CL>
-static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed, UmmaParams p, cudaStream_t s) {
+static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed, UmmaParams p, cudaStream_t s,
+                     int64_t stride_q_rows, int64_t stride_packed) {
     using Cfg = TsCfg<BT, (int)sizeof(OT)>;
     static_assert(BT % (8 * CL) == 0, "token-tile slices must be whole 8-row swizzle atoms");
     CUtensorMap map_act, map_pw;
-    uint64_t dims_a[2] = {(uint64_t)ldq, (uint64_t)p.M}, str_a[1] = {(uint64_t)ldq};
-    uint32_t box_a[2] = {128, BT / CL};
-    int rc = make_tensor_map(&map_act, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, q_x, dims_a, str_a, box_a, CU_TENSOR_MAP_SWIZZLE_128B);
+    const uint64_t L = (uint64_t)p.layers;
+    uint64_t dims_a[3] = {(uint64_t)ldq, (uint64_t)p.M, L};
+    uint64_t str_a[2] = {(uint64_t)ldq, (uint64_t)(L > 1 ? stride_q_rows * ldq : p.M * ldq)};
+    uint32_t box_a[3] = {128, BT / CL, 1};
+    int rc = make_tensor_map(&map_act, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, q_x, dims_a, str_a, box_a, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
-    uint64_t dims_p[2] = {(uint64_t)((p.K + 3) / 4), (uint64_t)p.N}, str_p[1] = {(uint64_t)ld_packed};
-    uint32_t box_p[2] = {TS_BK / 4, TS_ROWS};
-    rc = make_tensor_map(&map_pw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, packed, dims_p, str_p, box_p, CU_TENSOR_MAP_SWIZZLE_64B);
+    uint64_t dims_p[3] = {(uint64_t)((p.K + 3) / 4), (uint64_t)p.N, L};
+    uint64_t str_p[2] = {(uint64_t)ld_packed, (uint64_t)(L > 1 ? stride_packed : ld_packed * p.N)};
+    uint32_t box_p[3] = {TS_BK / 4, TS_ROWS, 1};
+    rc = make_tensor_map(&map_pw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, packed, dims_p, str_p, box_p, CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
     // output tile stores through TMA need a 16-byte aligned base and row pitch
     CUtensorMap map_out = map_pw;
-    p.tma_out = (BT >= 32) && ((uintptr_t)p.out % 16 == 0) && ((p.ldo * sizeof(OT)) % 16 == 0) && !(p.dbg & 512);
+    p.tma_out = (BT >= 32) && ((uintptr_t)p.out % 16 == 0) && ((p.ldo * sizeof(OT)) % 16 == 0) &&
+                ((p.stride_out * sizeof(OT)) % 16 == 0) && !(p.dbg & 512);
     if (p.tma_out) {
-        uint64_t dims_o[2] = {(uint64_t)p.N, (uint64_t)p.M}, str_o[1] = {(uint64_t)(p.ldo * sizeof(OT))};
-        uint32_t box_o[2] = {TS_ROWS, 32};
+        uint64_t dims_o[3] = {(uint64_t)p.N, (uint64_t)p.M, L};
+        uint64_t str_o[2] = {(uint64_t)(p.ldo * sizeof(OT)), (uint64_t)((L > 1 ? p.stride_out : p.ldo * p.M) * sizeof(OT))};
+        uint32_t box_o[3] = {TS_ROWS, 32, 1};
         rc = make_tensor_map(&map_out, sizeof(OT) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (std::is_same<OT, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16),
-                             2, p.out, dims_o, str_o, box_o, CU_TENSOR_MAP_SWIZZLE_NONE);
+                             3, p.out, dims_o, str_o, box_o, CU_TENSOR_MAP_SWIZZLE_NONE);
         if (rc) return rc;
     }
     auto kern = umma_ts_kernel<OT, BT, CL>;
@@ -361,7 +405,7 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
     p.m_tiles = (int)((p.M + BT - 1) / BT);
     p.n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);
     p.k_blocks = (int)((p.K + TS_BK - 1) / TS_BK);
-    const int super_tiles = p.m_tiles * ((p.n_tiles + CL - 1) / CL);
+    const int super_tiles = p.m_tiles * ((p.n_tiles + CL - 1) / CL) * p.layers;
     int clusters = sm_count() / CL;
     if (super_tiles < clusters) clusters = super_tiles;
     cudaLaunchConfig_t cfg = {};
@@ -391,26 +435,27 @@ static int ts_cluster_size() {
 
 template <typename OT>
 static int ts_dispatch_bt(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed,
-                          const UmmaParams& p, cudaStream_t s) {
-    if (p.M <= 32) return launch_ts<OT, 32, 1>(q_x, ldq, packed, ld_packed, p, s);
-    if (p.M <= 64) return launch_ts<OT, 64, 1>(q_x, ldq, packed, ld_packed, p, s);
-    if (p.M <= 128) return launch_ts<OT, 128, 1>(q_x, ldq, packed, ld_packed, p, s);
+                          const UmmaParams& p, cudaStream_t s, int64_t sq, int64_t sp) {
+    if (p.M <= 32) return launch_ts<OT, 32, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+    if (p.M <= 64) return launch_ts<OT, 64, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+    if (p.M <= 128) return launch_ts<OT, 128, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
     const int n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);
     const int cl = n_tiles >= 8 ? ts_cluster_size() : 1;
     static int bt = -1;
     if (bt < 0) { const char* e = getenv("TB200_GEMM_BT"); bt = e ? atoi(e) : 192; }
-    if constexpr (sizeof(OT) == 2) { if (bt == 160) return launch_ts<OT, 160, 1>(q_x, ldq, packed, ld_packed, p, s); }
-    if (cl == 4) return launch_ts<OT, 192, 4>(q_x, ldq, packed, ld_packed, p, s);
-    if (cl == 2) return launch_ts<OT, 192, 2>(q_x, ldq, packed, ld_packed, p, s);
-    return launch_ts<OT, 192, 1>(q_x, ldq, packed, ld_packed, p, s);
+    if constexpr (sizeof(OT) == 2) { if (bt == 160) return launch_ts<OT, 160, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp); }
+    if (cl == 4) return launch_ts<OT, 192, 4>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+    if (cl == 2) return launch_ts<OT, 192, 2>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+    return launch_ts<OT, 192, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
 }
 
 int gemm_ts_launch(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed, UmmaParams p,
-                   int out_dtype, cudaStream_t s) {
+                   int out_dtype, cudaStream_t s, int64_t sq, int64_t sp) {
+    if (p.layers < 1) p.layers = 1;
     switch (out_dtype) {
-        case TB200_F32:  return ts_dispatch_bt<float>(q_x, ldq, packed, ld_packed, p, s);
-        case TB200_BF16: return ts_dispatch_bt<__nv_bfloat16>(q_x, ldq, packed, ld_packed, p, s);
-        default:         return ts_dispatch_bt<__half>(q_x, ldq, packed, ld_packed, p, s);
+        case TB200_F32:  return ts_dispatch_bt<float>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+        case TB200_BF16: return ts_dispatch_bt<__nv_bfloat16>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+        default:         return ts_dispatch_bt<__half>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
     }
 }
 

@@ -19,7 +19,7 @@
 // Reference semantics: ScaledTernaryLinear.forward (binary/modules.py:101-109), ops.ternary_matmul
 // (impl/tf/moondream/ternary.py:279-281).
 #include <cstdlib>
-#include "tma.cuh"
+#include "umma.cuh"
 
 namespace tb200 {
 
@@ -761,10 +761,52 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
 
 using namespace tb200;
 
+// tokens from which the list is served by the grouped tcgen05 kernel (gemm_ts.cu) instead of mma.sync: above 8 tokens
+// the legacy IMMA pipe, not HBM, bounds the mma.sync kernel
+static int stream_umma_min_m() {
+    static const int v = getenv("TB200_STREAM_UMMA_MIN_M") ? atoi(getenv("TB200_STREAM_UMMA_MIN_M")) : 9;
+    return v;
+}
+static inline int64_t ru(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
 extern "C" size_t tb200_gemv_stream_workspace(int64_t M, int64_t K, int count) {
     if (M < 1 || K < 1 || count < 1) return 256;
     const StreamGeom gm = stream_geom(M, K);
-    return (size_t)gm.blob_stride * (size_t)count + 256;
+    const size_t image = (size_t)gm.blob_stride * (size_t)count + 256;
+    const int64_t rows = M * count;
+    const size_t umma = (size_t)(ru(rows * ru(K, 16), 256) + 2 * ru(rows * 4, 256) + 256);
+    return image > umma ? image : umma;
+}
+
+// > 8 tokens: per-token int8 quantisation of all layers in one launch (layout 1), then the grouped tcgen05 GEMM
+static int stream_umma(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                       const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                       const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                       void* out, int out_dtype, int64_t ldo, int64_t stride_out,
+                       int32_t* acc_out, int layers, void* workspace, cudaStream_t s) {
+    const int64_t ldq = ru(K, 16), rows = M * layers;
+    char* w = (char*)workspace;
+    int8_t* q_x = (int8_t*)w;      w += ru(rows * ldq, 256);
+    float* s_x = (float*)w;        w += ru(rows * 4, 256);
+    int32_t* sum_qx = (int32_t*)w;
+    const size_t xs = dtype_size(x_dtype);
+    if (layers == 1 || stride_x == M * ldx) {
+        int rc = tb200_quant_act_i8(x, x_dtype, rows, K, ldx, q_x, ldq, s_x, sum_qx, TB200_QLAYOUT_GEMM, s);
+        if (rc) return rc;
+    } else {
+        for (int l = 0; l < layers; ++l) {
+            int rc = tb200_quant_act_i8((const char*)x + (size_t)l * stride_x * xs, x_dtype, M, K, ldx, q_x + (int64_t)l * M * ldq, ldq,
+                                        s_x + (int64_t)l * M, sum_qx + (int64_t)l * M, TB200_QLAYOUT_GEMM, s);
+            if (rc) return rc;
+        }
+    }
+    UmmaParams p = {};
+    p.s_x = s_x; p.sum_qx = sum_qx; p.scale = scale; p.bias = bias;
+    p.out = out; p.ldo = ldo; p.acc_out = acc_out;
+    p.M = M; p.N = N; p.K = K; p.clip_val = fabsf(clip_val);
+    p.layers = layers; p.stride_act_rows = M; p.stride_sb = stride_sb; p.stride_out = stride_out;
+    { const char* e = getenv("TB200_GEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
+    return gemm_ts_launch(q_x, ldq, packed, ld_packed, p, out_dtype, s, M, stride_packed);
 }
 
 extern "C" int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
@@ -784,6 +826,9 @@ extern "C" int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t 
     TB_REQUIRE((uintptr_t)packed % 16 == 0 && stride_packed % 16 == 0, "gemv_stream: packed weights must be 16-byte aligned");
     TB_REQUIRE((uintptr_t)workspace % 256 == 0, "gemv_stream: workspace must be 256-byte aligned");
     TB_REQUIRE(count >= 1 && count <= 65535, "gemv_stream: bad layer count %d", count);
+    if (M >= stream_umma_min_m())
+        return stream_umma(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N, scale, bias, stride_sb,
+                           clip_val, out, out_dtype, ldo, stride_out, acc_out, count, workspace, (cudaStream_t)stream);
     return gemv_stream_impl(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N, scale, bias, stride_sb,
                             clip_val, out, out_dtype, ldo, stride_out, acc_out, count, workspace, (cudaStream_t)stream);
 }

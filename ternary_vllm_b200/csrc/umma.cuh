@@ -69,6 +69,24 @@ __device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uin
         "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
         ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
 }
+// Whole-warp forms: every lane executes the (warp-uniform) address arithmetic, so the compiler keeps it in uniform
+// registers, and one elected lane issues.  The single-thread forms above make the issuing loop divergent code whose
+// operands reach the uniform datapath through ELECT + R2UR.BROADCAST chains: ~13 dependent instructions per MMA, which
+// bounds skinny token tiles (the MMAs themselves are short).
+__device__ __forceinline__ void umma_i8_ts_warp(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
+}
+__device__ __forceinline__ void umma_commit_warp(uint32_t bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar) : "memory");
+}
 // 32 lanes x 32 columns (one 32-bit register per column) from registers into TMEM
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
     asm volatile(
@@ -91,11 +109,16 @@ struct UmmaParams {
     int m_tiles, n_tiles, k_blocks;
     float clip_val;
     int tma_out;      // epilogue stores through TMA (aligned output)
+    // grouped form (gemm_ts only): `layers` problems of identical shape in one persistent launch
+    int layers;                       // >= 1
+    int64_t stride_act_rows;          // s_x / sum_qx elements per layer (= M)
+    int64_t stride_sb;                // scale / bias elements per layer
+    int64_t stride_out;               // out elements per layer
     int dbg;          // TB200_GEMM_DBG experiments: 1 skip the epilogue body, 2 skip the expansion, 4 skip the MMAs
 };
 
 // shared epilogue of the tensor-core kernels: TMEM accumulator tile -> out (lane = output channel)
 int gemm_ts_launch(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed, UmmaParams p,
-                   int out_dtype, cudaStream_t s);
+                   int out_dtype, cudaStream_t s, int64_t stride_q_rows = 0, int64_t stride_packed = 0);
 
 }  // namespace tb200

@@ -17,8 +17,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t b, uint32_t ph) {
     while (!d) asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(d) : "r"(b), "r"(ph) : "memory");
 }
 
-constexpr int TILE = 16384;
-template <int V>
+template <int V, int TILE>
 __global__ void __launch_bounds__(64, 1) stream_k(const __grid_constant__ CUtensorMap map, const uint8_t* src, long long ntiles, int stages,
                                                   int rows_per_layer, unsigned* sink) {
     extern __shared__ uint8_t sm_raw[];
@@ -47,9 +46,16 @@ __global__ void __launch_bounds__(64, 1) stream_k(const __grid_constant__ CUtens
                 } else if (V == 1) {
                     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                                  ::"r"(dst), "l"(src + t * TILE), "r"(TILE), "r"(sb + 8 * s) : "memory");
-                } else {
+                } else if (V == 2) {
                     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                                  ::"r"(dst), "l"(&map), "r"(sb + 8 * s), "r"(0), "r"((int)(t * 128)) : "memory");
+                } else {
+                    // V == 4 / 5: a TILE is (bw bytes x 128 rows) of a [rows][1024 B] matrix; consecutive tiles of a CTA walk
+                    // the 1024/bw column blocks of one 128-row block (the tcgen05 GEMM's weight access pattern)
+                    const int bw = TILE / 128, kbs = 1024 / bw;
+                    const long long blk = t / kbs; const int kb = (int)(t - blk * kbs);
+                    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                                 ::"r"(dst), "l"(&map), "r"(sb + 8 * s), "r"(kb * bw), "r"((int)(blk * 128)) : "memory");
                 }
                 if (++s == stages) { s = 0; ph ^= 1u; }
             }
@@ -58,7 +64,7 @@ __global__ void __launch_bounds__(64, 1) stream_k(const __grid_constant__ CUtens
         int s = 0; uint32_t ph = 0; unsigned acc = 0;
         for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
             mbar_wait(sb + 8 * s, ph);
-            acc += reinterpret_cast<const unsigned*>(gb + s * TILE)[lane * 128];
+            acc += reinterpret_cast<const unsigned*>(gb + s * TILE)[lane * (TILE / 128)];
             __syncwarp();
             if (lane == 0) mbar_arrive(sb + 8 * (32 + s));
             if (++s == stages) { s = 0; ph ^= 1u; }
@@ -91,6 +97,7 @@ int main() {
     void* fp; cudaDriverEntryPointQueryResult q;
     cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &q);
     EncFn enc = (EncFn)fp;
+    constexpr int TILE = 16384;
     const long long ntiles = (long long)bytes / TILE;
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     for (int promo = 0; promo < 2; ++promo) {
@@ -111,9 +118,9 @@ int main() {
                     const size_t smem = (size_t)stages * TILE + 1024 + 64 * 8 + 64;
                     if (grid == 296 && smem > 110 * 1024) continue;
                     auto launch = [&]() {
-                        if (v == 0) { cudaFuncSetAttribute(stream_k<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); stream_k<0><<<grid, 64, smem>>>(m4, buf, ntiles, stages, N, sink); }
-                        if (v == 1) { cudaFuncSetAttribute(stream_k<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); stream_k<1><<<grid, 64, smem>>>(m4, buf, ntiles, stages, N, sink); }
-                        if (v == 2) { cudaFuncSetAttribute(stream_k<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); stream_k<2><<<grid, 64, smem>>>(m2, buf, ntiles, stages, N, sink); }
+                        if (v == 0) { cudaFuncSetAttribute(stream_k<0, 16384>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); stream_k<0, 16384><<<grid, 64, smem>>>(m4, buf, ntiles, stages, N, sink); }
+                        if (v == 1) { cudaFuncSetAttribute(stream_k<1, 16384>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); stream_k<1, 16384><<<grid, 64, smem>>>(m4, buf, ntiles, stages, N, sink); }
+                        if (v == 2) { cudaFuncSetAttribute(stream_k<2, 16384>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); stream_k<2, 16384><<<grid, 64, smem>>>(m2, buf, ntiles, stages, N, sink); }
                     };
                     launch(); cudaDeviceSynchronize();
                     cudaEventRecord(e0); launch(); launch(); cudaEventRecord(e1); cudaEventSynchronize(e1);
@@ -122,6 +129,28 @@ int main() {
                            2.0 * bytes / (ms * 1e-3) / 1e9, cudaGetErrorString(cudaGetLastError()));
                 }
             }
+        }
+    }
+    {   // strided column-block boxes: 64 B x 128 rows (8 KB, SWIZZLE_64B) and 128 B x 128 rows (16 KB, SWIZZLE_128B)
+        const long long rows = (long long)(bytes / 1024);
+        CUtensorMap m64, m128;
+        { cuuint64_t d[2] = {1024, (cuuint64_t)rows}, st[1] = {1024}; cuuint32_t bx[2] = {64, 128}, es[2] = {1, 1};
+          enc(&m64, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, buf, d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE); }
+        { cuuint64_t d[2] = {1024, (cuuint64_t)rows}, st[1] = {1024}; cuuint32_t bx[2] = {128, 128}, es[2] = {1, 1};
+          enc(&m128, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, buf, d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE); }
+        for (int v : {4, 5}) for (int stages : {8, 12, 20}) {
+            const int tile = v == 4 ? 8192 : 16384;
+            if (v == 5 && stages > 12) continue;
+            const size_t smem = (size_t)stages * tile + 1024 + 64 * 8 + 64;
+            const long long nt = (long long)bytes / tile;
+            auto launch = [&]() {
+                if (v == 4) { cudaFuncSetAttribute(stream_k<4, 8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); stream_k<4, 8192><<<148, 64, smem>>>(m64, buf, nt, stages, N, sink); }
+                else { cudaFuncSetAttribute(stream_k<5, 16384>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); stream_k<5, 16384><<<148, 64, smem>>>(m128, buf, nt, stages, N, sink); }
+            };
+            launch(); cudaDeviceSynchronize();
+            cudaEventRecord(e0); launch(); launch(); cudaEventRecord(e1); cudaEventSynchronize(e1);
+            float ms; cudaEventElapsedTime(&ms, e0, e1);
+            printf("variant %d (%3d B x 128 rows) stages %2d: %7.1f GB/s (%s)\n", v, tile / 128, stages, 2.0 * bytes / (ms * 1e-3) / 1e9, cudaGetErrorString(cudaGetLastError()));
         }
     }
     for (int grid : {148 * 2, 148 * 4, 148 * 8}) {
