@@ -5,11 +5,15 @@
 
 N=1 workload = BASELINE.json configs[1], the decode GEMV sweep: ternary Linear 4096x4096 and
 4096x11008 at batch 1/8/32 with bf16 activations.  One STEP runs every case of the sweep over a
-ring of distinct layers whose packed weights exceed L2 (so every layer is streamed from HBM).
-`value` = algorithmic bytes of the step / device time (GB/s), replayed as one CUDA graph with
-programmatic dependent launch between layers; `e2e` = the same sweep through the host-buffer
-C-ABI call (tb200_linear_forward_host: H2D of the tokens, kernel, D2H of the result per layer).
-Extra keys: per-case numbers, the tcgen05 prefill GEMM (configs[2]) in TOPS, `roofline`,
+ring of >= 64 distinct layers whose packed weights exceed L2 (so every layer is streamed from HBM),
+one tb200_gemv_stream call per case (activation quantiser launch + ONE persistent GEMV launch for
+the whole ring; tcgen05 grouped kernel above 8 tokens).  `value` = algorithmic bytes of the step /
+device time (GB/s), the step replayed as one CUDA graph; `e2e` = the same sweep through the
+host-buffer C-ABI call (tb200_gemv_stream_host: H2D of all activations of the ring, the two
+launches, D2H of all outputs, per case).  Every case also reports the same ring as a CHAIN of
+per-layer calls (`cases[i].chain`: tb200_gemv with programmatic dependent launch / tb200_linear_forward),
+which is what the sequential layers of one model do and is latency-bound.
+Extra keys: the tcgen05 prefill GEMM (configs[2]) in TOPS, ViT-L shapes (configs[3]), `roofline`,
 `cpu_baseline` (the oracle port of the reference forward timed on this box's host cores).
 
 N>1 (torchrun): BASELINE.json configs[4], the 7B projections N-sharded across ranks with an
@@ -310,7 +314,7 @@ def run_b200(args):
                 "achieved": dom["gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": dom["gbs"] / pk["hbm_gbs"],
                 "peak_source": pk["source"], "frac_of_spec_8TBs": dom["gbs"] / 8000.0,
                 "algorithmic_bytes_per_launch": algorithmic_bytes(4096, 11008, 1) * dom["layers"],
-                "avg_launch_us": dom["us_per_call"], "traffic": TRAFFIC_BYTES,
+                "avg_launch_us": dom["us_per_call"], "traffic": TRAFFIC_BYTES_PER_LAYER * dom["layers"],
                 "chain_of_single_layer_launches_gbs": dom["chain"]["gbs"]}
 
     # ---- e2e: host buffers through the C ABI ----
@@ -342,7 +346,10 @@ def run_b200(args):
 
 
 RING_MIN = 64               # layers per ring (>= 2.2 x L2 in packed bytes for both shapes)
-TRAFFIC_BYTES = None        # dram__bytes_read+write per launch of the dominant kernel, filled from profiles/ (see below)
+# dram__bytes_read.sum + dram__bytes_write.sum of gemv_stream_kernel<1,1,2,2> per layer of 4096x11008, M=1:
+# (284.18 + 4.33) MB over the 25 layers of the ncu capture (profiles/r1_gemv_stream_m1.summary.txt); the algorithmic
+# figure is 11.39 MB per layer
+TRAFFIC_BYTES_PER_LAYER = (284175104 + 4328960) / 25
 
 
 def run_e2e(args, lib, dev, rings, cases, step_bytes):

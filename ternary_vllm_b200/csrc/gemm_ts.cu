@@ -155,11 +155,11 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
             int s = 0; uint32_t ph = 0; int a = 0; int it = 0;
             for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
                 const int buf = it & 1;
-                mbar_wait(bar_tempty(buf), (((uint32_t)it >> 1) & 1u) ^ 1u);
+                mbar_wait_uniform(bar_tempty(buf), (((uint32_t)it >> 1) & 1u) ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BT);
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
-                    mbar_wait(bar_ready(s), ph);
+                    mbar_wait_uniform(bar_ready(s), ph);
                     tc_fence_after();
                     const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
                     if (!(p.dbg & 4)) {

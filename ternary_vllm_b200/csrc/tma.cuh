@@ -46,6 +46,21 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity)
         if (++spins > 20000000u) __trap();
     }
 }
+// whole-warp wait whose loop condition is a warp vote: the compiler can prove the control flow convergent and keeps
+// warp-uniform values of the surrounding loop in uniform registers
+__device__ __forceinline__ void mbar_wait_uniform(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (true) {
+        uint32_t done;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (__all_sync(0xffffffffu, done != 0)) break;
+        if (++spins > 20000000u) __trap();
+    }
+}
 // one non-blocking test: issue early, consume the result later (hides the ~70-clock PHASECHK + branch latency)
 __device__ __forceinline__ uint32_t mbar_test(uint32_t bar, uint32_t parity) {
     uint32_t done;
