@@ -36,7 +36,10 @@ template <int BT, int OSZ = 4> struct TsCfg {
     static constexpr int B_BYTES = BT * TS_BK;
     static constexpr int STAGE_BYTES = B_BYTES + TS_P_BYTES;
     static constexpr int STAGES = BT >= 192 ? 3 : BT >= 128 ? 4 : BT >= 64 ? 6 : BT >= 32 ? 12 : 8;   // 160 -> 4 stages of 48 KB
-    static constexpr int D_COLS = 2 * BT;
+    // skinny token tiles: TWO warps issue the MMAs of alternate k-blocks into their own accumulator (the issuing warp's
+    // instruction chain, not the tensor pipe, bounds 32-token tiles); the epilogue adds the two partial sums
+    static constexpr int DUAL = BT <= 32 ? 2 : 1;
+    static constexpr int D_COLS = 2 * BT * DUAL;
     // A tiles in TMEM: the expand -> MMA -> retire -> reuse loop of a slot is ~2000 clocks long, so skinny token tiles
     // (which finish a k-block's MMAs quickly and have TMEM columns to spare) keep six of them in flight
     static constexpr int NSA = BT <= 32 ? 6 : BT <= 64 ? 4 : 2;
@@ -100,7 +103,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
             mbar_init(bar_done(s), CL);                      // every CTA of the cluster must have retired the stage
         }
         for (int b = 0; b < 2; ++b) {
-            mbar_init(bar_tfull(b), 1);
+            mbar_init(bar_tfull(b), (CL == 1) ? Cfg::DUAL : 1);
             mbar_init(bar_tempty(b), 4);
         }
         mbar_fence_init();
@@ -147,8 +150,8 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                 }
             }
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer =====================
+    } else if (warp == 1 || (warp == 3 && CL == 1 && Cfg::DUAL == 2)) {
+        // ===================== MMA issuer(s) =====================
         // CL == 1: the whole warp runs the loop (uniform code, see umma_i8_ts_warp); clusters keep the single-thread form
         if (CL == 1) {
             constexpr uint32_t idesc = umma_idesc_i8(TS_ROWS, BT);
@@ -157,25 +160,34 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                 const int buf = it & 1;
                 mbar_wait_uniform(bar_tempty(buf), (((uint32_t)it >> 1) & 1u) ^ 1u);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BT);
+                constexpr int ND = Cfg::DUAL;
+                const int me = ND == 2 ? (warp == 3 ? 1 : 0) : 0;             // which alternate k-blocks / accumulator
+                const uint32_t d_tmem = tmem_base + (uint32_t)((buf * ND + me) * BT);
+                int mine_done = 0;
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
-                    mbar_wait_uniform(bar_ready(s), ph);
-                    tc_fence_after();
-                    const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
-                    if (!(p.dbg & 4)) {
+                    if (ND == 1 || (kb & 1) == me) {
+                        mbar_wait_uniform(bar_ready(s), ph);
+                        tc_fence_after();
+                        const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
+                        if (!(p.dbg & 4)) {
 #pragma unroll
-                        for (int j = 0; j < TS_KS; ++j) {
-                            const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
+                            for (int j = 0; j < TS_KS; ++j) {
+                                const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
 #pragma unroll
-                            for (int k = 0; k < 4; ++k)
-                                umma_i8_ts_warp(d_tmem, a_tmem + (uint32_t)(j * 32 + k * 8), bdesc + 2u * k, idesc,
-                                                (kb | j | k) ? 1u : 0u);
+                                for (int k = 0; k < 4; ++k)
+                                    umma_i8_ts_warp(d_tmem, a_tmem + (uint32_t)(j * 32 + k * 8), bdesc + 2u * k, idesc,
+                                                    (mine_done | j | k) ? 1u : 0u);
+                            }
                         }
+                        mine_done = 1;
+                        umma_commit_warp(bar_done(s));
+                        if (kb + ND >= p.k_blocks) umma_commit_warp(bar_tfull(buf));   // my last k-block of the tile
                     }
-                    umma_commit_warp(bar_done(s));
-                    if (kb == p.k_blocks - 1) umma_commit_warp(bar_tfull(buf));
                     if (++s == NS) { s = 0; ph ^= 1u; }
                     if (++a == TS_NSA) a = 0;
+                }
+                if (ND == 2 && me >= p.k_blocks) {      // a single k-block: the second issuer has nothing to add
+                    if (lane == 0) mbar_arrive(bar_tfull(buf));
                 }
             }
         } else if (lane == 0) {
@@ -251,8 +263,15 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                                  : "=r"(sqv[j]), "=r"(sqv[j + 1]), "=r"(sqv[j + 2]), "=r"(sqv[j + 3]) : "r"(sq_s + (c0 + j) * 4));
                 }
                 uint32_t r[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0);
+                constexpr int ND = (CL == 1) ? Cfg::DUAL : 1;
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * ND * BT + c0);
                 if (CH == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
+                if (ND == 2 && p.k_blocks > 1) {
+                    uint32_t r2[32];
+                    if (CH == 32) tmem_ld32(taddr + (uint32_t)BT, r2); else tmem_ld16(taddr + (uint32_t)BT, r2);
+#pragma unroll
+                    for (int j = 0; j < CH; ++j) r[j] += r2[j];
+                }
                 if (p.tma_out && CH == 32) {
                     // registers -> shared staging [token][channel] -> one TMA store of 32 tokens x 128 channels
                     // (256-byte rows, asynchronous); the staging buffers alternate per chunk
