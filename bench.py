@@ -16,8 +16,9 @@ which is what the sequential layers of one model do and is latency-bound.
 Extra keys: the tcgen05 prefill GEMM (configs[2]) in TOPS, ViT-L shapes (configs[3]), `roofline`,
 `cpu_baseline` (the oracle port of the reference forward timed on this box's host cores).
 
-N>1 (torchrun): BASELINE.json configs[4], the 7B projections N-sharded across ranks with an
-all-gather of the output shards (strong scaling: the same full layers on more GPUs).
+N>1 (torchrun -> bench_tp.py): the same sweep with every layer N-sharded across the ranks (configs[4]'s
+tensor parallelism), the all-gather fused into the GEMV epilogues over NVLink peer memory + one barrier per
+call (strong scaling: the same full layers on more GPUs); configs[4]'s other projections in `tp_cases`.
 """
 import argparse
 import json
@@ -175,9 +176,10 @@ CONFIG_N1 = {"workload": "configs[1] decode GEMV sweep: ternary Linear 4096x4096
              "l2_policy": "inputs larger than L2 (ring of 67 x 4.2 MB / 64 x 11.3 MB distinct packed layers per case, "
                           "every layer read once per step)",
              "api": "tb200_gemv_stream: one call per sweep case over its ring of layers"}
-CONFIG_TP = {"workload": "configs[4] 7B-class decoder projections 4096x11008, 11008x4096, 4096x32000 (lm_head), "
-                         "N-sharded across ranks, decode batch 1/8/32, all-gather of the output shards",
-             "l2_policy": "inputs larger than L2 (ring of distinct layers per shape)"}
+CONFIG_TP = {"workload": "configs[1] decode GEMV sweep (4096x4096, 4096x11008, batch 1/8/32, the N=1 rings) with every layer "
+                         "N-sharded across the ranks as in configs[4]; configs[4]'s 11008x4096 and 4096x32000 in tp_cases",
+             "l2_policy": "inputs larger than L2 (rings of 67 / 64 distinct full layers, every layer read once per step)",
+             "api": "tb200_gemv_stream_tp: one call per sweep case over the rank's row blocks of the ring + one barrier"}
 
 
 # ------------------------------------------------------------------------------------ B200 arm

@@ -1,18 +1,23 @@
 """bench_tp.py — the N>1 arm of bench.py (launched under torchrun, one rank per GPU).
 
-Workload = BASELINE.json configs[4]: 7B-class decoder projections 4096x11008, 11008x4096 and the
-4096x32000 lm_head, N-sharded across the ranks (ternary_vllm_b200.parallel.shard_rows), decode
-batches 1/8/32; every layer = local GEMV on the rank's row block + ONE all-gather of the bf16
-output shards over NCCL.  STRONG scaling: the same full layers on more GPUs, so
-`value` = algorithmic bytes of the full layers / max-over-ranks device time.
+Headline (`value`): the SAME decode sweep as the N=1 arm (BASELINE.json configs[1]: 4096x4096 and 4096x11008 at
+batch 1/8/32 over rings of 67/64 distinct layers), every layer N-sharded across the ranks
+(ternary_vllm_b200.parallel.shard_rows).  Per case ONE tb200_gemv_stream_tp call per rank over its row blocks of the
+whole ring, whose epilogues store the outputs into every rank's buffer over NVLink peer memory (the all-gather fused
+into the kernel), then ONE cross-rank barrier.  STRONG scaling: the same full layers on more GPUs, so
+`value` = algorithmic bytes of the full layers / max-over-ranks device time, directly comparable with the N=1 line.
+
+`tp_cases` adds configs[4]'s other projections (11008x4096, 4096x32000 lm_head) in the same form; `chain` is the
+sequential-layers form (one TPShardedLinear call + one barrier PER LAYER, latency-bound) with its NCCL all-gather
+baseline next to it.
 """
 import json
 import math
 import os
-import statistics
 
-TP_SHAPES = [(4096, 11008), (11008, 4096), (4096, 32000)]     # (K, N)
-TP_BATCHES = [1, 8, 32]
+TP_EXTRA_SHAPES = [(11008, 4096), (4096, 32000)]     # (K, N): configs[4] beyond the sweep's 4096x11008
+CHAIN_SHAPES = [(4096, 11008), (11008, 4096), (4096, 32000)]
+CHAIN_LAYERS = 8
 L2_BYTES = 126e6
 
 
@@ -20,9 +25,9 @@ def run_tp(args, metric):
     import torch
     import torch.distributed as dist
 
-    from bench import CONFIG_TP, ClockSampler, algorithmic_bytes, peaks
+    from bench import BATCHES, CONFIG_TP, RING_MIN, SHAPES, ClockSampler, algorithmic_bytes, peaks
     from ternary_vllm_b200 import ops
-    from ternary_vllm_b200.parallel import TPShardedLinear, shard_rows, shard_size
+    from ternary_vllm_b200.parallel import TPShardedLinear, TPShardedStream, shard_rows
 
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     dev = torch.device("cuda", local)
@@ -30,38 +35,34 @@ def run_tp(args, metric):
     dist.init_process_group("nccl", device_id=dev)
     pk = peaks()
 
-    # every rank builds only its own row block of every layer
-    rings = {}
-    for (K, N) in TP_SHAPES:
+    def build_stream(K, N, R):
+        """This rank's row block of R full layers (rows seeded per layer and rank; the reference's own init)."""
         a, b = shard_rows(N, world, rank)
-        per_layer = shard_size(N, world) * K / 4
-        R = max(4, min(32, int(math.ceil(2.2 * L2_BYTES / max(per_layer, 1)))))
-        g = torch.Generator(device=dev).manual_seed(1000 + K + N)            # same full matrices on every rank
-        layers = []
+        ld = ops.packed_pitch(K)
+        packed = torch.empty((R, b - a, ld), dtype=torch.uint8, device=dev)
+        gl = torch.Generator(device=dev).manual_seed(K * 131 + N * 7 + rank)
         for r in range(R):
-            # generate the rank's rows only (seeded per layer and row block so that shards are consistent)
-            gl = torch.Generator(device=dev).manual_seed(K * 131 + N * 7 + r * 1009 + rank)
-            W = torch.randn(b - a, K, generator=gl, device=dev).clip_(-1, 1)
-            packed = ops.quantize_pack(W, "ternary")
-            scale = torch.full((b - a,), 1.0 / math.sqrt(K), device=dev)
-            bias = torch.randn(b - a, generator=gl, device=dev)
-            layers.append(TPShardedLinear(packed, scale, bias, K, N, 100.0).enable_peer_gather(32))
-        rings[(K, N)] = layers
-    cases = [(K, N, M) for (K, N) in TP_SHAPES for M in TP_BATCHES]
-    xs = {c: torch.randn(c[2], c[0], device=dev, dtype=torch.bfloat16) for c in cases}
+            packed[r] = ops.quantize_pack(torch.randn(b - a, K, generator=gl, device=dev).clip_(-1, 1), "ternary")
+        scale = torch.full((R, b - a), 1.0 / math.sqrt(K), device=dev)
+        bias = torch.randn((R, b - a), generator=gl, device=dev)
+        return TPShardedStream(packed, scale, bias, K, N, 100.0, max_tokens=32)
 
-    def step(gather=True):
-        """gather=True: the product path (all-gather fused into the GEMV epilogue over NVLink peer memory + one
-        cross-rank barrier per layer); gather=False: local compute only; gather="nccl": NCCL all-gather baseline."""
-        with torch.no_grad():
-            for c in cases:
-                for layer in rings[c[:2]]:
-                    if gather is True:
-                        layer(xs[c])
-                    else:
-                        y = layer.local_forward(xs[c])
-                        if gather == "nccl":
-                            layer.gather(y)
+    streams, ring_len = {}, {}
+    for (K, N) in SHAPES + TP_EXTRA_SHAPES:
+        R = max(RING_MIN if (K, N) in SHAPES else 24, int(math.ceil(2.2 * L2_BYTES / (N * K / 4))))   # same rings as N=1
+        ring_len[(K, N)] = R
+        streams[(K, N)] = build_stream(K, N, R)
+    cases = [(K, N, M) for (K, N) in SHAPES for M in BATCHES]
+    extra = [(K, N, M) for (K, N) in TP_EXTRA_SHAPES for M in BATCHES]
+    g = torch.Generator(device=dev).manual_seed(99)                 # same activations on every rank (x is replicated)
+    xs = {c: torch.randn(ring_len[c[:2]], c[2], c[0], generator=g, device=dev, dtype=torch.bfloat16) for c in cases + extra}
+
+    def run_case(c, barrier=True):
+        return streams[c[:2]](xs[c], barrier=barrier)
+
+    def step(barrier=True):
+        for c in cases:
+            run_case(c, barrier)
 
     def timed(fn, iters):
         dist.barrier()
@@ -77,84 +78,141 @@ def run_tp(args, metric):
         dist.barrier()
         return float(t.item())
 
+    def graphed(fn):
+        """fn captured as one CUDA graph (the step holds no NCCL call: peer stores + symmetric-memory barrier)."""
+        st = torch.cuda.Stream(dev)
+        fn()
+        torch.cuda.synchronize()
+        n0 = ops.launch_count()
+        with torch.cuda.stream(st):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=st):
+                fn()
+        torch.cuda.synchronize()
+        return gr, ops.launch_count() - n0
+
     for _ in range(max(3, args.warmup)):
         step()
     torch.cuda.synchronize()
-    # one step = one CUDA graph (local kernels + NCCL all-gathers): decode layers are a few microseconds,
-    # eager launches from Python would measure the host
-    n0 = ops.launch_count()
     mode = "cuda graph"
     try:
-        if os.environ.get("TB200_TP_GRAPH", "1") != "1":      # the step holds no NCCL call (peer-memory gather), so it captures
+        if os.environ.get("TB200_TP_GRAPH", "1") != "1":
             raise RuntimeError("graph capture disabled")
-        st = torch.cuda.Stream(dev)
-        with torch.cuda.stream(st):
-            g_full = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g_full, stream=st):
-                step()
-            launches_per_step = ops.launch_count() - n0
-            g_local = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g_local, stream=st):
-                step(False)
-        torch.cuda.synchronize()
+        g_full, launches_per_step = graphed(step)
+        g_local, _ = graphed(lambda: step(False))
         run_full, run_local = g_full.replay, g_local.replay
-    except Exception as e:                               # capture of the collective refused: eager fallback
-        mode = f"eager ({type(e).__name__})"
+    except Exception as e:                               # capture refused: eager fallback
+        mode = f"eager ({type(e).__name__}: {e})"[:200]
         torch.cuda.synchronize()
-        launches_per_step = None
+        n0 = ops.launch_count()
+        step()
+        launches_per_step = ops.launch_count() - n0
         run_full, run_local = step, (lambda: step(False))
     for _ in range(3):
         run_full()
-    n1 = ops.launch_count()
     sampler = ClockSampler(local)
     sampler.start()
     ms = timed(run_full, args.steps)
     clocks = sampler.stop()
-    launches = launches_per_step * args.steps if launches_per_step is not None else ops.launch_count() - n1
-    ms_nogather = timed(run_local, max(2, args.steps // 2)) / max(2, args.steps // 2)
-    step("nccl")
-    ms_nccl = timed(lambda: step("nccl"), 2) / 2            # eager NCCL all-gather baseline (never captured)
-    ms_eager = timed(step, 2) / 2                           # the product path launched eagerly, for the same comparison
+    n_loc = max(2, args.steps // 2)
+    ms_nobarrier = timed(run_local, n_loc) / n_loc
 
-    # end to end: pinned host activations in, full gathered output back to pinned host memory, per layer
-    hx = {c: torch.randn(c[2], c[0], dtype=torch.bfloat16).pin_memory() for c in cases}
-    hy = {c: torch.empty(c[2], c[1], dtype=torch.bfloat16).pin_memory() for c in cases}
+    # per case (sweep + configs[4] extras): one call + one barrier, replayed as a graph
+    def case_rows(cs):
+        rows = []
+        for c in cs:
+            K, N, M = c
+            R = ring_len[(K, N)]
+            try:
+                gr, _ = graphed(lambda: run_case(c))
+                fn = gr.replay
+            except Exception:
+                fn = lambda: run_case(c)        # noqa: E731
+            for _ in range(2):
+                fn()
+            t = timed(fn, 10) / 10 * 1e-3
+            b = algorithmic_bytes(K, N, M) * R
+            rows.append({"K": K, "N": N, "M": M, "layers": R, "us_per_call": t * 1e6, "us_per_layer": t / R * 1e6,
+                         "gbs": b / t / 1e9, "frac_hbm_measured_aggregate": b / t / 1e9 / (pk["hbm_gbs"] * world),
+                         "tokens_per_s": M * R / t, "gather_bytes_received_per_rank": R * M * N * 2 * (world - 1) // world})
+        return rows
+
+    per_case = case_rows(cases)
+    tp_cases = case_rows(extra)
+
+    # the sequential-layers form: one call + one barrier per layer (latency-bound), NCCL all-gather baseline beside it
+    chain = []
+    xs1 = {}
+    for (K, N) in CHAIN_SHAPES:
+        st = streams[(K, N)]
+        layers = [TPShardedLinear(st.packed[r], st.scale[r], st.bias[r], K, N, 100.0).enable_peer_gather(32)
+                  for r in range(CHAIN_LAYERS)]
+        for M in BATCHES:
+            x = xs1.setdefault((K, M), torch.randn(M, K, device=dev, dtype=torch.bfloat16))
+
+            def run_chain(mode_="peer"):
+                with torch.no_grad():
+                    for layer in layers:
+                        if mode_ == "peer":
+                            layer(x)
+                        else:
+                            layer.gather(layer.local_forward(x))
+            try:
+                gr, _ = graphed(run_chain)
+                fn = gr.replay
+            except Exception:
+                fn = run_chain
+            fn()
+            t_peer = timed(fn, 5) / 5 / CHAIN_LAYERS * 1e-3
+            run_chain("nccl")
+            t_nccl = timed(lambda: run_chain("nccl"), 3) / 3 / CHAIN_LAYERS * 1e-3
+            b = algorithmic_bytes(K, N, M)
+            chain.append({"K": K, "N": N, "M": M, "us_per_layer_fused_peer_gather": t_peer * 1e6, "gbs": b / t_peer / 1e9,
+                          "us_per_layer_nccl_all_gather_eager": t_nccl * 1e6})
+        del layers
+
+    # end to end: pinned host activations in, full gathered outputs back to pinned host memory, per case
+    hx = {c: torch.randn(ring_len[c[:2]], c[2], c[0], dtype=torch.bfloat16).pin_memory() for c in cases}
+    hy = {c: torch.empty(ring_len[c[:2]], c[2], c[1], dtype=torch.bfloat16).pin_memory() for c in cases}
+    dx = {c: torch.empty_like(xs[c]) for c in cases}
 
     def step_e2e():
-        with torch.no_grad():
-            for c in cases:
-                for layer in rings[c[:2]]:
-                    xd = hx[c].to(dev, non_blocking=True)
-                    y = layer.gather(layer.local_forward(xd))
-                    hy[c].copy_(y, non_blocking=True)
+        for c in cases:
+            dx[c].copy_(hx[c], non_blocking=True)
+            y = streams[c[:2]](dx[c])
+            hy[c].copy_(y, non_blocking=True)
         torch.cuda.synchronize()
 
     step_e2e()
-    e2e_steps = max(2, min(5, args.steps))
+    e2e_steps = max(3, min(10, args.steps))
     ms_e2e = timed(step_e2e, e2e_steps) / e2e_steps
-    step_bytes = sum(algorithmic_bytes(*c) * len(rings[c[:2]]) for c in cases)
-    h2d = sum(c[2] * c[0] * 2 * len(rings[c[:2]]) for c in cases)
-    d2h = sum(c[2] * c[1] * 2 * len(rings[c[:2]]) for c in cases)
-    step_tokens = sum(c[2] * len(rings[c[:2]]) for c in cases)
+    step_bytes = sum(algorithmic_bytes(*c) * ring_len[c[:2]] for c in cases)
+    h2d = sum(hx[c].numel() * 2 for c in cases)
+    d2h = sum(hy[c].numel() * 2 for c in cases)
+    step_tokens = sum(c[2] * ring_len[c[:2]] for c in cases)
     value = step_bytes * args.steps / (ms * 1e-3) / 1e9
     if rank == 0:
         line = {
             "metric": metric, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 (u8 codes x s8 activations, s32 accumulate)", "data": "synthetic",
-            "config": dict(CONFIG_TP, parallelism=f"tp{world} (N-sharded, all-gather)"),
+            "config": dict(CONFIG_TP, parallelism=f"tp{world} (N-sharded, all-gather fused into the GEMV epilogues)"),
             "tokens_per_s": step_tokens * args.steps / (ms * 1e-3), "clocks": clocks,
-            "gpu_launches": launches, "launch_mode": mode, "ms_per_step_without_all_gather": ms_nogather,
-            "all_gather_share": max(0.0, 1.0 - ms_nogather / (ms / args.steps)),
-            "gather": "fused into the GEMV epilogue: stores to every rank's buffer over NVLink peer memory + 1 barrier per layer",
-            "eager_ms_per_step": {"fused_peer_gather": ms_eager, "nccl_all_gather_baseline": ms_nccl},
+            "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step, "launch_mode": mode,
+            "ms_per_step_without_barriers": ms_nobarrier,
+            "barrier_share": max(0.0, 1.0 - ms_nobarrier / (ms / args.steps)),
+            "gather": "fused into the epilogues of tb200_gemv_stream_tp: stores to every rank's buffer over NVLink peer "
+                      "memory + ONE symmetric-memory barrier per call (a call = one sweep case over its ring of layers)",
             "e2e": {"value": step_bytes / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
-                    "api": "TPShardedLinear.forward on pinned host activations, gathered output copied back to pinned host"},
+                    "api": "TPShardedStream.forward per sweep case on pinned host activations (every rank copies x in and "
+                           "the full gathered output back to pinned host memory)"},
+            "cases": per_case, "tp_cases": tp_cases, "chain": chain,
             "roofline": {"bound": "hbm", "achieved": value, "peak": pk["hbm_gbs"] * world, "unit": "GB/s",
-                                      "frac": value / (pk["hbm_gbs"] * world), "traffic": None,
-                                      "note": "aggregate over ranks; decode shards are collective-latency bound"},
+                         "frac": value / (pk["hbm_gbs"] * world), "traffic": None, "peak_source": pk["source"],
+                         "note": "aggregate over ranks (peak = ranks x measured copy rate); per-rank kernel as in the N=1 line"},
             "cpu_baseline": None,
         }
         print(json.dumps(line))
+    dist.barrier()
     dist.destroy_process_group()

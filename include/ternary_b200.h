@@ -187,6 +187,18 @@ int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t K, int64_t 
                       void* out, int out_dtype, int64_t ldo, int64_t stride_out,
                       int count, int32_t* acc_out, void* workspace, void* stream);
 
+/* Tensor-parallel form of tb200_gemv_stream (the reference has no distributed code): `packed`,
+ * `scale`, `bias` hold this rank's row block (N_local rows) of every layer; the all-gather is fused into the
+ * epilogues: each output element is stored into EVERY rank's [count, M, ldo] buffer through peer-mapped (NVLink)
+ * pointers.  out_peers[r] addresses element (layer 0, token 0, first column of THIS rank's block) of rank r's
+ * buffer (own buffer included), 1 <= n_peers <= 8.  ONE cross-rank barrier by the caller after the call makes the
+ * gathered outputs of the whole list consumable. */
+int tb200_gemv_stream_tp(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                         const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N_local,
+                         const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                         void* const* out_peers, int n_peers, int out_dtype, int64_t ldo, int64_t stride_out,
+                         int count, void* workspace, void* stream);
+
 /* tb200_gemv_stream with HOST activations x_host [count, M, K] and outputs out_host [count, M, N] (dense, pinned):
  * one H2D copy, the two launches, one D2H copy, in order on `stream`.  dev_x / dev_out: device staging buffers of the
  * same sizes.  The end-to-end form of a decode step over a list of layers (bench.py `e2e`). */

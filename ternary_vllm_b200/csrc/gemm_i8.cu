@@ -280,7 +280,7 @@ extern "C" int tb200_gemm_i8(const int8_t* q_x, int64_t ldq, const float* s_x, c
     TB_REQUIRE((uintptr_t)q_x % 16 == 0 && (uintptr_t)packed % 16 == 0, "gemm_i8: q_x and packed must be 16-byte aligned");
     TB_REQUIRE(dtype_ok(out_dtype), "gemm_i8: bad out dtype %d", out_dtype);
     if (M == 0 || N == 0) return TB200_OK;
-    UmmaParams p;
+    UmmaParams p = {};
     p.s_x = s_x; p.sum_qx = sum_qx; p.scale = scale; p.bias = bias;
     p.out = out; p.ldo = ldo; p.acc_out = acc_out;
     p.M = M; p.N = N; p.K = K; p.clip_val = fabsf(clip_val);

@@ -58,7 +58,7 @@ template <int BT, int OSZ = 4> struct TsCfg {
 template <typename OT, int BT, int CL>
 __global__ void __launch_bounds__(TS_THREADS, 1)
 umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_pw,
-               const __grid_constant__ CUtensorMap map_out, const UmmaParams p) {
+               const __grid_constant__ CUtensorMap map_out, const __grid_constant__ PeerMaps pm, const UmmaParams p) {
     using Cfg = TsCfg<BT, (int)sizeof(OT)>;
     constexpr int NS = Cfg::STAGES;
     constexpr int TS_NSA = Cfg::NSA;
@@ -225,7 +225,10 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         const int et = threadIdx.x - 128;
         OT* out_base = reinterpret_cast<OT*>(p.out);
         int it = 0, chunk_no = 0;
-        if (et == 0 && p.tma_out) tma_prefetch_desc(&map_out);
+        if (et == 0 && p.tma_out) {
+            tma_prefetch_desc(&map_out);
+            for (int r = 0; r < p.n_peers; ++r) tma_prefetch_desc(&pm.m[r]);
+        }
         for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
             const int buf = it & 1;
             const int layer = t / tiles_per_layer, tl = t - layer * tiles_per_layer;
@@ -291,8 +294,13 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     fence_proxy_async();
                     asm volatile("bar.sync 1, 128;" ::: "memory");
                     if (et == 0) {
-                        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                                     ::"l"(&map_out), "r"(stg), "r"(n_tile * TS_ROWS), "r"((int)(m0 + c0)), "r"(layer) : "memory");
+                        if (p.n_peers == 0) {
+                            tma_store_3d(&map_out, stg, n_tile * TS_ROWS, (int)(m0 + c0), layer);
+                        } else {
+#pragma unroll 1
+                            for (int r = 0; r < p.n_peers; ++r)     // tensor-parallel gather: the tile goes to every rank over NVLink
+                                tma_store_3d(&pm.m[r], stg, n_tile * TS_ROWS, (int)(m0 + c0), layer);
+                        }
                         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     }
                     ++chunk_no;
@@ -307,7 +315,12 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         const OT yv = from_f32<OT>(epilogue(tv, sc, bi, p.clip_val));
                         if (j < valid) {
                             if (acc_on) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
-                            orow[(int64_t)j * p.ldo] = yv;
+                            if (p.n_peers == 0) orow[(int64_t)j * p.ldo] = yv;
+                            else {
+#pragma unroll 1
+                                for (int r = 0; r < p.n_peers; ++r)     // unaligned peer buffers: 64-byte warp segments per rank
+                                    reinterpret_cast<OT*>(p.peers[r])[(orow - out_base) + (int64_t)j * p.ldo] = yv;
+                            }
                         }
                     }
                 }
@@ -374,6 +387,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         }
     }
 
+    if (p.n_peers > 0) __threadfence_system();      // peer stores are visible system-wide before the grid completes
     tc_fence_before();
     __syncthreads();
     if (CL > 1) {   // no CTA may exit while a peer can still multicast into its shared memory or arrive on its barriers
@@ -405,8 +419,11 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
     if (rc) return rc;
     // output tile stores through TMA need a 16-byte aligned base and row pitch
     CUtensorMap map_out = map_pw;
+    PeerMaps peer_maps;
+    for (int r = 0; r < 8; ++r) peer_maps.m[r] = map_pw;
     p.tma_out = (BT >= 32) && ((uintptr_t)p.out % 16 == 0) && ((p.ldo * sizeof(OT)) % 16 == 0) &&
                 ((p.stride_out * sizeof(OT)) % 16 == 0) && !(p.dbg & 512);
+    for (int r = 0; r < p.n_peers; ++r) p.tma_out = p.tma_out && ((uintptr_t)p.peers[r] % 16 == 0);
     if (p.tma_out) {
         uint64_t dims_o[3] = {(uint64_t)p.N, (uint64_t)p.M, L};
         uint64_t str_o[2] = {(uint64_t)(p.ldo * sizeof(OT)), (uint64_t)((L > 1 ? p.stride_out : p.ldo * p.M) * sizeof(OT))};
@@ -414,6 +431,12 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
         rc = make_tensor_map(&map_out, sizeof(OT) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (std::is_same<OT, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16),
                              3, p.out, dims_o, str_o, box_o, CU_TENSOR_MAP_SWIZZLE_NONE);
         if (rc) return rc;
+        for (int r = 0; r < p.n_peers; ++r) {          // one output map per tensor-parallel rank
+            rc = make_tensor_map(&peer_maps.m[r], sizeof(OT) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (std::is_same<OT, __half>::value ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16),
+                                 3, p.peers[r], dims_o, str_o, box_o, CU_TENSOR_MAP_SWIZZLE_NONE);
+            if (rc) return rc;
+        }
+        for (int r = p.n_peers; r < 8; ++r) peer_maps.m[r] = map_out;
     }
     auto kern = umma_ts_kernel<OT, BT, CL>;
     static bool configured = false;
@@ -437,7 +460,7 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
     attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = CL > 1 ? 1 : 0;
-    TB_CUDA(cudaLaunchKernelEx(&cfg, kern, map_act, map_pw, map_out, p));
+    TB_CUDA(cudaLaunchKernelEx(&cfg, kern, map_act, map_pw, map_out, peer_maps, p));
     TB_LAUNCH_CHECK();
     return TB200_OK;
 }

@@ -433,9 +433,10 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
                     if (p.n_peers == 0) {
                         out[(int64_t)tok * p.ldo + row] = yv;
                     } else {
-#pragma unroll 1
-                        for (int r = 0; r < p.n_peers; ++r)     // one small store per peer over NVLink (P2P-mapped memory)
-                            reinterpret_cast<OT*>(p.peers[r])[(int64_t)tok * p.ldo + row] = yv;
+#pragma unroll
+                        for (int r = 0; r < 8; ++r)             // one small store per peer over NVLink (P2P-mapped memory);
+                            if (r < p.n_peers)                  // constant indices keep the parameter block out of local memory
+                                reinterpret_cast<OT*>(p.peers[r])[(int64_t)tok * p.ldo + row] = yv;
                         wrote_peer = true;
                     }
                 }

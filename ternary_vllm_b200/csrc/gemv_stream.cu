@@ -42,6 +42,10 @@ struct StreamParams {
     const float* scale; const float* bias; int64_t stride_sb;
     void* out; int64_t ldo; int64_t stride_out; int out_dtype;
     int32_t* acc_out;
+    // tensor-parallel gather fused into the epilogue: when n_peers > 0 every [tokens x 16 rows] output tile is staged in
+    // shared memory and stored with ONE TMA tile store per rank into that rank's [layers, M, ldo] buffer (peer-mapped
+    // NVLink addresses; tensor maps in PeerMaps, already offset to this rank's column block; TMA clips rows >= N, tokens >= M)
+    int n_peers; uint32_t peer_stage_off;     // staging tiles of the aux warps, byte offset in dynamic shared memory
     int64_t N;
     int M, Mg, nks, row_blocks, layers;
     int stages, nslots, nimg;
@@ -70,9 +74,14 @@ __device__ __forceinline__ int img_vec(int sg, int pp, int i, int n, int t, int 
 // TEAMS = 2 (NG == 1 only): two teams of 4 MMA warps take alternate row blocks, every warp owning TWO 128-byte K
 // segments: the per-row-block work of a warp (barriers, recombination, slot hand-off) is amortised over twice the MMAs
 // and only four K-partials per output meet in shared memory.
-template <int NG, bool BREG, int TEAMS, int AUX>
+// PEER: tensor-parallel variant (fused gather); a separate instantiation so that the single-GPU kernel keeps its exact
+// code (the kernel is sensitive to the size of the aux warps' loop)
+struct NoPeerMaps { int unused; };
+template <bool PEER> struct PeerArg { using type = NoPeerMaps; };
+template <> struct PeerArg<true> { using type = PeerMaps; };
+template <int NG, bool BREG, int TEAMS, int AUX, bool PEER>
 __global__ void __launch_bounds__(sv_threads(AUX), 1)
-gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams p) {
+gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ typename PeerArg<PEER>::type pm, const StreamParams p) {
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
     uint8_t* gbase = smem_dyn + (base - smem_u32(smem_dyn));
@@ -460,6 +469,10 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
         }
         int sq_i = a % p.nslots; uint32_t spar = (uint32_t)(a / p.nslots) & 1u;     // AUX <= nslots: a / nslots == 0
         const bool store_acc = p.acc_out != nullptr;
+        if constexpr (PEER) {
+            if (lane == 0) for (int r = 0; r < p.n_peers; ++r) tma_prefetch_desc(&pm.m[r]);
+        }
+        [[maybe_unused]] int pcnt = 0;                   // staging tiles written by this warp (peer gather)
 #pragma unroll 1
         for (int sn0 = a; sn0 < my_groups; sn0 += SV_FIFO * AUX) {
 #pragma unroll
@@ -503,10 +516,12 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
             if (sq_i >= p.nslots) { sq_i -= p.nslots; spar ^= 1u; }
             // fragment: vv0 (row g, tok 2t), vv1 (row g, tok 2t+1), vv2 (row g+8, tok 2t), vv3 (row g+8, tok 2t+1)
             const int64_t obase = (int64_t)l * p.stride_out;
+            float yv[PEER ? NG : 1][4];
 #pragma unroll
             for (int q = 0; q < NG; ++q) {
 #pragma unroll
                 for (int e4 = 0; e4 < 4; ++e4) {
+                    if constexpr (PEER) yv[q][e4] = 0.0f;
                     const int e = e4 & 1, hi = e4 >> 1;
                     const int tok = 8 * q + 2 * t + e;
                     const int64_t row = hi ? row1 : row0;
@@ -516,14 +531,51 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const StreamParams
                         const float tv = __fmul_rn((float)av, sxv[q][e]);
                         const float y = epilogue(tv, hi ? sc1 : sc0, hi ? bi1 : bi0, p.clip_val);
                         const int64_t o = obase + (int64_t)tok * p.ldo + row;
-                        if (p.out_dtype == TB200_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(y);
-                        else if (p.out_dtype == TB200_F16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(y);
-                        else reinterpret_cast<float*>(p.out)[o] = y;
+                        if constexpr (!PEER) {
+                            if (p.out_dtype == TB200_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(y);
+                            else if (p.out_dtype == TB200_F16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(y);
+                            else reinterpret_cast<float*>(p.out)[o] = y;
+                        } else {
+                            yv[q][e4] = y;
+                        }
                     }
                 }
             }
+            if constexpr (PEER) {
+                // tile [8*NG tokens][16 rows] -> staging (two buffers per aux warp) -> one TMA store per rank
+                const uint32_t esz = p.out_dtype == TB200_F32 ? 4u : 2u;
+                const uint32_t stg = smem_u32(gbase) + p.peer_stage_off + (uint32_t)((a * 2 + (pcnt & 1)) * (NG * 8 * SV_ROWS)) * esz;
+                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");     // the stores that last read `stg` are done
+                __syncwarp();
+#pragma unroll
+                for (int q = 0; q < NG; ++q)
+#pragma unroll
+                    for (int e4 = 0; e4 < 4; ++e4) {
+                        const uint32_t el = (uint32_t)((8 * q + 2 * t + (e4 & 1)) * SV_ROWS + g + 8 * (e4 >> 1));
+                        if (p.out_dtype == TB200_F32) {
+                            asm volatile("st.shared.f32 [%0], %1;" ::"r"(stg + el * 4u), "f"(yv[q][e4]) : "memory");
+                        } else {
+                            unsigned short h;
+                            if (p.out_dtype == TB200_BF16) { const __nv_bfloat16 v = __float2bfloat16_rn(yv[q][e4]); h = *reinterpret_cast<const unsigned short*>(&v); }
+                            else { const __half v = __float2half_rn(yv[q][e4]); h = *reinterpret_cast<const unsigned short*>(&v); }
+                            asm volatile("st.shared.u16 [%0], %1;" ::"r"(stg + el * 2u), "h"(h) : "memory");
+                        }
+                    }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+#pragma unroll 1
+                    for (int r = 0; r < p.n_peers; ++r) tma_store_3d(&pm.m[r], stg, cp.rb * SV_ROWS, 0, l);
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+                ++pcnt;
+            }
             advance(cp);
           }
+        }
+        if (PEER && lane == 0) {
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // all tile stores of this warp have completed
+            __threadfence_system();
         }
     }
 }
@@ -645,13 +697,20 @@ static StreamGeom stream_geom(int64_t M, int64_t K) {
     gm.blob_stride = ((int64_t)gm.img_bytes + SV_TAIL + 255) / 256 * 256;
     return gm;
 }
-static size_t stream_smem(const StreamGeom& gm, int stages, int nslots, int nimg) {
+// byte offset (from the 1024-aligned base) of the peer staging tiles = end of the barrier block, 128-byte aligned
+static size_t stream_stage_off(const StreamGeom& gm, int stages, int nslots, int nimg) {
     const size_t img_pitch = ((size_t)gm.img_bytes + 127) & ~(size_t)127;
-    return 1024 + (size_t)stages * SV_TILE_BYTES + nimg * img_pitch + (size_t)nslots * gm.ng * 4096 +
-           (2 * SV_MAX_STAGES + 2 * SV_MAX_IMG + 2 * SV_MAX_SLOTS) * 8 + 64;
+    const size_t end = (size_t)stages * SV_TILE_BYTES + nimg * img_pitch + (size_t)nslots * gm.ng * 4096 +
+                       (2 * SV_MAX_STAGES + 2 * SV_MAX_IMG + 2 * SV_MAX_SLOTS) * 8;
+    return (end + 127) & ~(size_t)127;
+}
+// staging tiles of the tensor-parallel epilogue: up to 4 aux warps x 2 buffers x [8 * ng tokens][16 rows] x 4 bytes
+static size_t stream_stage_bytes(const StreamGeom& gm, bool peers) { return peers ? (size_t)4 * 2 * gm.ng * 8 * SV_ROWS * 4 : 0; }
+static size_t stream_smem(const StreamGeom& gm, int stages, int nslots, int nimg, bool peers = false) {
+    return 1024 + stream_stage_off(gm, stages, nslots, nimg) + stream_stage_bytes(gm, peers) + 64;
 }
 // ring depth first (bytes in flight), then a second image buffer, then more slots
-static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslots, int* nimg) {
+static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslots, int* nimg, bool peers = false) {
     const size_t limit = 227 * 1024;
     static const int st_env = getenv("TB200_STREAM_STAGES") ? atoi(getenv("TB200_STREAM_STAGES")) : 0;
     const int want_st = st_env > 0 ? st_env : 8;
@@ -659,7 +718,7 @@ static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslot
     for (int img = breg ? 1 : 2; img >= 1; --img)
         for (int st = want_st; st >= min_st; --st)
             for (int ns = (gm.ng > 2 ? 2 : gm.ng == 2 ? 4 : 8); ns >= (gm.ng == 1 ? 4 : 2); ns -= (gm.ng == 1 ? 4 : 2))   // multiples of the aux-warp count
-                if (stream_smem(gm, st, ns, img) <= limit) { *stages = st; *nslots = ns; *nimg = img; return true; }
+                if (stream_smem(gm, st, ns, img, peers) <= limit) { *stages = st; *nslots = ns; *nimg = img; return true; }
     return false;
 }
 
@@ -670,9 +729,9 @@ bool gemv_stream_fits(int64_t M, int64_t K) {
     return stream_pick(gm, gm.ng == 1 && gm.nks == 1, &a, &b2, &c);
 }
 
-template <int NG, bool BREG, int TEAMS, int AUX>
-static int launch_stream(const CUtensorMap& map, const StreamParams& p, size_t smem, int ctas, bool pdl, cudaStream_t s) {
-    auto kern = gemv_stream_kernel<NG, BREG, TEAMS, AUX>;
+template <int NG, bool BREG, int TEAMS, int AUX, bool PEER>
+static int launch_stream_v(const CUtensorMap& map, const typename PeerArg<PEER>::type& pm, const StreamParams& p, size_t smem, int ctas, bool pdl, cudaStream_t s) {
+    auto kern = gemv_stream_kernel<NG, BREG, TEAMS, AUX, PEER>;
     static size_t configured = 0;
     if (smem > configured) {
         TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -688,20 +747,28 @@ static int launch_stream(const CUtensorMap& map, const StreamParams& p, size_t s
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    TB_CUDA(cudaLaunchKernelEx(&cfg, kern, map, p));
+    TB_CUDA(cudaLaunchKernelEx(&cfg, kern, map, pm, p));
     TB_LAUNCH_CHECK();
     return TB200_OK;
+}
+
+template <int NG, bool BREG, int TEAMS, int AUX>
+static int launch_stream(const CUtensorMap& map, const PeerMaps* pm, const StreamParams& p, size_t smem, int ctas, bool pdl, cudaStream_t s) {
+    if (pm) return launch_stream_v<NG, BREG, TEAMS, AUX, true>(map, *pm, p, smem, ctas, pdl, s);
+    return launch_stream_v<NG, BREG, TEAMS, AUX, false>(map, NoPeerMaps{0}, p, smem, ctas, pdl, s);
 }
 
 int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
                      const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
                      const float* scale, const float* bias, int64_t stride_sb, float clip_val,
                      void* out, int out_dtype, int64_t ldo, int64_t stride_out,
-                     int32_t* acc_out, int layers, void* workspace, cudaStream_t s) {
+                     int32_t* acc_out, int layers, void* workspace, cudaStream_t s,
+                     void* const* peers = nullptr, int n_peers = 0) {
     const StreamGeom gm = stream_geom(M, K);
     const bool breg = gm.ng == 1 && gm.nks == 1;
     StreamParams p = {};
-    if (!stream_pick(gm, breg, &p.stages, &p.nslots, &p.nimg)) {
+    const bool tp = peers && n_peers > 0;
+    if (!stream_pick(gm, breg, &p.stages, &p.nslots, &p.nimg, tp)) {
         set_error("gemv_stream: M=%lld K=%lld does not fit the shared-memory activation image", (long long)M, (long long)K);
         return TB200_ENOTSUP;
     }
@@ -733,6 +800,31 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     p.scale = scale; p.bias = bias; p.stride_sb = stride_sb;
     p.out = out; p.ldo = ldo; p.stride_out = stride_out; p.out_dtype = out_dtype;
     p.acc_out = acc_out;
+    PeerMaps peer_maps;
+    const PeerMaps* pm = nullptr;
+    p.n_peers = 0;
+    if (tp) {
+        // one output tensor map per rank: [layers][M][N] elements at (stride_out, ldo) pitches, box = 8 * ng tokens x 16 rows
+        const size_t os = dtype_size(out_dtype);
+        if ((ldo * os) % 16 || (stride_out * os) % 16) {
+            set_error("gemv_stream_tp: ldo and stride_out must be multiples of 16 bytes");
+            return TB200_EINVAL;
+        }
+        const CUtensorMapDataType dt = out_dtype == TB200_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                     : out_dtype == TB200_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+        uint64_t dims_o[3] = {(uint64_t)N, (uint64_t)M, (uint64_t)layers};
+        uint64_t str_o[2] = {(uint64_t)(ldo * os), (uint64_t)((layers > 1 ? stride_out : ldo * M) * os)};
+        uint32_t box_o[3] = {SV_ROWS, (uint32_t)(8 * gm.ng), 1};
+        for (int r = 0; r < n_peers; ++r) {
+            if ((uintptr_t)peers[r] % 16) { set_error("gemv_stream_tp: peer pointer %d is not 16-byte aligned", r); return TB200_EINVAL; }
+            int rc2 = make_tensor_map(&peer_maps.m[r], dt, 3, peers[r], dims_o, str_o, box_o, CU_TENSOR_MAP_SWIZZLE_NONE);
+            if (rc2) return rc2;
+        }
+        for (int r = n_peers; r < 8; ++r) peer_maps.m[r] = peer_maps.m[0];
+        pm = &peer_maps;
+        p.n_peers = n_peers;
+        p.peer_stage_off = (uint32_t)stream_stage_off(gm, p.stages, p.nslots, p.nimg);
+    }
     p.N = N; p.M = (int)M; p.Mg = gm.Mg; p.nks = gm.nks;
     p.row_blocks = (int)((N + SV_ROWS - 1) / SV_ROWS);
     p.layers = layers;
@@ -743,17 +835,17 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     p.dbg = dbg_env;
     const int64_t total = (int64_t)p.row_blocks * layers;
     const int ctas = (int)(total < sm_count() ? total : sm_count());
-    const size_t smem = stream_smem(gm, p.stages, p.nslots, p.nimg);
+    const size_t smem = stream_smem(gm, p.stages, p.nslots, p.nimg, tp);
     switch (gm.ng) {
         case 1: {
             static const int teams = getenv("TB200_STREAM_TEAMS") ? atoi(getenv("TB200_STREAM_TEAMS")) : 2;
             if (teams == 2)
-                return breg ? launch_stream<1, true, 2, 2>(map, p, smem, ctas, true, s) : launch_stream<1, false, 2, 2>(map, p, smem, ctas, true, s);
-            return breg ? launch_stream<1, true, 1, 4>(map, p, smem, ctas, true, s) : launch_stream<1, false, 1, 4>(map, p, smem, ctas, true, s);
+                return breg ? launch_stream<1, true, 2, 2>(map, pm, p, smem, ctas, true, s) : launch_stream<1, false, 2, 2>(map, pm, p, smem, ctas, true, s);
+            return breg ? launch_stream<1, true, 1, 4>(map, pm, p, smem, ctas, true, s) : launch_stream<1, false, 1, 4>(map, pm, p, smem, ctas, true, s);
         }
-        case 2: return launch_stream<2, false, 1, 2>(map, p, smem, ctas, true, s);
-        case 3: return launch_stream<3, false, 1, 2>(map, p, smem, ctas, true, s);
-        default: return launch_stream<4, false, 1, 2>(map, p, smem, ctas, true, s);
+        case 2: return launch_stream<2, false, 1, 2>(map, pm, p, smem, ctas, true, s);
+        case 3: return launch_stream<3, false, 1, 2>(map, pm, p, smem, ctas, true, s);
+        default: return launch_stream<4, false, 1, 2>(map, pm, p, smem, ctas, true, s);
     }
 }
 
@@ -783,7 +875,8 @@ static int stream_umma(const void* x, int x_dtype, int64_t M, int64_t K, int64_t
                        const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
                        const float* scale, const float* bias, int64_t stride_sb, float clip_val,
                        void* out, int out_dtype, int64_t ldo, int64_t stride_out,
-                       int32_t* acc_out, int layers, void* workspace, cudaStream_t s) {
+                       int32_t* acc_out, int layers, void* workspace, cudaStream_t s,
+                       void* const* peers = nullptr, int n_peers = 0) {
     const int64_t ldq = ru(K, 16), rows = M * layers;
     char* w = (char*)workspace;
     int8_t* q_x = (int8_t*)w;      w += ru(rows * ldq, 256);
@@ -805,15 +898,18 @@ static int stream_umma(const void* x, int x_dtype, int64_t M, int64_t K, int64_t
     p.out = out; p.ldo = ldo; p.acc_out = acc_out;
     p.M = M; p.N = N; p.K = K; p.clip_val = fabsf(clip_val);
     p.layers = layers; p.stride_act_rows = M; p.stride_sb = stride_sb; p.stride_out = stride_out;
+    p.n_peers = peers ? n_peers : 0;
+    for (int r = 0; r < p.n_peers; ++r) p.peers[r] = peers[r];
     { const char* e = getenv("TB200_GEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
     return gemm_ts_launch(q_x, ldq, packed, ld_packed, p, out_dtype, s, M, stride_packed);
 }
 
-extern "C" int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
-                                 const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
-                                 const float* scale, const float* bias, int64_t stride_sb, float clip_val,
-                                 void* out, int out_dtype, int64_t ldo, int64_t stride_out,
-                                 int count, int32_t* acc_out, void* workspace, void* stream) {
+static int gemv_stream_entry(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                             const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                             const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                             void* out, int out_dtype, int64_t ldo, int64_t stride_out,
+                             int count, int32_t* acc_out, void* workspace, void* stream,
+                             void* const* peers, int n_peers) {
     TB_DEVICE_OR_RETURN();
     if (M == 0 || N == 0 || count == 0) return TB200_OK;
     TB_REQUIRE(x && packed && out && workspace, "gemv_stream: null pointer");
@@ -828,9 +924,36 @@ extern "C" int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t 
     TB_REQUIRE(count >= 1 && count <= 65535, "gemv_stream: bad layer count %d", count);
     if (M >= stream_umma_min_m())
         return stream_umma(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N, scale, bias, stride_sb,
-                           clip_val, out, out_dtype, ldo, stride_out, acc_out, count, workspace, (cudaStream_t)stream);
+                           clip_val, out, out_dtype, ldo, stride_out, acc_out, count, workspace, (cudaStream_t)stream, peers, n_peers);
     return gemv_stream_impl(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N, scale, bias, stride_sb,
-                            clip_val, out, out_dtype, ldo, stride_out, acc_out, count, workspace, (cudaStream_t)stream);
+                            clip_val, out, out_dtype, ldo, stride_out, acc_out, count, workspace, (cudaStream_t)stream, peers, n_peers);
+}
+
+extern "C" int tb200_gemv_stream(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                                 const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N,
+                                 const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                                 void* out, int out_dtype, int64_t ldo, int64_t stride_out,
+                                 int count, int32_t* acc_out, void* workspace, void* stream) {
+    return gemv_stream_entry(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N, scale, bias, stride_sb,
+                             clip_val, out, out_dtype, ldo, stride_out, count, acc_out, workspace, stream, nullptr, 0);
+}
+
+// Tensor-parallel form: this rank's row block (N_local rows) of every layer in the list; the epilogues store each
+// output element into EVERY rank's [count, M, ldo] buffer through peer-mapped (NVLink) pointers, so the all-gather of
+// the whole list costs no extra pass: ONE cross-rank barrier by the caller after the call makes all layers consumable.
+extern "C" int tb200_gemv_stream_tp(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                                    const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N_local,
+                                    const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                                    void* const* out_peers, int n_peers, int out_dtype, int64_t ldo, int64_t stride_out,
+                                    int count, void* workspace, void* stream) {
+    if (!(out_peers && n_peers >= 1 && n_peers <= 8)) {
+        set_error("gemv_stream_tp: bad peer list (n_peers=%d, 1..8 supported)", n_peers);
+        return TB200_EINVAL;
+    }
+    for (int r = 0; r < n_peers; ++r)
+        if (!out_peers[r]) { set_error("gemv_stream_tp: null peer pointer %d", r); return TB200_EINVAL; }
+    return gemv_stream_entry(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N_local, scale, bias, stride_sb,
+                             clip_val, out_peers[0], out_dtype, ldo, stride_out, count, nullptr, workspace, stream, out_peers, n_peers);
 }
 
 // End-to-end with HOST activations / outputs for a list of layers (weights resident on the device): one H2D copy of

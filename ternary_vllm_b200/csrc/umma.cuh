@@ -114,6 +114,7 @@ struct UmmaParams {
     int64_t stride_act_rows;          // s_x / sum_qx elements per layer (= M)
     int64_t stride_sb;                // scale / bias elements per layer
     int64_t stride_out;               // out elements per layer
+    void* peers[8]; int n_peers;      // tensor-parallel gather: store every element into each rank's buffer (see gemv.cu)
     int dbg;          // TB200_GEMM_DBG experiments: 1 skip the epilogue body, 2 skip the expansion, 4 skip the MMAs
 };
 

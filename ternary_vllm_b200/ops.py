@@ -325,5 +325,36 @@ def gemv_stream(xs, packed, scale, bias, clip_val, out=None, out_dtype=None, deb
     return (out, acc) if debug else out
 
 
+def gemv_stream_tp(xs, packed, scale, bias, clip_val, peer_ptrs, n_peers: int, out_dtype, ldo: int, stride_out: int,
+                   workspace=None):
+    """Tensor-parallel ``gemv_stream`` (``tb200_gemv_stream_tp``): ``packed [R, N_local, ld]`` is this rank's row block
+    of every layer; the epilogues store the rank's ``[R, M, N_local]`` outputs into every rank's ``[R, M, ldo]`` buffer.
+    ``peer_ptrs``: ctypes array of ``n_peers`` addresses, each already offset to this rank's first column.  The
+    caller issues the cross-rank barrier."""
+    _cuda(xs, packed, scale, bias)
+    assert packed.dim() == 3 and packed.dtype == torch.uint8 and packed.stride(2) == 1
+    R, N, _ = packed.shape
+    shared_x = xs.dim() == 2
+    assert xs.stride(-1) == 1
+    M, K = xs.shape[-2], xs.shape[-1]
+    if scale is not None:
+        assert scale.dtype == torch.float32 and scale.shape == (R, N) and scale.stride(1) == 1
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.shape == (R, N) and bias.stride(1) == 1
+    stride_sb = scale.stride(0) if scale is not None else (bias.stride(0) if bias is not None else 0)
+    if scale is not None and bias is not None:
+        assert scale.stride(0) == bias.stride(0)
+    need = L.lib().tb200_gemv_stream_workspace(M, K, R)
+    if workspace is None:
+        workspace = torch.empty((need,), dtype=torch.uint8, device=xs.device)
+    assert workspace.numel() >= need
+    with torch.cuda.device(xs.device):
+        L.check(L.lib().tb200_gemv_stream_tp(xs.data_ptr(), _dt(xs), M, K, xs.stride(-2), 0 if shared_x else xs.stride(0),
+                                             packed.data_ptr(), packed.stride(1), packed.stride(0), N,
+                                             _ptr(scale), _ptr(bias), stride_sb, float(clip_val),
+                                             peer_ptrs, n_peers, _DT[out_dtype], ldo, stride_out, R,
+                                             workspace.data_ptr(), _stream(xs)), "gemv_stream_tp")
+
+
 def launch_count() -> int:
     return int(L.lib().tb200_launch_count())

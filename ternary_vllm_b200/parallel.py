@@ -134,3 +134,58 @@ class TPShardedLinear(nn.Module):
         else:
             y = self.gather(self.local_forward(x2))
         return y.reshape(*x.shape[:-1], self.out_features)
+
+
+class TPShardedStream(nn.Module):
+    """A LIST of R independent layers of one shape (fused QKV / gate+up projections, experts, the layers of a batch
+    of models), N-sharded: this rank holds rows [start, stop) of every layer.  ``forward(xs)`` runs ONE
+    ``tb200_gemv_stream_tp`` over the rank's shards of all layers, whose epilogues store every output element into
+    every rank's ``[R, M, world*n_shard]`` buffer over NVLink peer memory, then ONE cross-rank barrier for the whole
+    list, and returns the full ``[R, M, N]`` outputs on every rank.  Decode shapes only (M <= 32)."""
+
+    def __init__(self, packed_shards: torch.Tensor, scale_shards, bias_shards, in_features: int, out_features: int,
+                 maxval: float, group=None, max_tokens: int = 32, dtype=torch.bfloat16):
+        super().__init__()
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.in_features, self.out_features, self.maxval = in_features, out_features, maxval
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.n_shard = shard_size(out_features, self.world)
+        self.start, self.stop = shard_rows(out_features, self.world, self.rank)
+        assert packed_shards.dim() == 3 and packed_shards.shape[1] == self.stop - self.start
+        self.register_buffer("packed", packed_shards)
+        self.register_buffer("scale", scale_shards)
+        self.register_buffer("bias", bias_shards)
+        R, dev = packed_shards.shape[0], packed_shards.device
+        self.ld = self.world * self.n_shard
+        self.max_tokens, self.dtype = max_tokens, dtype
+        esz = torch.empty((), dtype=dtype).element_size()
+        grp = group if group is not None else dist.group.WORLD
+        self._bufs, self._hdls, self._ptrs = [], [], []
+        for _ in range(2):                                   # alternate per call (see TPShardedLinear.enable_peer_gather)
+            buf = symm_mem.empty((R, max_tokens, self.ld), dtype=dtype, device=dev)
+            hdl = symm_mem.rendezvous(buf, grp)
+            self._bufs.append(buf)
+            self._hdls.append(hdl)
+            self._ptrs.append((ctypes.c_void_p * self.world)(*[int(hdl.buffer_ptrs[r]) + self.rank * self.n_shard * esz
+                                                               for r in range(self.world)]))
+        self._turn = 0
+        self._ws = None
+
+    def forward(self, xs: torch.Tensor, barrier: bool = True) -> torch.Tensor:
+        M, K = xs.shape[-2], xs.shape[-1]
+        assert M <= self.max_tokens and K == self.in_features
+        i = self._turn
+        self._turn ^= 1
+        R = self.packed.shape[0]
+        need = L.lib().tb200_gemv_stream_workspace(M, K, R)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty((need,), dtype=torch.uint8, device=xs.device)
+        if self.stop > self.start:
+            ops.gemv_stream_tp(xs, self.packed, self.scale, self.bias, self.maxval, self._ptrs[i], self.world, self.dtype,
+                               self.ld, self.max_tokens * self.ld, workspace=self._ws)
+        if barrier:
+            self._hdls[i].barrier(channel=0)             # every rank's blocks of every layer have landed in every buffer
+        return self._bufs[i][:, :M, : self.out_features]

@@ -90,3 +90,32 @@ def test_stream_repeated_calls_share_workspace(cuda):
     torch.cuda.synchronize()
     for xi, oi in zip(xs, outs):
         assert torch.equal(oi, ops.gemv_stream(xi, packed, sd, bd, 100.0))
+
+
+@pytest.mark.parametrize("M", [1, 8, 19, 32])
+@pytest.mark.parametrize("R,N,K,world", [(3, 400, 1024, 4), (2, 1376, 4096, 8), (2, 100, 5000, 2)])
+def test_stream_tp_peer_stores(cuda, M, R, N, K, world):
+    """tb200_gemv_stream_tp on ONE device: every 'rank' runs its row block of all layers and stores it into `world`
+    local stand-ins for the peer buffers; each buffer must end up bit-identical to the unsharded tb200_gemv_stream
+    output (the peer-store epilogues of both the mma.sync and the tcgen05 kernel, column offsets, ragged last shard)."""
+    import ctypes
+
+    from ternary_vllm_b200.parallel import shard_rows, shard_size
+
+    Ws, x, scale, bias = make_layers(R, N, K, M, seed=M + N + K + R + world)
+    packed = torch.stack([ops.quantize_pack(W.to(cuda), "ternary") for W in Ws])
+    xd, sd, bd = x.to(cuda), scale.to(cuda), bias.to(cuda)
+    want = ops.gemv_stream(xd, packed, sd, bd, 100.0)
+    n_shard = shard_size(N, world)
+    ld = world * n_shard
+    bufs = [torch.full((R, M, ld), float("nan"), dtype=torch.bfloat16, device=cuda) for _ in range(world)]
+    for rank in range(world):
+        a, b = shard_rows(N, world, rank)
+        if b <= a:
+            continue
+        ptrs = (ctypes.c_void_p * world)(*[buf.data_ptr() + rank * n_shard * 2 for buf in bufs])
+        ops.gemv_stream_tp(xd, packed[:, a:b].contiguous(), sd[:, a:b].contiguous(), bd[:, a:b].contiguous(), 100.0,
+                           ptrs, world, torch.bfloat16, ld, M * ld)
+    torch.cuda.synchronize()
+    for buf in bufs:
+        assert torch.equal(buf[:, :, :N], want)

@@ -43,6 +43,26 @@ for (K, N) in ((4096, 11008), (11008, 4096), (1024, 1000)):
             for _ in range(50): mod(x)
             torch.cuda.synchronize(); dt = (time.perf_counter() - t0) / 50
         if rank == 0: print(f"   {name:18s} M=1: {dt*1e6:7.1f} us per layer call (eager, host-inclusive)")
+# list form: TPShardedStream (one tb200_gemv_stream_tp call + one barrier for R layers) vs the unsharded tb200_gemv_stream
+from ternary_vllm_b200 import ops
+from ternary_vllm_b200.parallel import TPShardedStream, shard_rows
+for (K, N, R) in ((4096, 11008, 5), (1024, 1000, 3), (11008, 4096, 2)):
+    g = torch.Generator(device=dev).manual_seed(K + N + R)      # the same full layers on every rank
+    packed = torch.stack([ops.quantize_pack(torch.randn(N, K, generator=g, device=dev).clip_(-1, 1), "ternary") for _ in range(R)])
+    scale = torch.rand(R, N, generator=g, device=dev) / K ** 0.5
+    bias = torch.randn(R, N, generator=g, device=dev)
+    a, b = shard_rows(N, world, rank)
+    tps = TPShardedStream(packed[:, a:b].contiguous(), scale[:, a:b].contiguous(), bias[:, a:b].contiguous(), K, N, 100.0)
+    for M in (1, 8, 32):
+        xs = torch.randn(R, M, K, generator=g, device=dev, dtype=torch.bfloat16)
+        want = ops.gemv_stream(xs, packed, scale, bias, 100.0)
+        y1 = tps(xs).clone()
+        y2 = tps(xs).clone()
+        torch.cuda.synchronize()
+        good = torch.equal(want, y1) and torch.equal(want, y2)
+        ok = ok and good
+        if rank == 0:
+            print(f"stream K={K} N={N} R={R} M={M}: {good}")
 t = torch.tensor([1 if ok else 0], device=dev)
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
 if rank == 0: print("TP CHECK", "PASS" if t.item() == 1 else "FAIL")
