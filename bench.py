@@ -18,7 +18,8 @@ Extra keys: the tcgen05 prefill GEMM (configs[2]) in TOPS, ViT-L shapes (configs
 
 N>1 (torchrun -> bench_tp.py): the same sweep with every layer N-sharded across the ranks (configs[4]'s
 tensor parallelism), the all-gather fused into the GEMV epilogues over NVLink peer memory + one barrier per
-call (strong scaling: the same full layers on more GPUs); configs[4]'s other projections in `tp_cases`.
+call (weak scaling: the ring of full layers grows with the ranks so that every rank's shards stay larger than
+its L2); configs[4]'s other projections in `tp_cases`.
 """
 import argparse
 import json
@@ -159,7 +160,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak" if args.gpus == 1 else "strong", "vs_baseline": None,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": CONFIG_N1 if args.gpus == 1 else CONFIG_TP,
         "cpu_baseline": {"value": val, "unit": "GB/s", "cores": cores, "kind": "port",
                          "sample": "one layer per sweep case per step (6 forwards of configs[1]), oracle port of "
@@ -178,7 +179,8 @@ CONFIG_N1 = {"workload": "configs[1] decode GEMV sweep: ternary Linear 4096x4096
              "api": "tb200_gemv_stream: one call per sweep case over its ring of layers"}
 CONFIG_TP = {"workload": "configs[1] decode GEMV sweep (4096x4096, 4096x11008, batch 1/8/32, the N=1 rings) with every layer "
                          "N-sharded across the ranks as in configs[4]; configs[4]'s 11008x4096 and 4096x32000 in tp_cases",
-             "l2_policy": "inputs larger than L2 (rings of 67 / 64 distinct full layers, every layer read once per step)",
+             "l2_policy": "inputs larger than L2 on every rank (rings of 67 x ranks / 64 x ranks distinct full layers: each rank "
+                          "streams the same 281 / 721 MB of packed shards per case as the single GPU does, every layer read once per step)",
              "api": "tb200_gemv_stream_tp: one call per sweep case over the rank's row blocks of the ring + one barrier"}
 
 

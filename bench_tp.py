@@ -1,11 +1,13 @@
 """bench_tp.py — the N>1 arm of bench.py (launched under torchrun, one rank per GPU).
 
 Headline (`value`): the SAME decode sweep as the N=1 arm (BASELINE.json configs[1]: 4096x4096 and 4096x11008 at
-batch 1/8/32 over rings of 67/64 distinct layers), every layer N-sharded across the ranks
-(ternary_vllm_b200.parallel.shard_rows).  Per case ONE tb200_gemv_stream_tp call per rank over its row blocks of the
+batch 1/8/32), every layer N-sharded across the ranks (ternary_vllm_b200.parallel.shard_rows), over rings of
+67 x N / 64 x N distinct layers: the ring grows with the number of ranks so that each rank's shards of it (the same
+281 / 721 MB of packed weights as at N=1) stay larger than its L2 and are streamed from HBM.  Per case ONE tb200_gemv_stream_tp call per rank over its row blocks of the
 whole ring, whose epilogues store the outputs into every rank's buffer over NVLink peer memory (the all-gather fused
-into the kernel), then ONE cross-rank barrier.  STRONG scaling: the same full layers on more GPUs, so
-`value` = algorithmic bytes of the full layers / max-over-ranks device time, directly comparable with the N=1 line.
+into the kernel), then ONE cross-rank barrier.  WEAK scaling: per-GPU bytes are fixed, the layers are the same full
+layers; `value` = algorithmic bytes of the full layers of the step / max-over-ranks device time, directly comparable
+with the N=1 line.
 
 `tp_cases` adds configs[4]'s other projections (11008x4096, 4096x32000 lm_head) in the same form; `chain` is the
 sequential-layers form (one TPShardedLinear call + one barrier PER LAYER, latency-bound) with its NCCL all-gather
@@ -49,7 +51,9 @@ def run_tp(args, metric):
 
     streams, ring_len = {}, {}
     for (K, N) in SHAPES + TP_EXTRA_SHAPES:
-        R = max(RING_MIN if (K, N) in SHAPES else 24, int(math.ceil(2.2 * L2_BYTES / (N * K / 4))))   # same rings as N=1
+        # the N=1 ring length x world: every rank's SHARDS of the ring stay larger than its own L2 (the timing rule) and
+        # the packed bytes a GPU streams per step are the same at every N -> weak scaling
+        R = world * max(RING_MIN if (K, N) in SHAPES else 24, int(math.ceil(2.2 * L2_BYTES / (N * K / 4))))
         ring_len[(K, N)] = R
         streams[(K, N)] = build_stream(K, N, R)
     cases = [(K, N, M) for (K, N) in SHAPES for M in BATCHES]
@@ -194,7 +198,7 @@ def run_tp(args, metric):
     if rank == 0:
         line = {
             "metric": metric, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int8 (u8 codes x s8 activations, s32 accumulate)", "data": "synthetic",
             "config": dict(CONFIG_TP, parallelism=f"tp{world} (N-sharded, all-gather fused into the GEMV epilogues)"),
             "tokens_per_s": step_tokens * args.steps / (ms * 1e-3), "clocks": clocks,

@@ -387,7 +387,6 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         }
     }
 
-    if (p.n_peers > 0) __threadfence_system();      // peer stores are visible system-wide before the grid completes
     tc_fence_before();
     __syncthreads();
     if (CL > 1) {   // no CTA may exit while a peer can still multicast into its shared memory or arrive on its barriers

@@ -34,7 +34,8 @@ constexpr int SV_MMA_WARPS = 8;
 constexpr int sv_threads(int aux) { return (8 + 2 + aux) * 32; }
 constexpr int SV_MAX_STAGES = 12;
 constexpr int SV_MAX_SLOTS = 8;
-constexpr int SV_MAX_IMG = 2;
+constexpr int SV_MAX_IMG = 4;
+constexpr int SV_PEER_BUFS = 4;     // staging tiles per aux warp (tensor-parallel epilogue)
 constexpr int SV_TAIL = 256;           // blob tail: s_x[32] f32 | sum_qx[32] i32
 
 struct StreamParams {
@@ -544,8 +545,10 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
             if constexpr (PEER) {
                 // tile [8*NG tokens][16 rows] -> staging (two buffers per aux warp) -> one TMA store per rank
                 const uint32_t esz = p.out_dtype == TB200_F32 ? 4u : 2u;
-                const uint32_t stg = smem_u32(gbase) + p.peer_stage_off + (uint32_t)((a * 2 + (pcnt & 1)) * (NG * 8 * SV_ROWS)) * esz;
-                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");     // the stores that last read `stg` are done
+                const uint32_t stg = smem_u32(gbase) + p.peer_stage_off + (uint32_t)((a * SV_PEER_BUFS + (pcnt & (SV_PEER_BUFS - 1))) * (NG * 8 * SV_ROWS)) * esz;
+                // the stores that last read `stg` are done (a tile store queues behind the weight tiles in flight, so
+                // several staging buffers per warp are needed to keep the warp from waiting for it)
+                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(SV_PEER_BUFS - 1) : "memory");
                 __syncwarp();
 #pragma unroll
                 for (int q = 0; q < NG; ++q)
@@ -574,8 +577,8 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
           }
         }
         if (PEER && lane == 0) {
-            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // all tile stores of this warp have completed
-            __threadfence_system();
+            // all tile stores of this warp have completed; grid completion orders them before the caller's barrier kernel
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
         }
     }
 }
@@ -704,21 +707,28 @@ static size_t stream_stage_off(const StreamGeom& gm, int stages, int nslots, int
                        (2 * SV_MAX_STAGES + 2 * SV_MAX_IMG + 2 * SV_MAX_SLOTS) * 8;
     return (end + 127) & ~(size_t)127;
 }
-// staging tiles of the tensor-parallel epilogue: up to 4 aux warps x 2 buffers x [8 * ng tokens][16 rows] x 4 bytes
-static size_t stream_stage_bytes(const StreamGeom& gm, bool peers) { return peers ? (size_t)4 * 2 * gm.ng * 8 * SV_ROWS * 4 : 0; }
-static size_t stream_smem(const StreamGeom& gm, int stages, int nslots, int nimg, bool peers = false) {
-    return 1024 + stream_stage_off(gm, stages, nslots, nimg) + stream_stage_bytes(gm, peers) + 64;
+// staging tiles of the tensor-parallel epilogue: aux warps x SV_PEER_BUFS buffers x [8 * ng tokens][16 rows] x element size
+static size_t stream_stage_bytes(const StreamGeom& gm, bool peers, int aux, size_t esz) { return peers ? (size_t)aux * SV_PEER_BUFS * gm.ng * 8 * SV_ROWS * esz : 0; }
+static size_t stream_smem(const StreamGeom& gm, int stages, int nslots, int nimg, size_t peer_esz = 0) {
+    static const int teams = getenv("TB200_STREAM_TEAMS") ? atoi(getenv("TB200_STREAM_TEAMS")) : 2;
+    const int aux = (gm.ng == 1 && teams != 2) ? 4 : 2;         // as dispatched in gemv_stream_impl
+    return 1024 + stream_stage_off(gm, stages, nslots, nimg) + stream_stage_bytes(gm, peer_esz > 0, aux, peer_esz) + 64;
 }
 // ring depth first (bytes in flight), then a second image buffer, then more slots
-static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslots, int* nimg, bool peers = false) {
+static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslots, int* nimg, size_t peer_esz = 0) {
     const size_t limit = 227 * 1024;
     static const int st_env = getenv("TB200_STREAM_STAGES") ? atoi(getenv("TB200_STREAM_STAGES")) : 0;
     const int want_st = st_env > 0 ? st_env : 8;
     const int min_st = gm.nks < 3 ? 3 : (gm.nks < SV_MAX_STAGES ? gm.nks : SV_MAX_STAGES);
-    for (int img = breg ? 1 : 2; img >= 1; --img)
+    // images: with the B fragments in registers (breg) a buffer is free again as soon as the layer's fragments are loaded,
+    // but the NEXT layer's image must already be in flight then (its load queues behind the weight ring), so small
+    // images get up to four buffers
+    static const int img_env = getenv("TB200_STREAM_NIMG") ? atoi(getenv("TB200_STREAM_NIMG")) : 0;
+    const int want_img = img_env > 0 ? (img_env > SV_MAX_IMG ? SV_MAX_IMG : img_env) : (breg ? (gm.img_bytes <= 16384 ? 4 : 2) : 2);
+    for (int img = want_img; img >= 1; --img)
         for (int st = want_st; st >= min_st; --st)
             for (int ns = (gm.ng > 2 ? 2 : gm.ng == 2 ? 4 : 8); ns >= (gm.ng == 1 ? 4 : 2); ns -= (gm.ng == 1 ? 4 : 2))   // multiples of the aux-warp count
-                if (stream_smem(gm, st, ns, img, peers) <= limit) { *stages = st; *nslots = ns; *nimg = img; return true; }
+                if (stream_smem(gm, st, ns, img, peer_esz) <= limit) { *stages = st; *nslots = ns; *nimg = img; return true; }
     return false;
 }
 
@@ -768,7 +778,8 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     const bool breg = gm.ng == 1 && gm.nks == 1;
     StreamParams p = {};
     const bool tp = peers && n_peers > 0;
-    if (!stream_pick(gm, breg, &p.stages, &p.nslots, &p.nimg, tp)) {
+    const size_t peer_esz = tp ? dtype_size(out_dtype) : 0;
+    if (!stream_pick(gm, breg, &p.stages, &p.nslots, &p.nimg, peer_esz)) {
         set_error("gemv_stream: M=%lld K=%lld does not fit the shared-memory activation image", (long long)M, (long long)K);
         return TB200_ENOTSUP;
     }
@@ -835,7 +846,7 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     p.dbg = dbg_env;
     const int64_t total = (int64_t)p.row_blocks * layers;
     const int ctas = (int)(total < sm_count() ? total : sm_count());
-    const size_t smem = stream_smem(gm, p.stages, p.nslots, p.nimg, tp);
+    const size_t smem = stream_smem(gm, p.stages, p.nslots, p.nimg, peer_esz);
     switch (gm.ng) {
         case 1: {
             static const int teams = getenv("TB200_STREAM_TEAMS") ? atoi(getenv("TB200_STREAM_TEAMS")) : 2;
