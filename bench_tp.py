@@ -177,14 +177,15 @@ def run_tp(args, metric):
 
     # end to end: pinned host activations in, full gathered outputs back to pinned host memory, per case
     hx = {c: torch.randn(ring_len[c[:2]], c[2], c[0], dtype=torch.bfloat16).pin_memory() for c in cases}
-    hy = {c: torch.empty(ring_len[c[:2]], c[2], c[1], dtype=torch.bfloat16).pin_memory() for c in cases}
+    hy = {c: torch.empty(ring_len[c[:2]], c[2], c[1], dtype=torch.bfloat16).pin_memory() for c in cases} if rank == 0 else {}
     dx = {c: torch.empty_like(xs[c]) for c in cases}
 
     def step_e2e():
         for c in cases:
             dx[c].copy_(hx[c], non_blocking=True)
             y = streams[c[:2]](dx[c])
-            hy[c].copy_(y, non_blocking=True)
+            if rank == 0:                       # the caller reads the gathered result once, on rank 0
+                hy[c].copy_(y, non_blocking=True)
         torch.cuda.synchronize()
 
     step_e2e()
@@ -192,7 +193,7 @@ def run_tp(args, metric):
     ms_e2e = timed(step_e2e, e2e_steps) / e2e_steps
     step_bytes = sum(algorithmic_bytes(*c) * ring_len[c[:2]] for c in cases)
     h2d = sum(hx[c].numel() * 2 for c in cases)
-    d2h = sum(hy[c].numel() * 2 for c in cases)
+    d2h = sum(ring_len[c[:2]] * c[2] * c[1] * 2 for c in cases)
     step_tokens = sum(c[2] * ring_len[c[:2]] for c in cases)
     value = step_bytes * args.steps / (ms * 1e-3) / 1e9
     if rank == 0:
@@ -209,8 +210,8 @@ def run_tp(args, metric):
                       "memory + ONE symmetric-memory barrier per call (a call = one sweep case over its ring of layers)",
             "e2e": {"value": step_bytes / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
-                    "api": "TPShardedStream.forward per sweep case on pinned host activations (every rank copies x in and "
-                           "the full gathered output back to pinned host memory)"},
+                    "api": "TPShardedStream.forward per sweep case on pinned host activations (every rank copies x in; "
+                           "rank 0 copies the full gathered output back to pinned host memory)"},
             "cases": per_case, "tp_cases": tp_cases, "chain": chain,
             "roofline": {"bound": "hbm", "achieved": value, "peak": pk["hbm_gbs"] * world, "unit": "GB/s",
                          "frac": value / (pk["hbm_gbs"] * world), "traffic": None, "peak_source": pk["source"],
