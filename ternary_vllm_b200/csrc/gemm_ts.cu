@@ -126,6 +126,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         // ===================== TMA producer =====================
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;
+            if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");     // the quantised activations are complete
             for (int t = cluster_id; t < total_tiles; t += num_clusters) {
                 const int layer = t / tiles_per_layer, tl = t - layer * tiles_per_layer;
                 const int n_group = tl / p.m_tiles, m_tile = tl - n_group * p.m_tiles;
@@ -134,6 +135,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     mbar_wait(bar_done(s), ph ^ 1u);
                     mbar_arrive_expect_tx(bar_pfull(s), TS_P_BYTES);
                     tma_load_3d(sP + s * TS_P_BYTES, &map_pw, bar_pfull(s), kb * (TS_BK / 4), n_tile * TS_ROWS, layer);
+                    if (p.dbg & 8) { mbar_arrive(bar_ready(s)); if (++s == NS) { s = 0; ph ^= 1u; } continue; }   // experiment: no activation traffic
                     mbar_arrive_expect_tx(bar_ready(s), Cfg::B_BYTES);
 #pragma unroll
                     for (int j = 0; j < TS_KS; ++j) {
@@ -225,6 +227,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         const int et = threadIdx.x - 128;
         OT* out_base = reinterpret_cast<OT*>(p.out);
         int it = 0, chunk_no = 0;
+        if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");         // s_x / sum_qx come from the quantiser
         if (et == 0 && p.tma_out) {
             tma_prefetch_desc(&map_out);
             for (int r = 0; r < p.n_peers; ++r) tma_prefetch_desc(&pm.m[r]);
@@ -454,11 +457,20 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
     cfg.blockDim = dim3(TS_THREADS, 1, 1);
     cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
     cfg.stream = s;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (CL > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = CL; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    if (p.pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = CL > 1 ? 1 : 0;
+    cfg.numAttrs = na;
     TB_CUDA(cudaLaunchKernelEx(&cfg, kern, map_act, map_pw, map_out, peer_maps, p));
     TB_LAUNCH_CHECK();
     return TB200_OK;

@@ -912,6 +912,9 @@ static int stream_umma(const void* x, int x_dtype, int64_t M, int64_t K, int64_t
     p.n_peers = peers ? n_peers : 0;
     for (int r = 0; r < p.n_peers; ++r) p.peers[r] = peers[r];
     { const char* e = getenv("TB200_GEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
+    // the GEMM's prologue and launch latency overlap the quantiser (single quantiser launch directly before it)
+    static const int pdl_env = getenv("TB200_STREAM_UMMA_PDL") ? atoi(getenv("TB200_STREAM_UMMA_PDL")) : 1;
+    p.pdl = (pdl_env && (layers == 1 || stride_x == M * ldx)) ? 1 : 0;
     return gemm_ts_launch(q_x, ldq, packed, ld_packed, p, out_dtype, s, M, stride_packed);
 }
 

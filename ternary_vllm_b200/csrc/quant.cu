@@ -85,6 +85,9 @@ __global__ void __launch_bounds__(QW * 32, GC == 8 ? 4 : (GC == 4 ? 6 : 8))
 quant_act_kernel(const T* __restrict__ x, int64_t M, int64_t K, int64_t ldx,
                  int8_t* __restrict__ q, int64_t ldq, float* __restrict__ s_x,
                  int32_t* __restrict__ sum_qx, int layout, bool vec_ok) {
+    // a dependent kernel launched with programmatic stream serialisation (the grouped tcgen05 GEMM) may start its
+    // prologue and weight stream now; it waits (griddepcontrol.wait) before it reads q / s_x / sum_qx
+    asm volatile("griddepcontrol.launch_dependents;");
     const int lane = threadIdx.x & 31;
     const int64_t m = (int64_t)blockIdx.x * QW + (threadIdx.x >> 5);
     if (m >= M) return;
@@ -191,6 +194,7 @@ quant_act_row_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
                      int32_t* __restrict__ sum_qx, int layout, bool vec_ok) {
     __shared__ float sh_max[8];
     __shared__ int sh_sum[8];
+    asm volatile("griddepcontrol.launch_dependents;");      // see quant_act_kernel
     const int64_t m = blockIdx.x;
     const T* xr = x + m * ldx;
     int8_t* qr = q + m * ldq;
