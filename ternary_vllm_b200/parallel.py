@@ -30,6 +30,12 @@ def shard_rows(N: int, world: int, rank: int, align: int = ROW_ALIGN) -> tuple[i
     return start, min(N, start + per)
 
 
+def _rotated(rank: int, world: int) -> list[int]:
+    """Peer order of a rank's stores: rank+1, rank+2, ..., rank (an all-to-all schedule: at any moment the ranks
+    address different receivers instead of all starting with rank 0)."""
+    return [(rank + 1 + i) % world for i in range(world)]
+
+
 def shard_size(N: int, world: int, align: int = ROW_ALIGN) -> int:
     per = -(-N // world)
     return -(-per // align) * align
@@ -103,8 +109,9 @@ class TPShardedLinear(nn.Module):
         for _ in range(2):
             buf = symm_mem.empty((max_tokens, self._peer_ld), dtype=dtype, device=dev)
             hdl = symm_mem.rendezvous(buf, grp)
+            # destinations in rotated order (rank+1, rank+2, ..., rank): the ranks do not all store to the same peer first
             ptrs = (ctypes.c_void_p * self.world)(*[int(hdl.buffer_ptrs[r]) + self.rank * self.n_shard * esz
-                                                    for r in range(self.world)])
+                                                    for r in _rotated(self.rank, self.world)])
             self._peer_bufs.append(buf)
             self._peer_hdls.append(hdl)
             self._peer_ptrs.append(ptrs)
@@ -170,7 +177,7 @@ class TPShardedStream(nn.Module):
             self._bufs.append(buf)
             self._hdls.append(hdl)
             self._ptrs.append((ctypes.c_void_p * self.world)(*[int(hdl.buffer_ptrs[r]) + self.rank * self.n_shard * esz
-                                                               for r in range(self.world)]))
+                                                               for r in _rotated(self.rank, self.world)]))
         self._turn = 0
         self._ws = None
 

@@ -70,3 +70,14 @@ def test_biobjective_gradient_golden(golden):
     assert np.allclose(got.numpy(), golden["bio_g_out"], rtol=1e-5, atol=1e-6)
     n, c = tb.compute_smooth_binary_stats(net, eps=0.2)
     assert [float(n), float(c)] == golden["bio_stats"].tolist()
+
+
+def test_tp_peer_order_is_a_rotation():
+    """Every rank stores to all ranks exactly once, and at step i the ranks address pairwise different receivers."""
+    from ternary_vllm_b200.parallel import _rotated
+    for world in (1, 2, 4, 8):
+        orders = [_rotated(r, world) for r in range(world)]
+        for r, o in enumerate(orders):
+            assert sorted(o) == list(range(world)) and o[-1] == r
+        for i in range(world):
+            assert len({o[i] for o in orders}) == world
