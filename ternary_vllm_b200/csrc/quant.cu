@@ -9,6 +9,7 @@
 // Output layouts: 0 natural K order; 1 "kperm" (tcgen05 GEMM operand order: within every group of
 // 16, position 4i+b holds element 4b+i); 2 the GEMV's shared-memory image (kperm words, 16-byte
 // chunks arranged [slab of 2048 k][word j of the packed chunk][lane]).
+#include <type_traits>
 #include "common.cuh"
 
 namespace tb200 {
@@ -256,6 +257,102 @@ quant_act_row_kernel(const T* __restrict__ x, int64_t K, int64_t ldx,
     }
 }
 
+// Specialised warp-per-row quantiser for the shapes the layers actually have: aligned rows of exactly K = 512 * GC
+// elements, ldq == K, layout known at compile time.  No bounds predicates; ~8 instructions per element:
+// the rounded value's low byte IS the int8 code (r + 1.5 * 2^23 keeps the two's-complement integer in the low mantissa
+// bits), so packing is three PRMT per word and the row sum one dp4a per word.  Same bits as quant1 / store16q.
+template <typename T, int GC, int LAYOUT>
+__global__ void __launch_bounds__(QW * 32, GC == 8 ? 4 : (GC == 4 ? 6 : 8))
+quant_act_fast_kernel(const T* __restrict__ x, int64_t M, int64_t ldx, int8_t* __restrict__ q,
+                      float* __restrict__ s_x, int32_t* __restrict__ sum_qx) {
+    asm volatile("griddepcontrol.launch_dependents;");      // see quant_act_kernel
+    constexpr int K = 512 * GC;
+    constexpr int NV = sizeof(T) == 4 ? 4 : 2;               // uint4 per 16 elements
+    const int lane = threadIdx.x & 31;
+    const int64_t m = (int64_t)blockIdx.x * QW + (threadIdx.x >> 5);
+    if (m >= M) return;
+    const uint4* xr = reinterpret_cast<const uint4*>(x + m * ldx);
+    uint4 raw[GC][NV];
+#pragma unroll
+    for (int u = 0; u < GC; ++u)
+#pragma unroll
+        for (int j = 0; j < NV; ++j) raw[u][j] = __ldg(xr + (lane + 32 * u) * NV + j);
+    auto unpack = [&](int u, float (&v)[16]) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const uint32_t w4[4] = {raw[u][j].x, raw[u][j].y, raw[u][j].z, raw[u][j].w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (sizeof(T) == 4) {
+                    v[4 * j + c] = __uint_as_float(w4[c]);
+                } else if (std::is_same<T, __nv_bfloat16>::value) {
+                    v[8 * j + 2 * c] = __uint_as_float(w4[c] << 16);
+                    v[8 * j + 2 * c + 1] = __uint_as_float(w4[c] & 0xffff0000u);
+                } else {
+                    const __half2 h = *reinterpret_cast<const __half2*>(&w4[c]);
+                    const float2 f = __half22float2(h);
+                    v[8 * j + 2 * c] = f.x; v[8 * j + 2 * c + 1] = f.y;
+                }
+            }
+        }
+    };
+    float amax = 0.0f;
+#pragma unroll
+    for (int u = 0; u < GC; ++u) {
+        float v[16];
+        unpack(u, v);
+#pragma unroll
+        for (int t = 0; t < 16; ++t) amax = fmaxf(amax, fabsf(v[t]));
+    }
+    amax = warp_max(amax);
+    const float s = amax > 0.0f ? __fdiv_rn(amax, 127.0f) : 1.0f;
+    const float inv = amax > 0.0f ? __fdiv_rn(127.0f, amax) : 1.0f;
+    int lsum = 0;
+    int8_t* qr = q + m * (int64_t)K;
+#pragma unroll
+    for (int u = 0; u < GC; ++u) {
+        float v[16];
+        unpack(u, v);
+        uint32_t rb[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) {
+            float r = __fmul_rn(v[t], inv);
+            r = fminf(fmaxf(r, -127.0f), 127.0f);
+            rb[t] = __float_as_uint(__fadd_rn(r, 12582912.0f));
+        }
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            // natural: word i = elements 4i..4i+3 ; kperm: word i = elements i, 4+i, 8+i, 12+i
+            const int e0 = LAYOUT != 0 ? i : 4 * i, st = LAYOUT != 0 ? 4 : 1;
+            const uint32_t lo = __byte_perm(rb[e0], rb[e0 + st], 0x0040);
+            const uint32_t hi = __byte_perm(rb[e0 + 2 * st], rb[e0 + 3 * st], 0x0040);
+            w[i] = __byte_perm(lo, hi, 0x5410);
+            lsum = __dp4a((int)w[i], 0x01010101, lsum);
+        }
+        const int g = lane + 32 * u;
+        int pos = g;
+        if (LAYOUT == 2) {
+            const int c = g >> 2, j = g & 3;
+            pos = ((c >> 5) * 4 + j) * 32 + (c & 31);
+        }
+        *reinterpret_cast<uint4*>(qr + 16 * pos) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    lsum = warp_sum(lsum);
+    if (lane == 0) {
+        s_x[m] = s;
+        if (sum_qx) sum_qx[m] = lsum;
+    }
+}
+
+template <typename T, int GC>
+static void launch_quant_fast(const T* x, int64_t M, int64_t ldx, int8_t* q, float* s_x, int32_t* sum_qx, int layout, cudaStream_t st) {
+    const unsigned grid = (unsigned)((M + QW - 1) / QW);
+    if (layout == 0) quant_act_fast_kernel<T, GC, 0><<<grid, QW * 32, 0, st>>>(x, M, ldx, q, s_x, sum_qx);
+    else if (layout == 1) quant_act_fast_kernel<T, GC, 1><<<grid, QW * 32, 0, st>>>(x, M, ldx, q, s_x, sum_qx);
+    else quant_act_fast_kernel<T, GC, 2><<<grid, QW * 32, 0, st>>>(x, M, ldx, q, s_x, sum_qx);
+}
+
 }  // namespace tb200
 
 using namespace tb200;
@@ -277,7 +374,13 @@ extern "C" int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K
     // few rows: one CTA per row (the warp-per-row kernel would leave most SMs idle and is latency-bound per row)
     static const int64_t warp_min_rows = getenv("TB200_QUANT_WARP_MIN_ROWS") ? atoll(getenv("TB200_QUANT_WARP_MIN_ROWS")) : 4 * (int64_t)sm_count();
     const int64_t groups = ldq >> 4;
-    if (groups <= 32 * GC_MAX && M >= warp_min_rows) {
+    static const int fast_env = getenv("TB200_QUANT_FAST") ? atoi(getenv("TB200_QUANT_FAST")) : 1;
+    if (fast_env && vec_ok && ldq == K && (K == 1024 || K == 2048 || K == 4096) && M >= warp_min_rows) {
+        cudaStream_t st = (cudaStream_t)stream;
+        if (K == 1024) { TB_DISPATCH_DTYPE(dtype, T, (launch_quant_fast<T, 2>((const T*)x, M, ldx, q_x, s_x, sum_qx, layout, st))); }
+        else if (K == 2048) { TB_DISPATCH_DTYPE(dtype, T, (launch_quant_fast<T, 4>((const T*)x, M, ldx, q_x, s_x, sum_qx, layout, st))); }
+        else { TB_DISPATCH_DTYPE(dtype, T, (launch_quant_fast<T, 8>((const T*)x, M, ldx, q_x, s_x, sum_qx, layout, st))); }
+    } else if (groups <= 32 * GC_MAX && M >= warp_min_rows) {
         const unsigned grid = (unsigned)((M + QW - 1) / QW);
         cudaStream_t st = (cudaStream_t)stream;
         if (groups <= 64) {

@@ -135,7 +135,9 @@ def test_ternary_init_vs_oracle(cuda, N, K, dtype):
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("layout", [0, 1, 2])
-@pytest.mark.parametrize("M,K", [(1, 64), (5, 77), (3, 4096), (40, 1000), (2, 11008)])
+@pytest.mark.parametrize("M,K", [(1, 64), (5, 77), (3, 4096), (40, 1000), (2, 11008),
+                                 # >= 4 rows per SM: the warp-per-row kernels (specialised for K = 1024 / 2048 / 4096, generic otherwise)
+                                 (700, 4096), (650, 1024), (600, 2048), (640, 512), (610, 3000)])
 def test_quant_act_bit_exact(cuda, dtype, layout, M, K):
     g = torch.Generator().manual_seed(M * 7 + K)
     x = (torch.randn(M, K, generator=g) * 3).to(dtype)
