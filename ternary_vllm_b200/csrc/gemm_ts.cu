@@ -292,7 +292,11 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         const uint32_t addr = stg + (uint32_t)((j * TS_ROWS + q * 32 + lane) * sizeof(OT));
                         if (sizeof(OT) == 4) asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(to_f32(yv)) : "memory");
                         else asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(*reinterpret_cast<const unsigned short*>(&yv)) : "memory");
-                        if (acc_on && n < p.N && m0 + c0 + j < p.M) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
+                    }
+                    if (acc_on) {                   // parity output (debug): a separate, warp-uniformly skipped block keeps the
+#pragma unroll                                     // 32 predicated global stores out of the hot loop above
+                        for (int j = 0; j < CH; ++j)
+                            if (n < p.N && m0 + c0 + j < p.M) p.acc_out[(m0 + c0 + j) * p.N + n] = (int)r[j] - sqv[j];
                     }
                     fence_proxy_async();
                     asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -317,7 +321,6 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         const float tv = __fmul_rn((float)a, sxv[j]);
                         const OT yv = from_f32<OT>(epilogue(tv, sc, bi, p.clip_val));
                         if (j < valid) {
-                            if (acc_on) p.acc_out[(m0 + c0 + j) * p.N + n] = a;
                             if (p.n_peers == 0) orow[(int64_t)j * p.ldo] = yv;
                             else {
 #pragma unroll 1
@@ -325,6 +328,11 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                                     reinterpret_cast<OT*>(p.peers[r])[(orow - out_base) + (int64_t)j * p.ldo] = yv;
                             }
                         }
+                    }
+                    if (acc_on) {
+#pragma unroll
+                        for (int j = 0; j < CH; ++j)
+                            if (j < valid) p.acc_out[(m0 + c0 + j) * p.N + n] = (int)r[j] - sqv[j];
                     }
                 }
             }

@@ -2,6 +2,7 @@
 
     python tools/prof_case.py gemv [M]     # 40 distinct 4096x11008 layers, M tokens (default 1), plain launches
     python tools/prof_case.py gemm         # quant + tcgen05 GEMM, M=4096 K=4096 N=11008, 3 times
+    python tools/prof_case.py vit          # the same for the ViT-L QKV shape, M=8224 K=1024 N=3072
 """
 import math
 import os
@@ -59,7 +60,7 @@ elif case == "grouped":
                                            R, 0, torch.cuda.current_stream().cuda_stream), "grouped")
     torch.cuda.synchronize()
 else:
-    M, K, N = 4096, 4096, 11008
+    M, K, N = (32 * 257, 1024, 3072) if case == "vit" else (4096, 4096, 11008)     # vit: configs[3] QKV projection
     packed = ops.quantize_pack(torch.randn(N, K, generator=g, device=dev).clip_(-1, 1), "ternary")
     scale = torch.full((N,), 1 / math.sqrt(K), device=dev)
     bias = torch.randn(N, generator=g, device=dev)
