@@ -261,6 +261,11 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                 // per-token scale and code offset of the chunk first (registers), so that the 32 output
                 // chains below are independent of each other and of the global stores
                 float sxv[CH]; int sqv[CH];
+                uint32_t r[32];
+                constexpr int ND = (CL == 1) ? Cfg::DUAL : 1;
+                constexpr bool SPLIT_LD = (CH == 32 && ND == 1);      // TMEM load issued first, waited for after the barrier below
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * ND * BT + c0);
+                if (SPLIT_LD) tmem_ld32_issue(taddr, r);
 #pragma unroll
                 for (int j = 0; j < CH; j += 4) {
                     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
@@ -268,10 +273,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];"
                                  : "=r"(sqv[j]), "=r"(sqv[j + 1]), "=r"(sqv[j + 2]), "=r"(sqv[j + 3]) : "r"(sq_s + (c0 + j) * 4));
                 }
-                uint32_t r[32];
-                constexpr int ND = (CL == 1) ? Cfg::DUAL : 1;
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * ND * BT + c0);
-                if (CH == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
+                if (!SPLIT_LD) { if (CH == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r); }
                 if (ND == 2 && p.k_blocks > 1) {
                     uint32_t r2[32];
                     if (CH == 32) tmem_ld32(taddr + (uint32_t)BT, r2); else tmem_ld16(taddr + (uint32_t)BT, r2);
@@ -284,6 +286,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     const uint32_t stg = sOut + (uint32_t)(chunk_no & 1) * Cfg::OUT_STAGE_BYTES;
                     if (et == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store that last read `stg` is done
                     asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (SPLIT_LD) tmem_ld32_wait(r);
 #pragma unroll
                     for (int j = 0; j < CH; ++j) {
                         const int a = (int)r[j] - sqv[j];
@@ -311,7 +314,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     }
                     ++chunk_no;
-                } else if (n < p.N) {
+                } else if (SPLIT_LD ? (tmem_ld32_wait(r), n < p.N) : (n < p.N)) {     // the wait is warp-wide: before the row test
                     OT* orow = out + m0 * p.ldo + n + (int64_t)c0 * p.ldo;
                     int valid = (int)((p.M - m0 - c0) < CH ? (p.M - m0 - c0) : CH);            // tokens of the chunk in range
                     if (p.dbg & 256) valid = (sc == 12345.678f) ? valid : 0;
