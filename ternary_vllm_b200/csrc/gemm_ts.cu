@@ -505,8 +505,16 @@ static int ts_dispatch_bt(const int8_t* q_x, int64_t ldq, const uint8_t* packed,
     if (p.M <= 128) return launch_ts<OT, 128, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
     const int n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);
     const int cl = n_tiles >= 8 ? ts_cluster_size() : 1;
-    static int bt = -1;
-    if (bt < 0) { const char* e = getenv("TB200_GEMM_BT"); bt = e ? atoi(e) : 192; }
+    static int bt_env = -1;
+    if (bt_env < 0) { const char* e = getenv("TB200_GEMM_BT"); bt_env = e ? atoi(e) : 0; }
+    int bt = bt_env;
+    if (bt == 0) {
+        // tiles go round-robin to one CTA per SM: pick the token tile (192 or 160) with the smaller rounds x tile cost
+        // (wave quantisation: M=8224, N=1024 is 3 rounds either way, so the smaller tile wins; ties go to 192)
+        const int64_t layers = p.layers < 1 ? 1 : p.layers;
+        auto cost = [&](int64_t b) { const int64_t tiles = (int64_t)n_tiles * ((p.M + b - 1) / b) * layers; return (tiles + sm_count() - 1) / sm_count() * b; };
+        bt = (cl == 1 && cost(160) < cost(192)) ? 160 : 192;
+    }
     if constexpr (sizeof(OT) == 2) { if (bt == 160) return launch_ts<OT, 160, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp); }
     if (cl == 4) return launch_ts<OT, 192, 4>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
     if (cl == 2) return launch_ts<OT, 192, 2>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
