@@ -7,9 +7,15 @@ Follows ``/root/reference/impl/tf/moondream/ternary.py``:
 * format C  ``ScaledTernaryPackedMM.pack_fn`` (:374-398) — same ``[N, ceil(K/4)]``
   shape as the ``pw`` the LCE-fork ops consume (:264-276, :316-328).
 
-Parity: pinned by the round trip the reference tests (``ternary_tests.py:17-38``)
-and by hand-derived known-answer bytes; TensorFlow is absent so the TF functions
-themselves were never executed ("parity unpinned" at byte level beyond that).
+Parity: PINNED.  ``oracle/make_golden_packing.py`` executes the reference's own source of
+these functions (taken from ``ternary.py`` with ``ast``; ``oracle/tf_stub.py`` stands in for
+the absent TensorFlow) and commits its outputs as ``tests/golden/packing_vectors.npz``;
+``tests/test_oracle_packing.py`` holds this restatement to those bytes (ragged lengths, the
+full alphabet, all 256 byte values through the unpackers), to the round trip the reference
+tests (``ternary_tests.py:17-38``, also executed from source) and to hand-derived
+known-answer bytes.  One reference quirk: for K % 4 != 0 the 2-D ``pack_fn`` raises
+(``tf.concat`` rank mismatch, ``ternary.py:380``); padding such rows with code 1 is an
+extension defined here.
 """
 from __future__ import annotations
 

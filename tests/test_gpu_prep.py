@@ -155,3 +155,60 @@ def test_quant_act_bit_exact(cuda, dtype, layout, M, K):
         assert ldq == (K + 4095) // 4096 * 4096
         qpad = qpad[:, ref_int8.gemv_layout_index(K)]
     assert np.array_equal(q.cpu().numpy(), qpad)
+
+
+# ---- the reference's own pack / unpack / packed-layer outputs (oracle/make_golden_packing.py) -----------------
+@pytest.fixture(scope="module")
+def pk():
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    return np.load(os.path.join(root, "tests", "golden", "packing_vectors.npz"), allow_pickle=False)
+
+
+@pytest.mark.parametrize("T", [1, 2, 3, 4, 5, 8, 63, 64, 1000, 5031])
+def test_pack_formats_A_B_vs_reference_bytes(cuda, pk, T):
+    t = torch.from_numpy(pk[f"ab_t_{T}"].astype(np.int8)).to(cuda)
+    for fmt, key in (("A", "a"), ("B", "b")):
+        got = ops.pack_format(t, fmt)
+        assert np.array_equal(got.cpu().numpy(), pk[f"{key}_packed_{T}"]), (fmt, T)
+        back = ops.unpack_format(got, fmt).cpu().numpy()
+        assert np.array_equal(back, pk[f"{key}_unpacked_{T}"].astype(np.int8)), (fmt, T)
+
+
+def test_unpack_formats_every_byte_vs_reference(cuda, pk):
+    allb = torch.arange(256, dtype=torch.int32).to(torch.uint8).to(cuda)
+    assert np.array_equal(ops.unpack_format(allb, "A").cpu().numpy(), pk["a_unpacked_allbytes"].astype(np.int8))
+    assert np.array_equal(ops.unpack_format(allb, "B").cpu().numpy(), pk["b_unpacked_allbytes"].astype(np.int8))
+
+
+@pytest.mark.parametrize("tag", ["c_5x4", "c_7x8", "c_9x32", "c_16x64", "c_12x260"])
+def test_format_C_ops_and_fused_op_vs_reference_packed_layers(cuda, pk, tag):
+    """a14/a16/a17: pack_fn bytes, unpack, and ops.ternary_matmul's maths against the outputs of the reference's own
+    ScaledTernaryPackedMM.pack_fn / .call and ScaledTernaryTf.call (float activations: tb200_gemv_f32)."""
+    w, x = pk[tag + "_w"], pk[tag + "_x"]
+    N, K = w.shape
+    wt = torch.from_numpy(w).to(cuda)
+    assert np.array_equal(ops.pack_format(wt, "C").cpu().numpy(), pk[tag + "_packed"])               # ops.pack_fn(int8 [N,K])
+    internal = ops.quantize_pack(wt.float(), "ternary")                                              # ternarise + pack
+    assert np.array_equal(internal.cpu().numpy()[:, : (K + 3) // 4], pk[tag + "_packed"])
+    assert np.array_equal(ops.unpack(internal, K).cpu().numpy(), w)                                  # ops.unpack_ternary
+    scale, bias = torch.from_numpy(pk[tag + "_scale"]).to(cuda), torch.from_numpy(pk[tag + "_bias"]).to(cuda)
+    for clip in (100.0, 0.5):
+        y = ops.gemv_f32(torch.from_numpy(x).to(cuda), internal, scale, bias, clip).cpu().numpy()
+        want = pk[tag + f"_mm_clip{clip}"]
+        assert np.allclose(y, want, rtol=1e-5, atol=2e-6), np.abs(y - want).max()
+    y = ops.gemv_f32(torch.from_numpy(x).to(cuda), internal, scale, bias, 100.0).cpu().numpy()
+    assert np.allclose(y, pk[tag + "_tf_call"], rtol=1e-5, atol=2e-6)
+    x3 = pk[tag + "_x3"]
+    y3 = ops.gemv_f32(torch.from_numpy(x3.reshape(-1, K)).to(cuda), internal, scale, bias, 100.0).cpu().numpy()
+    assert np.allclose(y3.reshape(2, 3, N), pk[tag + "_mm3"], rtol=1e-5, atol=2e-6)
+
+
+def test_ternary_mm_golden_on_gpu(cuda, golden):
+    """a18: matrix_mul_tests.py:29-37 `ternary_mm(m, tm)` == m @ sign(tm)^T, through tb200_gemv_f32 (scale 1, no bias,
+    no effective clip) on weights whose codes are sign(tm) in {-1,0,+1}."""
+    a, b = golden["tmm_a"], golden["tmm_b"]
+    codes = np.sign(b).astype(np.float32)                       # tm[i] > 0 -> +1, < 0 -> -1, == 0 -> skipped
+    packed = ops.quantize_pack(torch.from_numpy(codes).to(cuda), "ternary")
+    y = ops.gemv_f32(torch.from_numpy(a).to(cuda), packed, None, None, 3.0e38).cpu().numpy()
+    assert np.allclose(y, golden["tmm_out"], rtol=1e-5, atol=1e-5)
