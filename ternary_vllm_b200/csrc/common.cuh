@@ -5,6 +5,7 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <atomic>
 
 #include "../../include/ternary_b200.h"
@@ -13,9 +14,36 @@ namespace tb200 {
 
 // ---- error reporting (thread-local message, see tb200_last_error) ----------
 void set_error(const char* fmt, ...);
-int  check_device();                 // TB200_OK or TB200_ENODEV (cached per process)
-int  sm_count();
+// Device state is kept PER DEVICE ORDINAL (a process may drive several GPUs from several host threads):
+int  current_device();               // cudaGetDevice, -1 on failure
+int  check_device();                 // TB200_OK or TB200_ENODEV for the calling thread's current device
+int  sm_count();                     // SM count of the calling thread's current device
 extern std::atomic<uint64_t> g_launches;
+constexpr int TB_MAX_DEVICES = 64;
+
+// Tuning / ablation knobs.  The release library does not read the environment and carries no ablation branches in its
+// kernels: `make ABLATE=1` (-DTB200_ABLATE) builds the experiment library that honours the TB200_* variables quoted in
+// DESIGN.md / profiles/README.md.
+#ifdef TB200_ABLATE
+constexpr bool kAblate = true;
+static inline long long tb_knob(const char* name, long long dflt) { const char* e = getenv(name); return e ? atoll(e) : dflt; }
+#else
+constexpr bool kAblate = false;
+static inline long long tb_knob(const char*, long long dflt) { return dflt; }
+#endif
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device (per-context) attribute: remember what was requested
+// for every device ordinal separately (a process-wide flag would skip the opt-in on the second GPU).  Races between host
+// threads are benign (the attribute is set again with the same or a larger value).
+struct SmemOptIn { std::atomic<size_t> bytes[TB_MAX_DEVICES]; };
+template <typename Kern>
+static inline cudaError_t ensure_dynamic_smem(Kern kern, SmemOptIn& st, size_t smem) {
+    const int dev = current_device();
+    if (dev >= 0 && dev < TB_MAX_DEVICES && smem <= st.bytes[dev].load(std::memory_order_acquire)) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess && dev >= 0 && dev < TB_MAX_DEVICES) st.bytes[dev].store(smem, std::memory_order_release);
+    return e;
+}
 
 #define TB_REQUIRE(cond, ...)                                   \
     do {                                                        \

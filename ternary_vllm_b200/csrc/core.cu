@@ -15,35 +15,66 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 
-static int g_dev_state = 1;  // 1 = unknown, 0 = ok, <0 = error
-static int g_sms = 0;
+// per-device: 1 = unknown, 0 = ok, <0 = error
+static std::atomic<int> g_dev_state[TB_MAX_DEVICES];
+static std::atomic<int> g_dev_sms[TB_MAX_DEVICES];
+static std::atomic<bool> g_dev_init{false};
+static std::atomic<int> g_no_device{0};          // cudaGetDevice itself failed (no driver / no GPU): cached
+
+int current_device() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+    return dev;
+}
 
 int check_device() {
-    if (g_dev_state <= 0) {
-        if (g_dev_state < 0) set_error("no sm_100 CUDA device available (libternary_b200 has no CPU fallback)");
-        return g_dev_state;
+    if (g_no_device.load(std::memory_order_relaxed)) {
+        set_error("no CUDA device (libternary_b200 has no CPU fallback)");
+        return TB200_ENODEV;
     }
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
-    cudaDeviceProp p;
-    if (e == cudaSuccess) e = cudaGetDeviceProperties(&p, dev);
     if (e != cudaSuccess) {
         cudaGetLastError();
-        g_dev_state = TB200_ENODEV;
+        g_no_device.store(1);
         set_error("no CUDA device: %s (libternary_b200 has no CPU fallback)", cudaGetErrorString(e));
-        return g_dev_state;
+        return TB200_ENODEV;
     }
-    if (p.major != 10) {
-        g_dev_state = TB200_ENODEV;
-        set_error("device '%s' is sm_%d%d; libternary_b200 is built for sm_100a only", p.name, p.major, p.minor);
-        return g_dev_state;
+    if (dev < 0 || dev >= TB_MAX_DEVICES) { set_error("device ordinal %d out of range", dev); return TB200_ENODEV; }
+    // states: 0 = unknown (zero-initialised), 1 = ok, 2 = not sm_100
+    const int st = g_dev_state[dev].load(std::memory_order_acquire);
+    if (st == 1) return TB200_OK;
+    if (st == 2) {
+        set_error("device %d is not sm_100; libternary_b200 is built for sm_100a only (no CPU fallback)", dev);
+        return TB200_ENODEV;
     }
-    g_sms = p.multiProcessorCount;
-    g_dev_state = TB200_OK;
+    int major = 0, sms = 0;
+    e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("cannot query device %d: %s (libternary_b200 has no CPU fallback)", dev, cudaGetErrorString(e));
+        return TB200_ENODEV;
+    }
+    if (major != 10) {
+        g_dev_state[dev].store(2, std::memory_order_release);
+        set_error("device %d is sm_%dx; libternary_b200 is built for sm_100a only (no CPU fallback)", dev, major);
+        return TB200_ENODEV;
+    }
+    g_dev_sms[dev].store(sms, std::memory_order_relaxed);
+    g_dev_state[dev].store(1, std::memory_order_release);
     return TB200_OK;
 }
 
-int sm_count() { return g_sms > 0 ? g_sms : 148; }
+int sm_count() {
+    const int dev = current_device();
+    if (dev >= 0 && dev < TB_MAX_DEVICES) {
+        int sms = g_dev_sms[dev].load(std::memory_order_relaxed);
+        if (sms > 0) return sms;
+        if (check_device() == TB200_OK) return g_dev_sms[dev].load(std::memory_order_relaxed);
+    }
+    return 148;
+}
 
 // cuTensorMapEncodeTiled is fetched through the runtime so that the library has no link-time
 // dependency on libcuda (it must load, and fail loudly, on machines without a driver).
@@ -53,7 +84,8 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dt, int rank, const void* ptr,
                     const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
                     CUtensorMapSwizzle swz) {
-    static EncodeTiledFn enc = nullptr;
+    static std::atomic<EncodeTiledFn> enc_slot{nullptr};
+    EncodeTiledFn enc = enc_slot.load(std::memory_order_acquire);
     if (!enc) {
         void* fp = nullptr;
         cudaDriverEntryPointQueryResult qres;
@@ -64,6 +96,7 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dt, int rank, const vo
             return TB200_ECUDA;
         }
         enc = (EncodeTiledFn)fp;
+        enc_slot.store(enc, std::memory_order_release);
     }
     cuuint64_t d[5] = {1, 1, 1, 1, 1}, st[4] = {0, 0, 0, 0};
     cuuint32_t bx[5] = {1, 1, 1, 1, 1}, es[5] = {1, 1, 1, 1, 1};

@@ -135,7 +135,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     mbar_wait(bar_done(s), ph ^ 1u);
                     mbar_arrive_expect_tx(bar_pfull(s), TS_P_BYTES);
                     tma_load_3d(sP + s * TS_P_BYTES, &map_pw, bar_pfull(s), kb * (TS_BK / 4), n_tile * TS_ROWS, layer);
-                    if (p.dbg & 8) { mbar_arrive(bar_ready(s)); if (++s == NS) { s = 0; ph ^= 1u; } continue; }   // experiment: no activation traffic
+                    if (kAblate && (p.dbg & 8)) { mbar_arrive(bar_ready(s)); if (++s == NS) { s = 0; ph ^= 1u; } continue; }   // experiment: no activation traffic
                     mbar_arrive_expect_tx(bar_ready(s), Cfg::B_BYTES);
 #pragma unroll
                     for (int j = 0; j < TS_KS; ++j) {
@@ -171,7 +171,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         mbar_wait_uniform(bar_ready(s), ph);
                         tc_fence_after();
                         const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
-                        if (!(p.dbg & 4)) {
+                        if (!(kAblate && (p.dbg & 4))) {
 #pragma unroll
                             for (int j = 0; j < TS_KS; ++j) {
                                 const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
@@ -204,7 +204,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     mbar_wait(bar_ready(s), ph);
                     tc_fence_after();
                     const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
-                    if (!(p.dbg & 4)) {
+                    if (!(kAblate && (p.dbg & 4))) {
 #pragma unroll
                         for (int j = 0; j < TS_KS; ++j) {
                             const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
@@ -257,7 +257,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
             const uint32_t sx_s = sSX + (uint32_t)(buf * BT) * 4u;                 // shared-space addresses: explicit
             const uint32_t sq_s = sSX + (uint32_t)(2 * BT + buf * BT) * 4u;       // ld.shared keeps them off the generic path
 #pragma unroll 1
-            for (int c0 = 0; c0 < ((p.dbg & 1) ? 0 : BT); c0 += CH) {
+            for (int c0 = 0; c0 < ((kAblate && (p.dbg & 1)) ? 0 : BT); c0 += CH) {
                 // per-token scale and code offset of the chunk first (registers), so that the 32 output
                 // chains below are independent of each other and of the global stores
                 float sxv[CH]; int sqv[CH];
@@ -317,7 +317,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                 } else if (SPLIT_LD ? (tmem_ld32_wait(r), n < p.N) : (n < p.N)) {     // the wait is warp-wide: before the row test
                     OT* orow = out + m0 * p.ldo + n + (int64_t)c0 * p.ldo;
                     int valid = (int)((p.M - m0 - c0) < CH ? (p.M - m0 - c0) : CH);            // tokens of the chunk in range
-                    if (p.dbg & 256) valid = (sc == 12345.678f) ? valid : 0;
+                    if (kAblate && (p.dbg & 256)) valid = (sc == 12345.678f) ? valid : 0;
 #pragma unroll
                     for (int j = 0; j < CH; ++j) {
                         const int a = (int)r[j] - sqv[j];
@@ -369,7 +369,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         w[4 * c] = v.x; w[4 * c + 1] = v.y; w[4 * c + 2] = v.z; w[4 * c + 3] = v.w;
                     }
                     uint32_t r0[32], r1[32];
-                    if (!(p.dbg & 2)) {
+                    if (!(kAblate && (p.dbg & 2))) {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             r0[4 * j + 0] = w[j] & 0x03030303u;
@@ -384,7 +384,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     }
                     if (kbc >= TS_NSA) mbar_wait(bar_done(s2), ph2);   // the MMAs that read this A slot have retired
                     tc_fence_after();
-                    if (!(p.dbg & 2)) {
+                    if (!(kAblate && (p.dbg & 2))) {
                         const uint32_t ta = tmem_a0 + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * TS_A_COLS);
                         tmem_st32(ta, r0);
                         tmem_st32(ta + 32u, r1);
@@ -435,7 +435,7 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
     PeerMaps peer_maps;
     for (int r = 0; r < 8; ++r) peer_maps.m[r] = map_pw;
     p.tma_out = (BT >= 32) && ((uintptr_t)p.out % 16 == 0) && ((p.ldo * sizeof(OT)) % 16 == 0) &&
-                ((p.stride_out * sizeof(OT)) % 16 == 0) && !(p.dbg & 512);
+                ((p.stride_out * sizeof(OT)) % 16 == 0) && !(kAblate && (p.dbg & 512));
     for (int r = 0; r < p.n_peers; ++r) p.tma_out = p.tma_out && ((uintptr_t)p.peers[r] % 16 == 0);
     if (p.tma_out) {
         uint64_t dims_o[3] = {(uint64_t)p.N, (uint64_t)p.M, L};
@@ -452,11 +452,8 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
         for (int r = p.n_peers; r < 8; ++r) peer_maps.m[r] = map_out;
     }
     auto kern = umma_ts_kernel<OT, BT, CL>;
-    static bool configured = false;
-    if (!configured) {
-        TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-        configured = true;
-    }
+    static SmemOptIn optin;
+    TB_CUDA(ensure_dynamic_smem(kern, optin, Cfg::SMEM_BYTES));
     p.m_tiles = (int)((p.M + BT - 1) / BT);
     p.n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);
     p.k_blocks = (int)((p.K + TS_BK - 1) / TS_BK);
@@ -488,12 +485,8 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
 }
 
 static int ts_cluster_size() {
-    static int cl = -1;
-    if (cl < 0) {
-        const char* e = getenv("TB200_GEMM_CLUSTER");
-        cl = e ? atoi(e) : 1;     // measured: multicast clusters do not pay (the kernel is not L2-bound); kept as an option
-        if (cl != 1 && cl != 2 && cl != 4) cl = 1;
-    }
+    // measured: multicast clusters do not pay (the kernel is not L2-bound); an option of the experiment build only
+    static const int cl = [] { const int v = (int)tb_knob("TB200_GEMM_CLUSTER", 1); return (v == 2 || v == 4) ? v : 1; }();
     return cl;
 }
 
@@ -505,8 +498,7 @@ static int ts_dispatch_bt(const int8_t* q_x, int64_t ldq, const uint8_t* packed,
     if (p.M <= 128) return launch_ts<OT, 128, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
     const int n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);
     const int cl = n_tiles >= 8 ? ts_cluster_size() : 1;
-    static int bt_env = -1;
-    if (bt_env < 0) { const char* e = getenv("TB200_GEMM_BT"); bt_env = e ? atoi(e) : 0; }
+    static const int bt_env = (int)tb_knob("TB200_GEMM_BT", 0);
     int bt = bt_env;
     if (bt == 0) {
         // tiles go round-robin to one CTA per SM: pick the token tile (192 or 160) with the smaller rounds x tile cost

@@ -564,7 +564,7 @@ int get_weight_map(const uint8_t* packed, int64_t ld, int64_t N, int64_t stride,
             return TB200_OK;
         }
     MapEntry& e = g_maps[g_map_next];
-    static const int no4d = getenv("TB200_GEMV_NO4D") ? atoi(getenv("TB200_GEMV_NO4D")) : 0;
+    static const int no4d = (int)tb_knob("TB200_GEMV_NO4D", 0);
     int rc = TB200_ECUDA;
     e.one_box = false;
     if (ld % GV_SEG == 0 && !no4d) {
@@ -619,14 +619,11 @@ static int launch_gemv(const CUtensorMap& map, GemvParams p, int layers, cudaStr
     TB_REQUIRE(gemv_pick(p.M, p.nks, p.nrb, &p.stages, &p.nslots),
                "gemv: K=%lld N=%lld is too large for the shared-memory activation image", (long long)p.K, (long long)p.N);
     size_t smem = gemv_smem(p.M, p.nks, p.stages, p.nslots, p.nrb);
-    static const int solo_env = getenv("TB200_GEMV_SOLO") ? atoi(getenv("TB200_GEMV_SOLO")) : 0;
+    static const int solo_env = (int)tb_knob("TB200_GEMV_SOLO", 0);
     if (solo_env && smem < 120 * 1024) smem = 120 * 1024;     // experiment: one CTA per SM
     auto kern = gemv_mma_kernel<XT, OT, FUSED, VEC>;
-    static size_t configured = 0;   // per instantiation
-    if (smem > configured) {
-        TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static SmemOptIn optin;         // per instantiation and device
+    TB_CUDA(ensure_dynamic_smem(kern, optin, smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas, (unsigned)layers, 1);
     cfg.blockDim = dim3(GV_THREADS, 1, 1);

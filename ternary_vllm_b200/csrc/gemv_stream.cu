@@ -710,20 +710,20 @@ static size_t stream_stage_off(const StreamGeom& gm, int stages, int nslots, int
 // staging tiles of the tensor-parallel epilogue: aux warps x SV_PEER_BUFS buffers x [8 * ng tokens][16 rows] x element size
 static size_t stream_stage_bytes(const StreamGeom& gm, bool peers, int aux, size_t esz) { return peers ? (size_t)aux * SV_PEER_BUFS * gm.ng * 8 * SV_ROWS * esz : 0; }
 static size_t stream_smem(const StreamGeom& gm, int stages, int nslots, int nimg, size_t peer_esz = 0) {
-    static const int teams = getenv("TB200_STREAM_TEAMS") ? atoi(getenv("TB200_STREAM_TEAMS")) : 2;
+    static const int teams = (int)tb_knob("TB200_STREAM_TEAMS", 2);
     const int aux = (gm.ng == 1 && teams != 2) ? 4 : 2;         // as dispatched in gemv_stream_impl
     return 1024 + stream_stage_off(gm, stages, nslots, nimg) + stream_stage_bytes(gm, peer_esz > 0, aux, peer_esz) + 64;
 }
 // ring depth first (bytes in flight), then a second image buffer, then more slots
 static bool stream_pick(const StreamGeom& gm, bool breg, int* stages, int* nslots, int* nimg, size_t peer_esz = 0) {
     const size_t limit = 227 * 1024;
-    static const int st_env = getenv("TB200_STREAM_STAGES") ? atoi(getenv("TB200_STREAM_STAGES")) : 0;
+    static const int st_env = (int)tb_knob("TB200_STREAM_STAGES", 0);
     const int want_st = st_env > 0 ? st_env : 8;
     const int min_st = gm.nks < 3 ? 3 : (gm.nks < SV_MAX_STAGES ? gm.nks : SV_MAX_STAGES);
     // images: with the B fragments in registers (breg) a buffer is free again as soon as the layer's fragments are loaded,
     // but the NEXT layer's image must already be in flight then (its load queues behind the weight ring), so small
     // images get up to four buffers
-    static const int img_env = getenv("TB200_STREAM_NIMG") ? atoi(getenv("TB200_STREAM_NIMG")) : 0;
+    static const int img_env = (int)tb_knob("TB200_STREAM_NIMG", 0);
     const int want_img = img_env > 0 ? (img_env > SV_MAX_IMG ? SV_MAX_IMG : img_env) : (breg ? (gm.img_bytes <= 16384 ? 4 : 2) : 2);
     for (int img = want_img; img >= 1; --img)
         for (int st = want_st; st >= min_st; --st)
@@ -742,11 +742,8 @@ bool gemv_stream_fits(int64_t M, int64_t K) {
 template <int NG, bool BREG, int TEAMS, int AUX, bool PEER>
 static int launch_stream_v(const CUtensorMap& map, const typename PeerArg<PEER>::type& pm, const StreamParams& p, size_t smem, int ctas, bool pdl, cudaStream_t s) {
     auto kern = gemv_stream_kernel<NG, BREG, TEAMS, AUX, PEER>;
-    static size_t configured = 0;
-    if (smem > configured) {
-        TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static SmemOptIn optin;
+    TB_CUDA(ensure_dynamic_smem(kern, optin, smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas, 1, 1);
     cfg.blockDim = dim3(sv_threads(AUX), 1, 1);
@@ -842,14 +839,14 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     p.img_bytes = gm.img_bytes; p.grp_bytes = gm.grp_bytes;
     p.clip_val = fabsf(clip_val);
     p.one_box = one_box;
-    static const int dbg_env = getenv("TB200_STREAM_DBG") ? atoi(getenv("TB200_STREAM_DBG")) : 0;
+    static const int dbg_env = (int)tb_knob("TB200_STREAM_DBG", 0);
     p.dbg = dbg_env;
     const int64_t total = (int64_t)p.row_blocks * layers;
     const int ctas = (int)(total < sm_count() ? total : sm_count());
     const size_t smem = stream_smem(gm, p.stages, p.nslots, p.nimg, peer_esz);
     switch (gm.ng) {
         case 1: {
-            static const int teams = getenv("TB200_STREAM_TEAMS") ? atoi(getenv("TB200_STREAM_TEAMS")) : 2;
+            static const int teams = (int)tb_knob("TB200_STREAM_TEAMS", 2);
             if (teams == 2)
                 return breg ? launch_stream<1, true, 2, 2>(map, pm, p, smem, ctas, true, s) : launch_stream<1, false, 2, 2>(map, pm, p, smem, ctas, true, s);
             return breg ? launch_stream<1, true, 1, 4>(map, pm, p, smem, ctas, true, s) : launch_stream<1, false, 1, 4>(map, pm, p, smem, ctas, true, s);
@@ -867,7 +864,7 @@ using namespace tb200;
 // tokens from which the list is served by the grouped tcgen05 kernel (gemm_ts.cu) instead of mma.sync: above 8 tokens
 // the legacy IMMA pipe, not HBM, bounds the mma.sync kernel
 static int stream_umma_min_m() {
-    static const int v = getenv("TB200_STREAM_UMMA_MIN_M") ? atoi(getenv("TB200_STREAM_UMMA_MIN_M")) : 9;
+    static const int v = (int)tb_knob("TB200_STREAM_UMMA_MIN_M", 9);
     return v;
 }
 static inline int64_t ru(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
@@ -911,9 +908,9 @@ static int stream_umma(const void* x, int x_dtype, int64_t M, int64_t K, int64_t
     p.layers = layers; p.stride_act_rows = M; p.stride_sb = stride_sb; p.stride_out = stride_out;
     p.n_peers = peers ? n_peers : 0;
     for (int r = 0; r < p.n_peers; ++r) p.peers[r] = peers[r];
-    { const char* e = getenv("TB200_GEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
+    p.dbg = (int)tb_knob("TB200_GEMM_DBG", 0);
     // the GEMM's prologue and launch latency overlap the quantiser (single quantiser launch directly before it)
-    static const int pdl_env = getenv("TB200_STREAM_UMMA_PDL") ? atoi(getenv("TB200_STREAM_UMMA_PDL")) : 1;
+    static const int pdl_env = (int)tb_knob("TB200_STREAM_UMMA_PDL", 1);
     p.pdl = (pdl_env && (layers == 1 || stride_x == M * ldx)) ? 1 : 0;
     return gemm_ts_launch(q_x, ldq, packed, ld_packed, p, out_dtype, s, M, stride_packed);
 }

@@ -47,7 +47,7 @@ extern "C" int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64
     TB_REQUIRE(workspace && (uintptr_t)workspace % 256 == 0, "linear_forward: workspace must be non-null and 256-byte aligned");
     LinearWs ws = carve_ws(workspace, M, K);
     // measured on B200 (4096 -> 11008): two 8-token GEMV passes beat the tcgen05 GEMM's fixed cost, four do not
-    static const int gemv_max_env = getenv("TB200_GEMV_MAX_M") ? atoi(getenv("TB200_GEMV_MAX_M")) : TB200_LINEAR_GEMV_M;
+    static const int gemv_max_env = (int)tb_knob("TB200_GEMV_MAX_M", TB200_LINEAR_GEMV_M);
     if (M <= gemv_max_env) {
         int rc = tb200_quant_act_i8(x, x_dtype, M, K, ldx, ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, TB200_QLAYOUT_GEMM, stream);
         if (rc) return rc;

@@ -372,9 +372,9 @@ extern "C" int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K
     const size_t es = dtype_size(dtype);
     const bool vec_ok = ((uintptr_t)x % 16 == 0) && ((ldx * es) % 16 == 0);
     // few rows: one CTA per row (the warp-per-row kernel would leave most SMs idle and is latency-bound per row)
-    static const int64_t warp_min_rows = getenv("TB200_QUANT_WARP_MIN_ROWS") ? atoll(getenv("TB200_QUANT_WARP_MIN_ROWS")) : 4 * (int64_t)sm_count();
+    const int64_t warp_min_rows = tb_knob("TB200_QUANT_WARP_MIN_ROWS", 4 * (int64_t)sm_count());
     const int64_t groups = ldq >> 4;
-    static const int fast_env = getenv("TB200_QUANT_FAST") ? atoi(getenv("TB200_QUANT_FAST")) : 1;
+    static const int fast_env = (int)tb_knob("TB200_QUANT_FAST", 1);
     if (fast_env && vec_ok && ldq == K && (K == 1024 || K == 2048 || K == 4096) && M >= warp_min_rows) {
         cudaStream_t st = (cudaStream_t)stream;
         if (K == 1024) { TB_DISPATCH_DTYPE(dtype, T, (launch_quant_fast<T, 2>((const T*)x, M, ldx, q_x, s_x, sum_qx, layout, st))); }

@@ -65,6 +65,53 @@ def _require_cuda(x):
 
 
 # --------------------------------------------------------------------------- layers
+class _Touch:
+    """Write counter shared by a TrackedParameter and the layer that caches its packed form."""
+    __slots__ = ("n",)
+
+    def __init__(self):
+        self.n = 0
+
+
+class TrackedParameter(nn.Parameter):
+    """``nn.Parameter`` whose ``.data`` accesses are observable.
+
+    The reference mutates latent weights through ``.data`` (``p.data[:] = v`` when a checkpoint is loaded by
+    parameter name, convert.py:76-78; ``weights.data = ...`` in linear_to_quantized and clip_binary_weights,
+    binary/modules.py:226,261,292, binary/utils.py:77).  ``.data`` returns an alias with its OWN autograd version
+    counter, so such writes never bump ``weights._version`` and a cached packed copy would silently go stale.
+    Here every ``.data`` read or assignment bumps a counter that is part of the cache key, so the next forward
+    re-packs (conservatively: a read-only ``.data`` access costs one re-pack).  In-place ops on the parameter itself
+    (optimiser steps, ``load_state_dict``) are caught by ``_version`` as before.  Not covered: writing through an
+    alias obtained BEFORE a forward and kept across it (``d = p.data; layer(x); d[:] = v``) -- call
+    ``invalidate_packed()`` for that."""
+
+    def __new__(cls, data=None, requires_grad=True):
+        if data is None:
+            data = torch.empty(0)
+        p = torch.Tensor._make_subclass(cls, data, requires_grad)
+        p._tb_touch = _Touch()
+        return p
+
+    @property
+    def data(self):
+        self._tb_touch.n += 1
+        return torch.Tensor.data.__get__(self)
+
+    @data.setter
+    def data(self, value):
+        self._tb_touch.n += 1
+        torch.Tensor.data.__set__(self, value)
+
+    def __deepcopy__(self, memo):
+        r = type(self)(torch.Tensor.data.__get__(self).clone(memory_format=torch.preserve_format), self.requires_grad)
+        memo[id(self)] = r
+        return r
+
+    def __reduce_ex__(self, proto):
+        return (TrackedParameter, (torch.Tensor.data.__get__(self), self.requires_grad))
+
+
 class _PackedQuantLinear(nn.Module):
     """Shared machinery: latent fp weights + cached 2-bit packed form + fused kernels."""
 
@@ -75,26 +122,40 @@ class _PackedQuantLinear(nn.Module):
     def __init__(self, in_features: int, out_features: int, bias: bool = True, max_val=100.0):
         super().__init__()
         self.in_features, self.out_features = in_features, out_features
-        self.weights = nn.Parameter(torch.randn(out_features, in_features))
+        self.weights = TrackedParameter(torch.randn(out_features, in_features))
         self.bias = nn.Parameter(torch.randn(out_features)) if bias else None
         if self._has_scale:
             self.scale = nn.Parameter(torch.full((out_features,), 1.0))
         self.maxval = abs(max_val)
         self.act_quant = True
-        self._packed = None
+        # the packed weights are a BUFFER: they follow .to()/.cuda() with the module; not part of the state dict (the
+        # reference's checkpoint keys are weights / bias / scale only) until freeze() makes them the deployed form
+        self.register_buffer("_packed", None, persistent=False)
         self._packed_key = None
         self._frozen = False
+        self._released = False
 
     # -- packed-weight cache ------------------------------------------------------------
     def _key(self):
         w = self.weights
-        return (w.data_ptr(), w._version, tuple(w.shape), w.dtype, w.device)
+        try:
+            version = w._version
+        except RuntimeError:           # parameters created under torch.inference_mode() have no version counter
+            version = -1
+        touch = getattr(w, "_tb_touch", None)
+        return (w.data_ptr() if w.numel() else 0, version, touch.n if touch is not None else -1,
+                tuple(w.shape), w.dtype, w.device)
 
     def invalidate_packed(self):
-        """Call after mutating ``weights.data`` in place (``.data`` writes do not bump the
-        autograd version counter, so they cannot be detected)."""
+        """Force a re-pack on the next forward.  Needed only for writes this module cannot see (see
+        TrackedParameter); ``.data`` writes, in-place ops, ``load_state_dict`` and ``.to()`` are tracked."""
+        if self._released:
+            raise TernaryB200Error("the latent weights of this layer were released by freeze(release_latent=True); "
+                                   "it can no longer be re-packed")
         self._packed_key = None
         self._frozen = False
+        if "_packed" in self._buffers:
+            self._non_persistent_buffers_set.add("_packed")
 
     def packed_weights(self) -> torch.Tensor:
         """uint8 ``[out_features, pitch]`` in the reference's format C; rebuilt when stale."""
@@ -102,18 +163,36 @@ class _PackedQuantLinear(nn.Module):
             return self._packed
         key = self._key()
         if self._packed is None or self._packed_key != key:
-            self._packed = ops.quantize_pack(self.weights.detach(), self._mode)
+            if self._released:
+                raise TernaryB200Error("latent weights were released; the packed weights are missing")
+            self._packed = ops.quantize_pack(torch.Tensor.data.__get__(self.weights), self._mode)
             self._packed_key = key
         return self._packed
 
     def freeze(self, release_latent: bool = False):
-        """Pack now and stop checking for weight updates (deployment).  ``release_latent``
-        additionally drops the latent fp weights (the module can then no longer train)."""
+        """Pack now and stop checking for weight updates (deployment).  The packed weights become a persistent
+        buffer (saved by ``state_dict()`` as ``_packed``, restored by ``load_state_dict``).  ``release_latent``
+        additionally drops the latent fp weights (the module can then no longer train or re-pack)."""
         self.packed_weights()
         self._frozen = True
+        self._non_persistent_buffers_set.discard("_packed")
         if release_latent:
             self.weights = nn.Parameter(torch.empty(0, device=self._packed.device), requires_grad=False)
+            self._released = True
         return self
+
+    def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys, error_msgs):
+        pk = state_dict.get(prefix + "_packed")
+        if pk is not None and not self._frozen:
+            # a checkpoint of a frozen layer: adopt its deployed form
+            self._packed = torch.empty_like(pk, device=self.weights.device if self._packed is None else self._packed.device)
+            self._frozen = True
+            self._non_persistent_buffers_set.discard("_packed")
+            w = state_dict.get(prefix + "weights")
+            if w is not None and w.numel() == 0:
+                self.weights = nn.Parameter(torch.empty(0, device=self._packed.device), requires_grad=False)
+                self._released = True
+        super()._load_from_state_dict(state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys, error_msgs)
 
     def codes(self) -> torch.Tensor:
         """int8 ``[out_features, in_features]`` quantised weights (ops.unpack_ternary)."""
@@ -141,6 +220,9 @@ class _PackedQuantLinear(nn.Module):
             raise TernaryB200Error("ternary_vllm_b200 layers run on CUDA (sm_100a) only; there is no CPU fallback")
         scale = self.scale if self._has_scale else None
         pw = self.packed_weights()
+        if pw.device != x.device:
+            raise TernaryB200Error(f"packed weights live on {pw.device} but the input is on {x.device}; move the "
+                                   "layer with .to() (the packed buffer follows the module)")
         if not self.act_quant:
             x2 = x.reshape(-1, x.shape[-1])
             if x2.shape[0] > ops.L.GEMV_MAX_M:

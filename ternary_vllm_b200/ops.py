@@ -200,7 +200,8 @@ def gemv(x, packed, scale, bias, clip_val, out_dtype=None, debug=False, pdl=Fals
 
 
 def gemv_q(q_x, s_x, sum_qx, K, packed, scale, bias, clip_val, out_dtype=torch.bfloat16, debug=False, pdl=False):
-    """Decode GEMV on activations pre-quantised with ``quant_act_i8(layout=2)`` (4 tokens per pass)."""
+    """Decode GEMV on activations pre-quantised with ``quant_act_i8(layout=1)`` (the kperm order; 8 tokens per pass
+    over the weights)."""
     _cuda(q_x, s_x, sum_qx, packed, scale, bias)
     M, N = q_x.shape[0], packed.shape[0]
     scale = _f32_or_none(scale, N, q_x.device)
@@ -249,14 +250,25 @@ def gemm_i8(q_x, s_x, sum_qx, K, packed, scale, bias, clip_val, out_dtype=torch.
 
 
 _ws_cache: dict = {}
+_ws_retired: list = []
 
 
 def _workspace(M: int, K: int, device) -> torch.Tensor:
+    """Per-(device, stream) scratch for the activation quantiser.  A workspace that has been handed out is NEVER freed:
+    a CUDA graph captured through ternary_matmul has its address baked into its kernel nodes, so outgrown generations
+    are retired to a keep-alive list instead of being released (growth is geometric, so at most ~2x the largest need
+    stays allocated).  While a stream is capturing, a workspace private to that capture is allocated from the graph's
+    own memory pool, so replays never alias an eager call's scratch."""
     need = L.lib().tb200_linear_workspace(M, K)
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    stream = torch.cuda.current_stream(device)
+    if torch.cuda.is_current_stream_capturing():
+        return torch.empty((max(need, 256),), dtype=torch.uint8, device=device)      # owned by the graph's private pool
+    key = (device.index, stream.cuda_stream)
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < need:
-        ws = torch.empty((max(need, 1 << 20),), dtype=torch.uint8, device=device)
+        if ws is not None:
+            _ws_retired.append(ws)
+        ws = torch.empty((max(need, 1 << 20, 2 * (ws.numel() if ws is not None else 0)),), dtype=torch.uint8, device=device)
         _ws_cache[key] = ws
     return ws
 
@@ -264,7 +276,13 @@ def _workspace(M: int, K: int, device) -> torch.Tensor:
 def ternary_matmul(x: torch.Tensor, pw: torch.Tensor, scale, bias, clip_val: float, out_dtype=None, out=None) -> torch.Tensor:
     """``ops.ternary_matmul(x, pw, scale, bias, clip_val)`` (impl/tf/moondream/ternary.py:279-281):
     ``clip((x @ unpack(pw)^T) * scale + bias, +-clip_val)`` for ``x [..., K]`` and ``pw [N, ld]``.
-    M <= 16 tokens run the HBM-bound GEMV (8 tokens per pass), larger M the tcgen05 kind::i8 GEMM."""
+    M <= 8 tokens: one GEMV launch with the activation quantisation fused in its prologue; M <= 16: quantiser +
+    two 8-token GEMV passes; larger M: quantiser + the tcgen05 kind::i8 GEMM (``tb200_linear_forward``).
+    Under ``torch.compile`` the call is routed through the registered custom op ``ternary_b200::ternary_matmul``
+    (an opaque node: no graph break)."""
+    if out is None and torch.compiler.is_compiling():
+        return torch.ops.ternary_b200.ternary_matmul(x, pw, scale, bias, float(clip_val),
+                                                     x.dtype if out_dtype is None else out_dtype)
     _cuda(x, pw, scale, bias)
     K = x.shape[-1]
     N = pw.shape[0]
@@ -358,3 +376,50 @@ def gemv_stream_tp(xs, packed, scale, bias, clip_val, peer_ptrs, n_peers: int, o
 
 def launch_count() -> int:
     return int(L.lib().tb200_launch_count())
+
+
+# ------------------------------------------------------------------ torch.library registration
+# The C-ABI calls above are invisible to torch.compile / export; the ops below wrap them as opaque custom ops with
+# shape-only ("fake") implementations, so a compiled model keeps the layer as ONE node instead of graph-breaking.
+@torch.library.custom_op("ternary_b200::ternary_matmul", mutates_args=(), device_types="cuda")
+def _ternary_matmul_op(x: torch.Tensor, pw: torch.Tensor, scale: torch.Tensor | None, bias: torch.Tensor | None,
+                       clip_val: float, out_dtype: torch.dtype) -> torch.Tensor:
+    return ternary_matmul(x, pw, scale, bias, clip_val, out_dtype=out_dtype)
+
+
+@_ternary_matmul_op.register_fake
+def _(x, pw, scale, bias, clip_val, out_dtype):
+    return x.new_empty((*x.shape[:-1], pw.shape[0]), dtype=out_dtype)
+
+
+@torch.library.custom_op("ternary_b200::quantize_pack", mutates_args=(), device_types="cuda")
+def _quantize_pack_op(w: torch.Tensor, mode: str) -> torch.Tensor:
+    return quantize_pack(w, mode)
+
+
+@_quantize_pack_op.register_fake
+def _(w, mode):
+    return w.new_empty((w.shape[0], packed_pitch(w.shape[1])), dtype=torch.uint8)
+
+
+@torch.library.custom_op("ternary_b200::unpack", mutates_args=(), device_types="cuda")
+def _unpack_op(packed: torch.Tensor, K: int) -> torch.Tensor:
+    return unpack(packed, K)
+
+
+@_unpack_op.register_fake
+def _(packed, K):
+    return packed.new_empty((packed.shape[0], K), dtype=torch.int8)
+
+
+@torch.library.custom_op("ternary_b200::quant_act_i8", mutates_args=(), device_types="cuda")
+def _quant_act_op(x: torch.Tensor, layout: int) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    return quant_act_i8(x, layout=layout)
+
+
+@_quant_act_op.register_fake
+def _(x, layout):
+    M, K = x.shape
+    ldq = (K + 4095) // 4096 * 4096 if layout == 2 else (K + 15) // 16 * 16
+    return (x.new_empty((M, ldq), dtype=torch.int8), x.new_empty((M,), dtype=torch.float32),
+            x.new_empty((M,), dtype=torch.int32))

@@ -67,7 +67,12 @@ class TPShardedLinear(nn.Module):
         rank = dist.get_rank(group) if dist.is_initialized() else 0
         a, b = shard_rows(layer.out_features, world, rank)
         w = layer.weights.detach()[a:b]
-        packed = ops.quantize_pack(w.contiguous(), layer._mode) if matmul is None else w.contiguous()
+        if matmul is not None:
+            packed = w.contiguous()
+        elif b > a:
+            packed = ops.quantize_pack(w.contiguous(), layer._mode)
+        else:       # empty trailing shard (N not a multiple of world x 16): nothing to pack, the rank only gathers
+            packed = torch.empty((0, ops.packed_pitch(layer.in_features)), dtype=torch.uint8, device=w.device)
         scale = layer.scale.detach()[a:b].float().contiguous() if getattr(layer, "scale", None) is not None else None
         bias = layer.bias.detach()[a:b].float().contiguous() if layer.bias is not None else None
         return cls(packed, scale, bias, layer.in_features, layer.out_features, layer.maxval, group, matmul)
@@ -118,26 +123,40 @@ class TPShardedLinear(nn.Module):
         self._peer_turn = 0
         return self
 
-    def forward_peer(self, x2: torch.Tensor) -> torch.Tensor:
+    def forward_peer(self, x2: torch.Tensor, alias_ok: bool = False) -> torch.Tensor:
+        """Fused peer gather.  Every rank MUST take this path together (the barrier is collective): a rank whose row
+        block is empty (N not a multiple of world x 16) skips the kernel launch but still takes the barrier.
+        The result lives in one of two internal symmetric buffers that peers overwrite TWO calls later; by default
+        a copy is returned (tiny for <= 32 tokens).  ``alias_ok=True`` returns the view itself: valid only until the
+        second following call on this layer."""
         M, K = x2.shape
         i = self._peer_turn
         self._peer_turn ^= 1
         buf, hdl, ptrs = self._peer_bufs[i], self._peer_hdls[i], self._peer_ptrs[i]
         n_local = self.stop - self.start
-        ws = ops._workspace(M, K, x2.device)
-        with torch.cuda.device(x2.device):
-            L.check(L.lib().tb200_linear_forward_tp(
-                x2.data_ptr(), ops._dt(x2), M, K, x2.stride(0), self.packed.data_ptr(), self.packed.stride(0), n_local,
-                ops._ptr(self.scale), ops._ptr(self.bias), float(self.maxval), ptrs, self.world,
-                ops._DT[self._peer_dtype], self._peer_ld, ws.data_ptr(), ops._stream(x2)), "linear_forward_tp")
+        if n_local > 0:
+            ws = ops._workspace(M, K, x2.device)
+            with torch.cuda.device(x2.device):
+                L.check(L.lib().tb200_linear_forward_tp(
+                    x2.data_ptr(), ops._dt(x2), M, K, x2.stride(0), self.packed.data_ptr(), self.packed.stride(0), n_local,
+                    ops._ptr(self.scale), ops._ptr(self.bias), float(self.maxval), ptrs, self.world,
+                    ops._DT[self._peer_dtype], self._peer_ld, ws.data_ptr(), ops._stream(x2)), "linear_forward_tp")
         hdl.barrier(channel=0)                   # every rank's block has landed in every buffer
-        return buf[:M, : self.out_features]
+        y = buf[:M, : self.out_features]
+        return y if alias_ok else y.clone()
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def uses_peer_gather(self, x2: torch.Tensor) -> bool:
+        """Path choice of ``forward``: depends only on rank-uniform facts (never on this rank's shard size), so all
+        ranks issue the same collective."""
+        return bool(getattr(self, "_peer_bufs", None)) and x2.shape[0] <= min(self._peer_tokens, L.GEMV_MAX_M) \
+            and x2.is_cuda and x2.dtype == self._peer_dtype
+
+    def forward(self, x: torch.Tensor, alias_ok: bool = False) -> torch.Tensor:
+        """Full ``[..., N]`` output on every rank.  <= 32 tokens with ``enable_peer_gather``: the fused NVLink gather
+        (returns a fresh tensor unless ``alias_ok``, see ``forward_peer``); otherwise NCCL ``all_gather_into_tensor``."""
         x2 = x.reshape(-1, x.shape[-1])
-        if getattr(self, "_peer_bufs", None) and x2.shape[0] <= min(self._peer_tokens, L.GEMV_MAX_M) \
-                and x2.is_cuda and x2.dtype == self._peer_dtype and self.stop > self.start:
-            y = self.forward_peer(x2 if x2.stride(-1) == 1 else x2.contiguous())
+        if self.uses_peer_gather(x2):
+            y = self.forward_peer(x2 if x2.stride(-1) == 1 else x2.contiguous(), alias_ok)
         else:
             y = self.gather(self.local_forward(x2))
         return y.reshape(*x.shape[:-1], self.out_features)
@@ -181,7 +200,10 @@ class TPShardedStream(nn.Module):
         self._turn = 0
         self._ws = None
 
-    def forward(self, xs: torch.Tensor, barrier: bool = True) -> torch.Tensor:
+    def forward(self, xs: torch.Tensor, barrier: bool = True, alias_ok: bool = False) -> torch.Tensor:
+        """``[R, M, N]`` gathered outputs.  They live in one of two internal symmetric buffers that peers overwrite TWO
+        calls later: a copy is returned unless ``alias_ok=True`` (then the view is valid until the second following
+        call; what a consumer that reads the result immediately, or a benchmark, wants)."""
         M, K = xs.shape[-2], xs.shape[-1]
         assert M <= self.max_tokens and K == self.in_features
         i = self._turn
@@ -195,4 +217,5 @@ class TPShardedStream(nn.Module):
                                self.ld, self.max_tokens * self.ld, workspace=self._ws)
         if barrier:
             self._hdls[i].barrier(channel=0)             # every rank's blocks of every layer have landed in every buffer
-        return self._bufs[i][:, :M, : self.out_features]
+        y = self._bufs[i][:, :M, : self.out_features]
+        return y if alias_ok else y.clone()

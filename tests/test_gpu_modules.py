@@ -172,3 +172,127 @@ def test_quantize_moondream(cuda, capsys):
     with torch.no_grad():
         y = h[1].mlp.fc2(torch.nn.functional.gelu(h[1].mlp.fc1(torch.randn(5, 64, device=cuda))))
     assert y.shape == (5, 64) and torch.isfinite(y).all()
+
+
+# ---- the packed-weight cache under the reference's own write idioms -----------------------
+@pytest.mark.parametrize("idiom", ["data_slice", "data_copy", "data_assign", "inplace", "load_state_dict", "ref_clip"])
+def test_packed_cache_follows_reference_write_idioms(cuda, idiom):
+    """forward -> mutate the latent weights the way the reference does -> forward must use the NEW codes.
+    `p.data[:] = v` is convert.py:78 (checkpoint load by parameter name); `weights.data = ...` is
+    binary/modules.py:226,261,292 and binary/utils.py:77.  None of the .data forms bumps weights._version."""
+    torch.manual_seed(5)
+    layer = tb.ScaledTernaryLinear(256, 96).to(cuda)
+    x = torch.randn(3, 256, device=cuda, dtype=torch.bfloat16)
+    with torch.no_grad():
+        y0 = layer(x).clone()
+    w2 = torch.randn(96, 256, device=cuda).clip(-1, 1)
+    if idiom == "data_slice":
+        for name, p in layer.named_parameters():              # convert.py:76-78
+            if name == "weights":
+                p.data[:] = w2
+    elif idiom == "data_copy":
+        layer.weights.data.copy_(w2)
+    elif idiom == "data_assign":
+        layer.weights.data = w2.clone()
+    elif idiom == "inplace":
+        with torch.no_grad():
+            layer.weights.copy_(w2)
+    elif idiom == "load_state_dict":
+        sd = layer.state_dict()
+        sd["weights"] = w2.clone()
+        layer.load_state_dict(sd)
+    else:                                                      # the reference's clip_binary_weights body verbatim
+        layer.weights.data = (layer.weights.data * 3).clip(-1, 1)
+        w2 = layer.weights.detach().clone()
+    with torch.no_grad():
+        y1 = layer(x)
+    assert np.array_equal(layer.codes().cpu().numpy(), ref_int8.codes_of(w2.cpu().numpy()))
+    want = oracle_layer(layer, x, "ternary")
+    assert np.all(np.abs(y1.float().cpu().numpy() - want) <= 2.0 ** -7 * np.abs(want) + 1e-5)
+    assert not torch.equal(y0, y1)
+
+
+def test_freeze_state_dict_round_trip_and_release(cuda):
+    torch.manual_seed(6)
+    layer = tb.ScaledTernaryLinear(128, 64).to(cuda)
+    x = torch.randn(2, 128, device=cuda, dtype=torch.bfloat16)
+    assert sorted(layer.state_dict()) == ["bias", "scale", "weights"]          # the reference's checkpoint keys only
+    with torch.no_grad():
+        y = layer(x)
+    layer.freeze(release_latent=True)
+    sd = layer.state_dict()
+    assert "_packed" in sd and sd["weights"].numel() == 0
+    assert torch.equal(layer(x), y)
+    with pytest.raises(tb.TernaryB200Error):
+        layer.invalidate_packed()
+    fresh = tb.ScaledTernaryLinear(128, 64).to(cuda)
+    fresh.load_state_dict(sd)
+    assert torch.equal(fresh(x), y) and fresh._frozen and fresh._packed.device == x.device
+
+
+def test_torch_compile_keeps_the_layer_as_one_op(cuda):
+    """the ops are registered with torch.library, so torch.compile captures the layer without a graph
+    break (fullgraph=True would raise otherwise)."""
+    torch.manual_seed(8)
+    layer = tb.ScaledTernaryLinear(256, 128).to(cuda).eval()
+    layer.freeze()
+    x = torch.randn(4, 256, device=cuda, dtype=torch.bfloat16)
+    want = layer(x)
+    fn = torch.compile(lambda t: layer(t) * 2.0, backend="aot_eager", fullgraph=True)
+    got = fn(x)
+    assert torch.equal(got, want * 2.0)
+    y = torch.ops.ternary_b200.ternary_matmul(x, layer.packed_weights(), layer.scale.detach(), layer.bias.detach(),
+                                              100.0, torch.bfloat16)
+    assert torch.equal(y, want)
+    torch.library.opcheck(torch.ops.ternary_b200.ternary_matmul.default,
+                          (x, layer.packed_weights(), layer.scale.detach(), layer.bias.detach(), 100.0, torch.bfloat16),
+                          test_utils=("test_schema", "test_faketensor"))
+
+
+def test_two_host_threads_two_streams(cuda):
+    """The C ABI is called from two host threads on two streams at once (every kernel family, first use included:
+    the per-device dynamic-shared-memory opt-in and tensor-map caches are shared state)."""
+    import threading
+    torch.manual_seed(9)
+    layers = [tb.ScaledTernaryLinear(1024, 512).to(cuda).eval().freeze() for _ in range(2)]
+    xs = {M: torch.randn(M, 1024, device=cuda, dtype=torch.bfloat16) for M in (1, 12, 200)}
+    with torch.no_grad():
+        want = [{M: l(x).clone() for M, x in xs.items()} for l in layers]
+    torch.cuda.synchronize()
+    errs = []
+
+    def work(i):
+        try:
+            st = torch.cuda.Stream(cuda)
+            with torch.cuda.stream(st), torch.no_grad():
+                for _ in range(20):
+                    for M, x in xs.items():
+                        x.record_stream(st)
+                        if not torch.equal(layers[i](x), want[i][M]):
+                            errs.append((i, M))
+            st.synchronize()
+        except Exception as e:      # noqa: BLE001
+            errs.append(repr(e))
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+
+
+def test_second_device_if_present(cuda):
+    """Per-device state (SM count, dynamic shared-memory opt-in): a layer on cuda:1 after one on cuda:0."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU")
+    torch.manual_seed(10)
+    a = tb.ScaledTernaryLinear(4096, 512).to("cuda:0").eval()
+    b = copy_to = tb.ScaledTernaryLinear(4096, 512).to("cuda:1").eval()
+    b.load_state_dict(a.state_dict())
+    for M in (1, 12, 300):
+        x = torch.randn(M, 4096, dtype=torch.bfloat16)
+        with torch.no_grad():
+            ya, yb = a(x.to("cuda:0")), b(x.to("cuda:1"))
+        assert torch.equal(ya.cpu(), yb.cpu())
+    with pytest.raises(tb.TernaryB200Error):
+        a.freeze()
+        a(torch.randn(1, 4096, dtype=torch.bfloat16, device="cuda:1"))

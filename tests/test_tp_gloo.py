@@ -60,7 +60,7 @@ def _worker(rank, world, port, N, K, M, ret):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("N,K,M", [(100, 32, 3), (48, 64, 1), (17, 16, 2)])
+@pytest.mark.parametrize("N,K,M", [(100, 32, 3), (48, 64, 1), (17, 16, 2), (16, 16, 2)])      # (16, .): rank 1 owns no rows
 def test_tp_all_gather_world2(N, K, M):
     world = 2
     mgr = mp.Manager()
@@ -68,3 +68,12 @@ def test_tp_all_gather_world2(N, K, M):
     mp.spawn(_worker, args=(world, _free_port(), N, K, M, ret), nprocs=world, join=True)
     assert len(ret) == world and all(v[0] for v in ret.values()), dict(ret)
     assert ret[0][1] == 0 and ret[0][2] == ret[1][1] and ret[1][2] == N
+
+
+def test_peer_gather_path_choice_is_rank_uniform():
+    """the fused-gather path must not depend on whether THIS rank's shard is empty (an NCCL all-gather on
+    one rank against a symmetric-memory barrier on the others hangs)."""
+    import inspect
+    from ternary_vllm_b200.parallel import TPShardedLinear
+    src = inspect.getsource(TPShardedLinear.uses_peer_gather)
+    assert "self.stop" not in src and "self.start" not in src
