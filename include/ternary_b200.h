@@ -208,6 +208,40 @@ int tb200_gemv_stream_host(const void* x_host, int x_dtype, int64_t M, int64_t K
                            void* out_host, int out_dtype, int count,
                            void* dev_x, void* dev_out, void* workspace, void* stream);
 
+/* ---- a CHAIN of dependent layers in one launch (the fused MLP block) -----------------------
+ * The reference wires the layer as fc1 -> gelu_new -> fc2 (impl/tf/moondream/layers.py:32-43) and passes the
+ * activation INTO the ternary layer, applied after the clip (impl/tf/moondream/ternary.py:245-246,298-299;
+ * utils/conversion.py:185-196):   h_{l+1} = act_l( clip((q(h_l) @ unpack(pw_l)^T) * s_x * scale_l + bias_l) ).
+ * tb200_chain_forward runs n such layers, each consuming the previous one's output, in ONE persistent launch for
+ * decode shapes (M <= TB200_CHAIN_MAX_M tokens): the weight stream never stops at a layer boundary, the boundary is
+ * a flag in global memory, and every layer's input is quantised per token to int8 inside the kernel.  Activations
+ * between layers are kept in x's dtype (the reference keeps x.dtype); the activation function is evaluated in fp32 on
+ * that stored precision. */
+#define TB200_ACT_NONE      0
+#define TB200_ACT_GELU_TANH 1 /* gelu_new / keras gelu(approximate=True): 0.5x(1+tanh(sqrt(2/pi)(x+0.044715x^3))) */
+#define TB200_ACT_RELU      2
+#define TB200_CHAIN_MAX_LAYERS 128
+#define TB200_CHAIN_MAX_M 8
+#define TB200_CHAIN_CTRL_BYTES 16640 /* control block at the start of the workspace: 128 B + one 128-byte line per layer */
+typedef struct tb200_chain_layer {
+    const uint8_t* packed;   /* [N, ld_packed] format C, device */
+    int64_t ld_packed, N, K; /* K must equal the previous layer's N */
+    const float* scale;      /* [N] f32 or NULL, device */
+    const float* bias;       /* [N] f32 or NULL, device */
+    float clip_val;
+    int32_t act;             /* TB200_ACT_*: applied after the clip */
+} tb200_chain_layer;
+/* A plan is a caller-owned blob: build it ONCE on the host (tb200_chain_plan_bytes(n) bytes; holds the layers' TMA
+ * descriptors), copy it to 256-byte aligned device memory, pass both copies to tb200_chain_forward.  *workspace_bytes
+ * receives the size of the device workspace (inter-layer activations + the control block); the workspace belongs
+ * to this plan and its first TB200_CHAIN_CTRL_BYTES bytes must be ZERO before the first call (the kernel maintains them afterwards). */
+size_t tb200_chain_plan_bytes(int n_layers);
+int tb200_chain_plan_build(const tb200_chain_layer* layers, int n_layers, int64_t M_max, int act_elem_size,
+                           void* plan_host, size_t* workspace_bytes);
+/* x [M, ldx] x_dtype -> out [M, ldo] out_dtype (N of the last layer).  flags: TB200_FLAG_PDL as for tb200_gemv. */
+int tb200_chain_forward(const void* plan_host, const void* plan_dev, const void* x, int x_dtype, int64_t M, int64_t ldx,
+                        void* out, int out_dtype, int64_t ldo, void* workspace, int flags, void* stream);
+
 /* Prefill shape: tcgen05.mma kind::i8, TMEM accumulators.  Takes PRE-QUANTISED activations
  * from tb200_quant_act_i8(kperm=1): q_x int8 [M, ldq], s_x [M], sum_qx [M].
  * Requires ldq % 16 == 0, ld_packed % 16 == 0, 16-byte aligned base pointers. */

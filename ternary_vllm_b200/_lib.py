@@ -10,13 +10,22 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libternary_b200.so")
+# TB200_LIB selects another build of the same ABI (the experiment library of `make ABLATE=1`); never a fallback
+LIB_PATH = os.environ.get("TB200_LIB") or os.path.join(_HERE, "libternary_b200.so")
 
 TB200_F32, TB200_BF16, TB200_F16 = 0, 1, 2
 Q_TERNARY, Q_SIGN, Q_STEP = 0, 1, 2
 FMT_A, FMT_B, FMT_C = 0, 1, 2
 GEMV_MAX_M = 32
 FLAG_PDL = 1
+ACT_NONE, ACT_GELU_TANH, ACT_RELU = 0, 1, 2
+CHAIN_MAX_M, CHAIN_MAX_LAYERS = 8, 128
+
+
+class ChainLayerDesc(C.Structure):
+    """``tb200_chain_layer`` of include/ternary_b200.h"""
+    _fields_ = [("packed", C.c_void_p), ("ld_packed", C.c_int64), ("N", C.c_int64), ("K", C.c_int64),
+                ("scale", C.c_void_p), ("bias", C.c_void_p), ("clip_val", C.c_float), ("act", C.c_int32)]
 
 ERRORS = {-1: "TB200_EINVAL", -2: "TB200_ECUDA", -3: "TB200_ENODEV", -4: "TB200_ENOTSUP"}
 
@@ -70,6 +79,9 @@ SIGNATURES = {
                                     _vp, _vp, _i64, _f32, _vp, _i32, _i32, _i64, _i64, _i32, _vp, _vp]),
     "tb200_gemv_stream_host": (_i32, [_vp, _i32, _i64, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _i64, _f32,
                                       _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "tb200_chain_plan_bytes": (_sz, [_i32]),
+    "tb200_chain_plan_build": (_i32, [_vp, _i32, _i64, _i32, _vp, _vp]),
+    "tb200_chain_forward": (_i32, [_vp, _vp, _vp, _i32, _i64, _i64, _vp, _i32, _i64, _vp, _i32, _vp]),
     "tb200_gemm_i8": (_i32, [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
                              _vp, _i32, _i64, _vp, _vp]),
     "tb200_linear_workspace": (_sz, [_i64, _i64]),

@@ -281,7 +281,8 @@ def ternary_matmul(x: torch.Tensor, pw: torch.Tensor, scale, bias, clip_val: flo
     Under ``torch.compile`` the call is routed through the registered custom op ``ternary_b200::ternary_matmul``
     (an opaque node: no graph break)."""
     if out is None and torch.compiler.is_compiling():
-        return torch.ops.ternary_b200.ternary_matmul(x, pw, scale, bias, float(clip_val),
+        return torch.ops.ternary_b200.ternary_matmul(x, pw, None if scale is None else scale.detach(),
+                                                     None if bias is None else bias.detach(), float(clip_val),
                                                      x.dtype if out_dtype is None else out_dtype)
     _cuda(x, pw, scale, bias)
     K = x.shape[-1]
@@ -423,3 +424,78 @@ def _(x, layout):
     ldq = (K + 4095) // 4096 * 4096 if layout == 2 else (K + 15) // 16 * 16
     return (x.new_empty((M, ldq), dtype=torch.int8), x.new_empty((M,), dtype=torch.float32),
             x.new_empty((M,), dtype=torch.int32))
+
+
+# ------------------------------------------------------------------ a chain of dependent layers (fused MLP block)
+_ACTS = {None: L.ACT_NONE, "none": L.ACT_NONE, "gelu_new": L.ACT_GELU_TANH, "gelu_tanh": L.ACT_GELU_TANH,
+         "gelu_pytorch_tanh": L.ACT_GELU_TANH, "relu": L.ACT_RELU}
+
+
+class ChainPlan:
+    """Plan + workspace of ``tb200_chain_forward``: ``layers`` is a list of ``(packed [N, ld] uint8, scale [N] | None,
+    bias [N] | None, clip_val, activation)`` with ``activation`` in {None, "gelu_new", "relu"}; every layer consumes the
+    previous one's output (``K_l == N_{l-1}``).  The reference wires fc1 -> gelu_new -> fc2 this way
+    (impl/tf/moondream/layers.py:32-43; the activation is applied after the clip, ternary.py:245-246).
+    The plan keeps references to the tensors it points to.  Decode shapes only: ``M <= 8`` tokens per call."""
+
+    def __init__(self, layers, in_features: int, dtype=torch.bfloat16, max_tokens: int = L.CHAIN_MAX_M):
+        assert 1 <= len(layers) <= L.CHAIN_MAX_LAYERS and 1 <= max_tokens <= L.CHAIN_MAX_M
+        self.dtype, self.max_tokens, self.in_features = dtype, max_tokens, in_features
+        dev = layers[0][0].device
+        self._keep = []
+        descs = (L.ChainLayerDesc * len(layers))()
+        K = in_features
+        for i, (pw, scale, bias, clip_val, act) in enumerate(layers):
+            _cuda(pw, scale, bias)
+            assert pw.dtype == torch.uint8 and pw.dim() == 2 and pw.stride(1) == 1
+            N = pw.shape[0]
+            scale, bias = _f32_or_none(scale, N, dev), _f32_or_none(bias, N, dev)
+            self._keep += [pw, scale, bias]
+            descs[i] = L.ChainLayerDesc(pw.data_ptr(), pw.stride(0), N, K, _ptr(scale), _ptr(bias), float(clip_val), _ACTS[act])
+            K = N
+        self.out_features = K
+        nbytes = L.lib().tb200_chain_plan_bytes(len(layers))
+        host = torch.zeros(nbytes, dtype=torch.uint8)
+        ws_bytes = L.C.c_size_t(0)
+        esz = torch.empty((), dtype=dtype).element_size()
+        with torch.cuda.device(dev):
+            L.check(L.lib().tb200_chain_plan_build(descs, len(layers), max_tokens, esz, host.data_ptr(), L.C.byref(ws_bytes)),
+                    "chain_plan_build")
+        self.plan_host = host
+        self.plan_dev = host.to(dev)                          # cudaMalloc'ed: 256-byte aligned
+        self.workspace = torch.zeros(ws_bytes.value, dtype=torch.uint8, device=dev)     # control block zero before first use
+        self.n_layers = len(layers)
+
+    def hidden(self, layer: int, M: int) -> torch.Tensor:
+        """The inter-layer activations the last call left in the workspace: output of ``layer`` (not the last one),
+        ``[M, N_layer]`` in the plan's dtype, decoded from the kernel's flagged 8-byte words {value(s), flag}.  For
+        parity tests."""
+        import struct
+        base = 64 + 192 * layer
+        raw = bytes(self.plan_host[base + 128: base + 192].tolist())
+        N, = struct.unpack_from("<i", raw, 16)
+        pitch, = struct.unpack_from("<i", raw, 44)
+        off, = struct.unpack_from("<q", raw, 48)
+        words = self.workspace[off: off + M * pitch * 8].view(torch.int32).view(M, pitch, 2)
+        assert bool((words[:, : (N + 1) // 2 if self.dtype != torch.float32 else N, 1] == words[0, 0, 1]).all()), "stale flag"
+        vals = words[:, :, 0].contiguous()
+        if self.dtype == torch.float32:
+            return vals.view(torch.float32)[:, :N]
+        return vals.view(self.dtype).view(M, 2 * pitch)[:, :N]
+
+    def forward(self, x: torch.Tensor, out: torch.Tensor | None = None, out_dtype=None, pdl: bool = False) -> torch.Tensor:
+        _cuda(x)
+        assert x.dtype == self.dtype and x.shape[-1] == self.in_features
+        x2 = x.reshape(-1, self.in_features)
+        if x2.stride(-1) != 1:
+            x2 = x2.contiguous()
+        M = x2.shape[0]
+        if M > self.max_tokens:
+            raise TernaryB200Error(f"ChainPlan serves at most {self.max_tokens} tokens per call, got {M}")
+        if out is None:
+            out = torch.empty((M, self.out_features), dtype=out_dtype or x.dtype, device=x.device)
+        with torch.cuda.device(x.device):
+            L.check(L.lib().tb200_chain_forward(self.plan_host.data_ptr(), self.plan_dev.data_ptr(), x2.data_ptr(), _dt(x2), M,
+                                                x2.stride(0), out.data_ptr(), _DT[out.dtype], out.stride(0),
+                                                self.workspace.data_ptr(), L.FLAG_PDL if pdl else 0, _stream(x)), "chain_forward")
+        return out.reshape(*x.shape[:-1], self.out_features)
