@@ -26,37 +26,35 @@
 namespace tb200 {
 
 constexpr int CH_ROWS = 16, CH_SEG = 128, CH_TILE = 16 * 1024;
-constexpr int CH_MMA_WARPS = 8, CH_AUX = 3;     // 12 warps = 3 warpgroups: two of MMA warps, one of producer + aux warps
-constexpr int CH_WARP_PRODUCER = CH_MMA_WARPS, CH_WARP_AUX0 = CH_MMA_WARPS + 1;
-constexpr int CH_THREADS = (CH_MMA_WARPS + 1 + CH_AUX) * 32;
-constexpr int CH_MMA_THREADS = CH_MMA_WARPS * 32;
+constexpr int CH_DOT_WARPS = 16, CH_TEAM = 8, CH_AUX = 3;   // 20 warps = 5 warpgroups: four of dot-product warps, one of producer + aux warps
+constexpr int CH_WARP_PRODUCER = CH_DOT_WARPS, CH_WARP_AUX0 = CH_DOT_WARPS + 1;
+constexpr int CH_THREADS = (CH_DOT_WARPS + 1 + CH_AUX) * 32;
+constexpr int CH_DOT_THREADS = CH_DOT_WARPS * 32;
 constexpr int CH_MAX_STAGES = 12, CH_MAX_SLOTS = 8;
-constexpr int CH_SLOT_U4 = 4 * 32;                 // four K-partials (one team) x 32 lanes, uint4 each
-constexpr uint32_t CH_MAGIC = 0x7b200c42u;
-constexpr int CH_REPLICAS = 16;                    // copies of every inter-layer activation buffer
+constexpr int CH_CACHE = 3;                        // 16-element groups a thread keeps in registers between its two passes
+constexpr uint32_t CH_MAGIC = 0x7b200c43u;
 
 // device-side layer descriptor inside the plan blob (192 bytes, 64-byte aligned: the tensor map is used in place)
 struct ChainLayer {
     CUtensorMap map;                               // 128 B
     const float* scale; const float* bias;
     int32_t N, K, nks, row_blocks;
-    float clip_val; int32_t act, one_box, h_pitch; // h_pitch: flagged 8-byte WORDS per token of this layer's output buffer
-    int64_t h_off;                                 // byte offset of that buffer in the workspace (last layer: unused)
-    int64_t h_rep_stride;                          // words between the replicas of that buffer
+    float clip_val; int32_t act, one_box, h_pitch; // h_pitch: ELEMENTS per token of this layer's output buffer (N rounded up to 16)
+    int64_t h_off;                                 // byte offset of that buffer (two sets) in the workspace (last layer: unused)
+    int64_t h_set_stride;                          // bytes between the two sets (even / odd generation)
 };
 static_assert(sizeof(ChainLayer) == 192, "plan layout");
 struct ChainHeader {
     uint32_t magic, n_layers;
     int32_t max_nks, max_rb, M_max, esz;           // esz: bytes per inter-layer activation element
     int64_t ws_bytes;
-    int32_t replicas;
-    char pad[28];
+    char pad[32];
 };
 static_assert(sizeof(ChainHeader) == 64, "plan layout");
 // control block at the start of the workspace (zero before the first call; the kernel maintains it)
 // every layer's counter sits on its own 128-byte line (pollers of one layer do not queue behind arrivals of another)
 constexpr int CH_CNT_STRIDE = 32;
-struct ChainCtrl { uint32_t gen, done, pad[30]; uint32_t counter[TB200_CHAIN_MAX_LAYERS * CH_CNT_STRIDE]; };
+struct ChainCtrl { uint32_t gen, done, last_M, pad[29]; uint32_t counter[TB200_CHAIN_MAX_LAYERS * CH_CNT_STRIDE]; };
 constexpr size_t CH_CTRL_BYTES = TB200_CHAIN_CTRL_BYTES;
 static_assert(sizeof(ChainCtrl) <= CH_CTRL_BYTES, "control block");
 
@@ -64,31 +62,33 @@ struct ChainParams {
     const void* x; int64_t ldx;
     void* out; int64_t ldo; int out_dtype;
     uint8_t* ws;
-    int M, stages, nslots;
+    int stages, nslots, n_layers;
     uint32_t img_bytes;
     int pdl;
-    int inflight;         // tiles of one SM allowed to be outstanding in the memory system (0: the whole ring)
-    int replicas;         // copies of every inter-layer buffer (see the consumer side)
-    long long* trace;     // experiment build only: per CTA and layer, globaltimer stamps {enter, input ready, image built, last tile}
+    int gate;             // 1: one thread per CTA waits for the layer's row-block counter before the data words are read
+    long long* trace;     // experiment build only: per CTA and layer, time stamps (tools/chain_trace.py)
 };
 __device__ __forceinline__ long long chain_gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-#define CH_STAMP(l, k) do { if (kAblate && p.trace && ct == 0) p.trace[((int64_t)b * TB200_CHAIN_MAX_LAYERS + (l)) * 8 + (k)] = chain_gtimer(); } while (0)
-#define CH_STAMP_AUX(l, k) do { if (kAblate && p.trace && lane == 0) p.trace[((int64_t)b * TB200_CHAIN_MAX_LAYERS + (l)) * 8 + (k)] = chain_gtimer(); } while (0)
+constexpr int CH_TR = 32;   // trace slots per (CTA, layer)
+#define CH_SLOT(l, k) p.trace[((int64_t)b * TB200_CHAIN_MAX_LAYERS + (l)) * CH_TR + (k)]
+#define CH_STAMP(l, k) do { if (kAblate && p.trace && ct == 0) CH_SLOT(l, k) = chain_gtimer(); } while (0)
+#define CH_CLK(l, k) do { if (kAblate && p.trace && ct == 0) CH_SLOT(l, k) = clock64(); } while (0)
+#define CH_STAMP_AUX(l, k) do { if (kAblate && p.trace && lane == 0) CH_SLOT(l, k) = chain_gtimer(); } while (0)
+#define CH_CLK_AUX(l, k) do { if (kAblate && p.trace && lane == 0) CH_SLOT(l, k) = clock64(); } while (0)
 
 // per-layer facts the warps need, copied to shared memory once
 struct LayerInfo {
     const float* scale; const float* bias;
-    uint8_t* hout;                                 // this layer's output rows (inter-layer buffer), null for the last layer
-    int64_t rep_stride;                            // words between its replicas
+    uint8_t* hout;                                 // this layer's output buffer, set 0 (null for the last layer)
+    int64_t set_stride;                            // bytes to set 1
     int N, K, nks, RB;
     float clip; int act, pitch, one_box;
 };
 
-__device__ __forceinline__ void imma_c(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
-        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+__device__ __forceinline__ int dp4a_us(uint32_t a_u8, uint32_t b_s8, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_u8), "r"(b_s8), "r"(c));
+    return d;
 }
 __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
     uint32_t v;
@@ -100,30 +100,21 @@ __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-// one fence + one relaxed reduction by ONE lane after a __syncwarp(): the barrier orders the other lanes' stores
-// before the fence (cumulativity), as in a cooperative grid barrier.  (__threadfence() is fence.sc here and
-// red.release adds a second MEMBAR: 2 x MEMBAR + CCTL.IVALL per row block in the first version.)
-__device__ __forceinline__ void publish_add(uint32_t* p, uint32_t v) {
-    asm volatile("fence.acq_rel.gpu;\n\tred.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+// 32 bytes in one request (sm_100: 256-bit global loads), from L2, never from a stale L1 line
+__device__ __forceinline__ void ld_relaxed_256(const void* p, uint32_t (&r)[8]) {
+    asm volatile("ld.relaxed.gpu.global.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "l"(p) : "memory");
 }
-__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p) {
-    uint64_t v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
+__device__ __forceinline__ void st_relaxed_u16(void* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u16 [%0], %1;" ::"l"(p), "h"((unsigned short)v) : "memory");
 }
-__device__ __forceinline__ ulonglong2 ld_relaxed_u64x2(const uint64_t* p) {
-    ulonglong2 v;
-    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v) {
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_u32(void* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void red_relaxed_add(uint32_t* p, uint32_t v) {
     asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-// 16 bytes from L2 (never from a possibly stale L1 line: the buffers are rewritten by other SMs during the kernel)
 __device__ __forceinline__ uint4 ld_cg_u4(const void* p) {
     uint4 v;
     asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
@@ -145,9 +136,29 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 }
 template <typename T> __device__ __forceinline__ float round_to(float v) { return to_f32(from_f32<T>(v)); }
 
-__device__ __forceinline__ int chain_img_vec(int sg, int pp, int i, int n, int t, int Mg) {
-    return ((((sg * 2 + pp) * 4 + i) * Mg + n) << 2) + t;
+// Inter-layer activations are stored INVERTED (~bits) in the activation dtype, and an all-zero element means "not
+// written yet": the buffers start as zeros, the value whose bits are all ones (a NaN no conversion produces) is never
+// stored, so data and validity travel in the same single-copy-atomic element and no fence is needed between a
+// producer's stores and its counter increment.
+template <typename T> __device__ __forceinline__ uint32_t chain_encode(float y);
+template <> __device__ __forceinline__ uint32_t chain_encode<float>(float y) {
+    const uint32_t bits = __float_as_uint(y);
+    return ~(bits == 0xffffffffu ? 0x7fffffffu : bits);
 }
+template <> __device__ __forceinline__ uint32_t chain_encode<__nv_bfloat16>(float y) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(y);
+    const uint32_t bits = *reinterpret_cast<const unsigned short*>(&h);
+    return (~(bits == 0xffffu ? 0x7fffu : bits)) & 0xffffu;
+}
+template <> __device__ __forceinline__ uint32_t chain_encode<__half>(float y) {
+    const __half h = __float2half_rn(y);
+    const uint32_t bits = *reinterpret_cast<const unsigned short*>(&h);
+    return (~(bits == 0xffffu ? 0x7fffu : bits)) & 0xffffu;
+}
+
+// position of 16-element group gi in the activation image (uint4 units): inside every 32-group segment the (chunk, word)
+// index is transposed so that the eight chunk lanes of a warp read eight consecutive uint4 (no bank conflict)
+__device__ __forceinline__ int chain_img_pos(int gi) { return (gi & ~31) | ((gi & 3) << 3) | ((gi >> 2) & 7); }
 
 // walk of a CTA through ITS row blocks of all layers: (l, rb) with rb = b, b + G, ... < RB[l]; n counts them
 struct Walk {
@@ -162,21 +173,23 @@ struct Walk {
     }
 };
 
-template <typename XT>
+template <typename XT, int M>
 __global__ void __launch_bounds__(CH_THREADS, 1)
 gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
     uint8_t* gbase = smem_dyn + (base - smem_u32(smem_dyn));
-    // ring[stages][16 KB] | image[img_bytes] | slots[nslots][128] uint4 | red_f[64] | red_i[64] | sx[16] | layers | barriers
+    // ring[stages][16 KB] | image[M][groups] uint4 | slots[nslots][8 warps][16 rows][M] int | red_f[2][M][16] | red_i[2][M][16] |
+    // sx[2][8] | layers | barriers
+    constexpr int SLOT_INTS = CH_TEAM * CH_ROWS * M;
     const uint32_t sRing = base;
-    uint32_t* xq = reinterpret_cast<uint32_t*>(gbase + (size_t)p.stages * CH_TILE);
-    uint4* slots = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(xq) + ((p.img_bytes + 127u) & ~127u));
-    float* red_f = reinterpret_cast<float*>(slots + (size_t)p.nslots * CH_SLOT_U4);
-    int* red_i = reinterpret_cast<int*>(red_f + 64);
-    float* sx_sm = reinterpret_cast<float*>(red_i + 64);
+    uint4* img = reinterpret_cast<uint4*>(gbase + (size_t)p.stages * CH_TILE);
+    int* slots = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(img) + ((p.img_bytes + 127u) & ~127u));
+    float* red_f = reinterpret_cast<float*>(slots + (size_t)p.nslots * SLOT_INTS);
+    int* red_i = reinterpret_cast<int*>(red_f + 2 * M * CH_DOT_WARPS);
+    float* sx_sm = reinterpret_cast<float*>(red_i + 2 * M * CH_DOT_WARPS);
     LayerInfo* lay = reinterpret_cast<LayerInfo*>(sx_sm + 16);
-    const int L = (int)plan->n_layers;
+    const int L = p.n_layers;                 // from the parameter bank: rematerialised for free (read from the plan it was spilled)
     uint64_t* bars = reinterpret_cast<uint64_t*>(lay + L);
     const uint32_t sBar = smem_u32(bars);
     auto bar_full = [&](int s) { return sBar + 8u * s; };
@@ -194,123 +207,219 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
         LayerInfo li;
         li.scale = cl.scale; li.bias = cl.bias;
         li.hout = (l + 1 < L) ? p.ws + cl.h_off : nullptr;
-        li.rep_stride = cl.h_rep_stride;
+        li.set_stride = cl.h_set_stride;
         li.N = cl.N; li.K = cl.K; li.nks = cl.nks; li.RB = cl.row_blocks;
         li.clip = cl.clip_val; li.act = cl.act; li.pitch = cl.h_pitch; li.one_box = cl.one_box;
         lay[l] = li;
     }
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 4); }
-        for (int q = 0; q < p.nslots; ++q) { mbar_init(bar_sfull(q), 4); mbar_init(bar_sempty(q), 1); }
+        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), CH_TEAM); }
+        for (int q = 0; q < p.nslots; ++q) { mbar_init(bar_sfull(q), CH_TEAM); mbar_init(bar_sempty(q), 1); }
         mbar_fence_init();
     }
     __syncthreads();
     if (p.pdl) asm volatile("griddepcontrol.launch_dependents;");
-    // register budget by role (per warpgroup): the MMA warps hold 64 registers of B fragments, 32 of accumulators and 32 of
-    // A fragments; the producer and the aux warps need few
-    if (warp < CH_MMA_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
-    else asm volatile("setmaxnreg.dec.sync.aligned.u32 104;");
 
-    if (warp == CH_WARP_PRODUCER) {
-        // ===================== weight tiles of ALL layers: independent of every activation =====================
-        if (lane == 0) {
-            int s = 0; uint32_t ph = 0;
-            int sl = 0; uint32_t phl = 0; int issued = 0;       // trailing position: the tile `inflight` issues back
-            Walk w; w.start(lay, L, b);
-            while (w.l < L) {
-                const CUtensorMap* map = &layers[w.l].map;
-                const int nks = lay[w.l].nks, one_box = lay[w.l].one_box;
-                for (int ks = 0; ks < nks; ++ks) {
-                    mbar_wait_relaxed(bar_empty(s), ph ^ 1u);
-                    // at most `inflight` tiles of this SM outstanding in the memory system: a deeper queue adds no bandwidth
-                    // (the ring still fills up with LANDED tiles) but delays every other load and store of the kernel -- the
-                    // flag and activation traffic of the layer boundaries -- by the time it takes to drain
-                    if (p.inflight > 0 && issued >= p.inflight) {
-                        mbar_wait_relaxed(bar_full(sl), phl);
-                        if (++sl == p.stages) { sl = 0; phl ^= 1u; }
-                    }
-                    ++issued;
-                    mbar_arrive_expect_tx(bar_full(s), CH_TILE);
-                    if (one_box) {
-                        tma_load_4d(sRing + s * CH_TILE, map, bar_full(s), 0, w.rb * CH_ROWS, ks * 8, 0);
-                    } else {
+    if (warp >= CH_DOT_WARPS) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");   // 4 x 32 x (96 - 64) = exactly what 16 dot-product warps need to go from 96 to 104
+        if (warp == CH_WARP_PRODUCER) {
+            // ===================== weight tiles of ALL layers: independent of every activation =====================
+            if (lane == 0) {
+                int s = 0; uint32_t ph = 0;
+                Walk w; w.start(lay, L, b);
+                while (w.l < L) {
+                    const CUtensorMap* map = &layers[w.l].map;
+                    const int nks = lay[w.l].nks, one_box = lay[w.l].one_box;
+                    for (int ks = 0; ks < nks; ++ks) {
+                        mbar_wait_relaxed(bar_empty(s), ph ^ 1u);
+                        mbar_arrive_expect_tx(bar_full(s), CH_TILE);
+                        if (one_box) {
+                            tma_load_4d(sRing + s * CH_TILE, map, bar_full(s), 0, w.rb * CH_ROWS, ks * 8, 0);
+                        } else {
 #pragma unroll
-                        for (int sg = 0; sg < 8; ++sg)
-                            tma_load_3d(sRing + s * CH_TILE + sg * (CH_ROWS * CH_SEG), map, bar_full(s), ks * 256 + sg * 32, w.rb * CH_ROWS, 0);
+                            for (int sg = 0; sg < 8; ++sg)
+                                tma_load_3d(sRing + s * CH_TILE + sg * (CH_ROWS * CH_SEG), map, bar_full(s), ks * 256 + sg * 32, w.rb * CH_ROWS, 0);
+                        }
+                        if (++s == p.stages) { s = 0; ph ^= 1u; }
                     }
-                    if (++s == p.stages) { s = 0; ph ^= 1u; }
+                    w.next(lay, L, b, G);
                 }
-                w.next(lay, L, b, G);
             }
+            return;
         }
-    } else if (warp < CH_MMA_WARPS) {
+        // ===================== reduction of the K-partials + fused epilogue (+ activation) =====================
+        // lane -> row (lane & 15); the two half-warps add four warps' partials each, then take alternate tokens
+        const int a = warp - CH_WARP_AUX0;
+        const int row_l = lane & 15, half = lane >> 4;
+        if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");      // earlier kernels may still read out / the h buffers
+        const uint32_t gen = ld_acquire_u32(&ctrl->gen);
+        const int set = (int)(gen & 1u);
+        const int prevM = (int)ld_relaxed_u32(&ctrl->last_M);
+        Walk w; w.start(lay, L, b);
+        while (w.l < L) {
+            if ((w.n % CH_AUX) == a) {
+                const LayerInfo& li = lay[w.l];
+                const int l = w.l, par = l & 1;
+                const int sq_i = w.n % p.nslots;
+                const uint32_t spar = (uint32_t)(w.n / p.nslots) & 1u;
+                const int64_t row = (int64_t)w.rb * CH_ROWS + row_l;
+                float sc = 1.0f, bi = 0.0f;                               // requested before the wait for the partial sums
+                if (li.scale && row < li.N) sc = __ldg(li.scale + row);
+                if (li.bias && row < li.N) bi = __ldg(li.bias + row);
+                // scale / bias are read once per call (cold in L2) and their loads would queue behind the weight stream right
+                // when the layer's last row blocks wait for them: ask L2 for the same rows of the next two layers now
+                if (lane < 4) {
+                    const int l2 = l + 1 + (lane >> 1);
+                    if (l2 < L && w.rb < lay[l2].RB) {
+                        const float* ptr = (lane & 1) ? lay[l2].bias : lay[l2].scale;
+                        if (ptr) prefetch_l2(ptr + (int64_t)w.rb * CH_ROWS);
+                    }
+                }
+                CH_CLK_AUX(l, 17);
+                mbar_wait(bar_sfull(sq_i), spar);
+                CH_CLK_AUX(l, 18);
+                const int* sl = slots + (size_t)sq_i * SLOT_INTS + (half * 4 * CH_ROWS + row_l) * M;
+                int tot[M]; float sxv[M]; int sumq[M];
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    int v = 0;
+#pragma unroll
+                    for (int wv = 0; wv < 4; ++wv) v += sl[wv * CH_ROWS * M + m];
+                    tot[m] = v;
+                    sxv[m] = sx_sm[par * 8 + m];
+                    int sq = 0;
+#pragma unroll
+                    for (int j = 0; j < CH_DOT_WARPS / 4; ++j) {
+                        const int4 a0 = *reinterpret_cast<const int4*>(red_i + (par * M + m) * CH_DOT_WARPS + 4 * j);
+                        sq += a0.x + a0.y + a0.z + a0.w;
+                    }
+                    sumq[m] = sq;
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_sempty(sq_i));                // partial sums and token scalars are in registers
+                float yv[M];
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    const int av = tot[m] + __shfl_xor_sync(0xffffffffu, tot[m], 16) - sumq[m];
+                    const float tv = __fmul_rn((float)av, sxv[m]);
+                    float y = epilogue(tv, sc, bi, li.clip);
+                    // the activation function sees the value in the STORED (activation dtype) precision
+                    if (li.act == TB200_ACT_GELU_TANH) y = gelu_tanh(round_to<XT>(y));
+                    else if (li.act == TB200_ACT_RELU) y = fmaxf(y, 0.0f);
+                    yv[m] = row < li.N ? y : 0.0f;                           // rows of the padding: zeros for the next layer's image
+                }
+                CH_CLK_AUX(l, 19);
+                if (li.hout) {
+                    // this call's set gets the values (every row up to the pitch: the consumers read whole 16-element groups);
+                    // the other set, read by the previous call, is cleared for the next one
+                    uint8_t* hs = li.hout + (int64_t)set * li.set_stride;
+                    uint8_t* ho = li.hout + (int64_t)(set ^ 1) * li.set_stride;
+#pragma unroll
+                    for (int m = 0; m < M; ++m)
+                        if (half == (m & 1)) {
+                            const int64_t o = ((int64_t)m * li.pitch + row) * sizeof(XT);
+                            if (sizeof(XT) == 2) st_relaxed_u16(hs + o, chain_encode<XT>(yv[m]));
+                            else st_relaxed_u32(hs + o, chain_encode<XT>(yv[m]));
+                        }
+#pragma unroll
+                    for (int m = 0; m < TB200_CHAIN_MAX_M; ++m)
+                        if (m < prevM && half == (m & 1)) {
+                            const int64_t o = ((int64_t)m * li.pitch + row) * sizeof(XT);
+                            if (sizeof(XT) == 2) st_relaxed_u16(ho + o, 0u);
+                            else st_relaxed_u32(ho + o, 0u);
+                        }
+                    __syncwarp();
+                    if (lane == 0) red_relaxed_add(&ctrl->counter[l * CH_CNT_STRIDE], 1u);     // hint for the pollers
+                } else {
+#pragma unroll
+                    for (int m = 0; m < M; ++m)
+                        if (half == (m & 1) && row < li.N) {
+                            const int64_t o = (int64_t)m * p.ldo + row;
+                            if (p.out_dtype == TB200_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(yv[m]);
+                            else if (p.out_dtype == TB200_F16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(yv[m]);
+                            else reinterpret_cast<float*>(p.out)[o] = yv[m];
+                        }
+                }
+                CH_CLK_AUX(l, 20);
+            }
+            w.next(lay, L, b, G);
+        }
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
         // ===================== activation image of every layer + dot products =====================
-        const int ct = threadIdx.x;                          // 0..255
-        const int g = lane >> 2, t = lane & 3;
-        const int team = warp >> 2, wq = warp & 3, wseg = 2 * wq;
-        const uint32_t sSeg = wseg * (CH_ROWS * CH_SEG) + g * CH_SEG;
-        const uint32_t phys0 = ((2 * t) ^ g) << 4, phys1 = ((2 * t + 1) ^ g) << 4;
-        const int M = p.M, stages = p.stages, nslots = p.nslots;
+        // Two teams of eight warps take alternate row blocks.  In a team, warp q owns 128-byte K segment q of every tile (512
+        // weights of each of the 16 rows); lane (r4, ch) owns 16-byte chunk ch of rows r4, r4+4, r4+8, r4+12.  The 64 int8
+        // activations that chunk multiplies stay in registers for the whole layer (K <= 4096), so a tile costs 4 LDS.128 +
+        // 64 LOP3 + 64 M IDP.4A per lane: 2-bit field i of every packed byte is masked in place (value code * 4^i) and dotted
+        // with the matching activation bytes; the four field sums are recombined exactly with shifts.  IDP.4A and LOP3 issue
+        // on different pipes (tools/microbench/int_rates.cu: 3.0-3.2 warp instructions/clk/SM for the mix with >= 16 warps;
+        // the legacy IMMA path computes eight token columns whatever M is and tops out at 0.5 IMMA/clk/SM).
+        const int ct = threadIdx.x;                          // 0..511
+        const int r4 = lane >> 3, ch = lane & 7;
+        const int team = warp >> 3, wq = warp & 7;
+        const int stages = p.stages, nslots = p.nslots;
         if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");      // x (and the control block) come from earlier kernels
         const uint32_t gen = ld_acquire_u32(&ctrl->gen);
+        const int set = (int)(gen & 1u);
         int s = 0; uint32_t ph = 0;                          // weight ring (global tile sequence of this CTA)
         int sq = 0; uint32_t spar = 0;                       // slot ring
-        int acc[2][4][4];                                    // [segment][field][fragment]: eight independent IMMA chains
+        uint4 xa[M][4];                                      // activation words of this lane's chunk, current k-slice
+        // byte offsets of this lane's four weight chunks inside a tile (SWIZZLE_128B: chunk ^ (row & 7))
+        uint32_t woff[4];
 #pragma unroll
-        for (int j = 0; j < 2; ++j)
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int e = 0; e < 4; ++e) acc[j][i][e] = 0;
-        uint4 b2[2][2][4];                                   // B fragments of this warp's two segments for the current k-slice
-        const uint4* xqv = reinterpret_cast<const uint4*>(xq);
-        auto load_b = [&](int ks) {
-#pragma unroll
-            for (int j = 0; j < 2; ++j)
-#pragma unroll
-                for (int pp = 0; pp < 2; ++pp)
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        b2[j][pp][i] = g < M ? xqv[chain_img_vec(ks * 8 + wseg + j, pp, i, g, t, M)] : make_uint4(0u, 0u, 0u, 0u);
-        };
-        int cur = -1;
+        for (int q = 0; q < 4; ++q) {
+            const int row = r4 + 4 * q;
+            woff[q] = wq * (CH_ROWS * CH_SEG) + row * CH_SEG + ((ch ^ (row & 7)) << 4);
+        }
+        int cur = -1, ngroups = 0;
+        long long tr_full = 0, tr_slot = 0;                  // experiment build: cycles this thread waited for tiles / for a slot
         Walk w; w.start(lay, L, b);
+        auto load_x = [&](int ks) {
+#pragma unroll
+            for (int m = 0; m < M; ++m)
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) xa[m][jj] = img[m * ngroups + ks * 256 + wq * 32 + jj * 8 + ch];
+        };
         while (w.l < L) {
             const LayerInfo& li = lay[w.l];
             if (w.l != cur) {
                 // ---------- entering layer w.l: its input must be complete, then quantise it into the image ----------
                 cur = w.l;
-                const int l = cur;
-                CH_STAMP(l, 0);
+                const int l = cur, par = l & 1;
+                CH_STAMP(l, 0); CH_CLK(l, 8);
                 const int K = li.K, nks = li.nks;
-                const uint32_t want = gen + 1u;              // flag value of this call's inter-layer words
+                ngroups = nks * 256;
+                const int nu = (nks + 1) >> 1;               // 512-group slices of the input: group gi = u * 512 + ct
                 const XT* xin = reinterpret_cast<const XT*>(p.x);
-                const uint64_t* hw = nullptr; int64_t pitch_w = 0;
+                const uint8_t* hin = nullptr; int64_t pitch_b = 0;
                 const bool vec0 = ((reinterpret_cast<uintptr_t>(p.x) | (uintptr_t)(p.ldx * sizeof(XT))) & 15) == 0;
                 if (l > 0) {
                     const LayerInfo& pl = lay[l - 1];
-                    // every CTA reads the WHOLE previous output at the same moment: 148 readers of the same L2 lines are served one
-                    // after the other (measured: 7 KB/us per SM), so the producers store `replicas` copies and CTA b reads copy b % R
-                    hw = reinterpret_cast<const uint64_t*>(pl.hout) + (int64_t)(b % p.replicas) * pl.rep_stride; pitch_w = pl.pitch;
-                    if (ct == 0) {
-                        // coarse wait: ONE poller per CTA on the layer's row-block counter (relaxed loads; the counter is only
-                        // a hint that the data is on its way -- the flags inside the data words are what is verified below)
-                        const uint32_t need = want * (uint32_t)pl.RB;
-                        const uint32_t* cnt = &ctrl->counter[(l - 1) * CH_CNT_STRIDE];
-                        uint32_t spins = 0;
-                        while ((int)(ld_relaxed_u32(cnt) - need) < 0) {
-                            if (++spins > 50000000u) __trap();          // a protocol bug traps instead of hanging the GPU
+                    hin = pl.hout + (int64_t)set * pl.set_stride; pitch_b = (int64_t)pl.pitch * sizeof(XT);
+                    if (p.gate) {
+                        if (ct == 0) {
+                            // coarse wait: ONE poller per CTA on the layer's row-block counter (relaxed loads; the counter is only
+                            // a hint that the data is on its way -- the elements themselves say whether they have been written)
+                            const uint32_t need = (gen + 1u) * (uint32_t)pl.RB;
+                            const uint32_t* cnt = &ctrl->counter[(l - 1) * CH_CNT_STRIDE];
+                            uint32_t spins = 0;
+                            while ((int)(ld_relaxed_u32(cnt) - need) < 0) {
+                                if (++spins > 50000000u) __trap();          // a protocol bug traps instead of hanging the GPU
+                            }
                         }
+                        asm volatile("bar.sync 1, %0;" ::"n"(CH_DOT_THREADS) : "memory");
                     }
-                    asm volatile("bar.sync 1, %0;" ::"n"(CH_MMA_THREADS) : "memory");
                 }
-                CH_STAMP(l, 1);
+                CH_CLK(l, 9);
                 // one 16-element group of token m as fp32 (zero beyond K).  Layer 0 reads the caller's plain activations;
-                // later layers read the flagged words the previous layer's epilogue stored: {value(s), flag} per 8 bytes, so
-                // no fence is needed between the producer's data and its counter increment -- a word whose flag is not
-                // `want` yet simply makes the group invalid and it is fetched again.
-                constexpr int EPW = sizeof(XT) == 4 ? 1 : 2;           // elements per flagged word
+                // later layers read what the previous layer's epilogue stored (inverted bits, zero = not written yet): a group
+                // with a missing element is simply fetched again.
                 auto fetch = [&](int m, int gi, float (&v)[16]) -> bool {
+                    if (16 * gi >= K) {
+#pragma unroll
+                        for (int tt = 0; tt < 16; ++tt) v[tt] = 0.0f;
+                        return true;
+                    }
                     if (l == 0) {
                         const XT* src = xin + (int64_t)m * p.ldx + 16 * (int64_t)gi;
                         if (vec0 && 16 * gi + 16 <= K) {
@@ -328,48 +437,31 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
                         }
                         return true;
                     }
-                    const uint64_t* src = hw + (int64_t)m * pitch_w + (16 / EPW) * (int64_t)gi;
-                    bool ok = true;
-                    if (16 * gi + 16 <= K) {
+                    const uint8_t* src = hin + (int64_t)m * pitch_b + (int64_t)gi * (16 * sizeof(XT));
+                    uint32_t miss = 0;
+                    if (sizeof(XT) == 2) {
+                        uint32_t r[8];
+                        ld_relaxed_256(src, r);
 #pragma unroll
-                        for (int j = 0; j < 8 / EPW; ++j) {             // 16-byte loads of two flagged words
-                            const ulonglong2 r = ld_relaxed_u64x2(src + 2 * j);
-                            ok = ok && (uint32_t)(r.x >> 32) == want && (uint32_t)(r.y >> 32) == want;
-                            if (EPW == 2) {
-                                const uint32_t w0 = (uint32_t)r.x, w1 = (uint32_t)r.y;
-                                const XT* e0 = reinterpret_cast<const XT*>(&w0);
-                                const XT* e1 = reinterpret_cast<const XT*>(&w1);
-                                v[4 * j] = to_f32(e0[0]); v[4 * j + 1] = to_f32(e0[1]); v[4 * j + 2] = to_f32(e1[0]); v[4 * j + 3] = to_f32(e1[1]);
-                            } else {
-                                v[2 * j] = __uint_as_float((uint32_t)r.x); v[2 * j + 1] = __uint_as_float((uint32_t)r.y);
-                            }
+                        for (int j = 0; j < 8; ++j) {
+                            miss |= (r[j] - 0x00010001u) & ~r[j] & 0x80008000u;      // a 16-bit lane that is zero
+                            const uint32_t wbits = ~r[j];
+                            const XT* e = reinterpret_cast<const XT*>(&wbits);
+                            v[2 * j] = to_f32(e[0]); v[2 * j + 1] = to_f32(e[1]);
                         }
                     } else {
 #pragma unroll
-                        for (int j = 0; j < 16 / EPW; ++j) {            // ragged tail: word by word
-                            const bool in_k = 16 * gi + EPW * j < K;
-                            const uint64_t r = in_k ? ld_relaxed_u64(src + j) : ((uint64_t)want << 32);
-                            ok = ok && (uint32_t)(r >> 32) == want;
-                            const uint32_t w0 = (uint32_t)r;
-                            if (EPW == 2) {
-                                const XT* e0 = reinterpret_cast<const XT*>(&w0);
-                                v[2 * j] = to_f32(e0[0]);
-                                v[2 * j + 1] = (16 * gi + 2 * j + 1 < K) ? to_f32(e0[1]) : 0.0f;
-                            } else {
-                                v[j] = __uint_as_float(w0);
-                            }
+                        for (int h = 0; h < 2; ++h) {
+                            uint32_t r[8];
+                            ld_relaxed_256(src + 32 * h, r);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) { miss |= (uint32_t)(r[j] == 0u); v[8 * h + j] = __uint_as_float(~r[j]); }
                         }
                     }
-                    return ok;
+                    return miss == 0u;
                 };
-                constexpr int CACHE = 3;                     // groups per thread kept in registers between the two passes
-                const int tot = M * nks;                     // groups of this thread
-                const bool cached = tot <= CACHE;
-                // NOTE: everything below indexes its register arrays with compile-time constants only.  With ~225 KB of the
-                // SM carved out as shared memory there is practically no L1 left, so a local-memory (stack) array costs an L2
-                // round trip per access: the first version kept the cached groups in a dynamically indexed array and spent
-                // 2.3 us (K = 4096) / 5.6 us (K = 11008) per layer right here.
                 auto quantise_group = [&](const float (&v)[16], float inv, int m, int gi, int& ls) {
+                    if (gi >= ngroups) return;    // beyond the image (odd number of 256-group slices)
                     uint32_t qb[16];              // low byte = two's-complement int8 code (rint via the 1.5 * 2^23 trick)
 #pragma unroll
                     for (int tt = 0; tt < 16; ++tt) {
@@ -377,143 +469,176 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
                         q = fminf(fmaxf(q, -127.0f), 127.0f);
                         qb[tt] = __float_as_uint(__fadd_rn(q, 12582912.0f));
                     }
-                    const int c = gi >> 2, jw = gi & 3, lc = c & 7;
+                    uint32_t wd[4];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {   // word i = elements i, 4+i, 8+i, 12+i (field i of the 4 bytes of packed word gi)
-                        const uint32_t wd = __byte_perm(__byte_perm(qb[i], qb[4 + i], 0x0040), __byte_perm(qb[8 + i], qb[12 + i], 0x0040), 0x5410);
-                        ls = __dp4a((int)wd, 0x01010101, ls);
-                        xq[chain_img_vec(c >> 3, lc & 1, i, m, lc >> 1, M) * 4 + jw] = wd;
+                    for (int i = 0; i < 4; ++i) {   // word i = elements i, 4+i, 8+i, 12+i: the bytes that meet field i of packed word gi
+                        wd[i] = __byte_perm(__byte_perm(qb[i], qb[4 + i], 0x0040), __byte_perm(qb[8 + i], qb[12 + i], 0x0040), 0x5410);
+                        ls = __dp4a((int)wd[i], 0x01010101, ls);
                     }
+                    img[m * ngroups + chain_img_pos(gi)] = make_uint4(wd[0], wd[1], wd[2], wd[3]);
                 };
                 auto token_scale = [&](int m) -> float {     // after the barrier: absmax of token m -> 127/amax; s_x to shared
-                    const float4 r0 = *reinterpret_cast<const float4*>(red_f + m * 8);
-                    const float4 r1 = *reinterpret_cast<const float4*>(red_f + m * 8 + 4);
-                    const float vmax = fmaxf(fmaxf(fmaxf(r0.x, r0.y), fmaxf(r0.z, r0.w)), fmaxf(fmaxf(r1.x, r1.y), fmaxf(r1.z, r1.w)));
-                    if (ct == 0) sx_sm[m] = vmax > 0.0f ? __fdiv_rn(vmax, 127.0f) : 1.0f;
+                    float vmax = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < CH_DOT_WARPS / 4; ++j) {
+                        const float4 r0 = *reinterpret_cast<const float4*>(red_f + (par * M + m) * CH_DOT_WARPS + 4 * j);
+                        vmax = fmaxf(vmax, fmaxf(fmaxf(r0.x, r0.y), fmaxf(r0.z, r0.w)));
+                    }
+                    if (ct == 0) sx_sm[par * 8 + m] = vmax > 0.0f ? __fdiv_rn(vmax, 127.0f) : 1.0f;
                     return vmax > 0.0f ? __fdiv_rn(127.0f, vmax) : 1.0f;
                 };
-                if (cached) {
-                    float vc[CACHE][16];
-                    // all loads of the thread are issued before the first use (ONE L2 round trip), and again until every flag is set
+                // NOTE: register arrays below are indexed with compile-time constants only.  With ~225 KB of the SM carved out as
+                // shared memory there is practically no L1 left, so a local-memory (stack) array costs an L2 round trip per access.
+                constexpr int NKC = CH_CACHE / M > 0 ? CH_CACHE / M : 1;   // 512-group slices per token whose groups fit the register cache
+                if (nu <= NKC) {
+                    float vc[M][NKC][16];
+                    // all loads of the thread are issued before the first use (ONE L2 round trip), and again until every element is there
                     uint32_t spins = 0;
                     bool ok;
                     do {
                         ok = true;
 #pragma unroll
-                        for (int c = 0; c < CACHE; ++c)
-                            if (c < tot) { const int m = c / nks, u = c - m * nks; ok = fetch(m, u * 256 + ct, vc[c]) && ok; }
+                        for (int m = 0; m < M; ++m)
+#pragma unroll
+                            for (int u = 0; u < NKC; ++u)
+                                if (u < nu) ok = fetch(m, u * CH_DOT_THREADS + ct, vc[m][u]) && ok;
                         if (!ok && ++spins > 20000000u) __trap();
                     } while (!ok);
-                    CH_STAMP(l, 6);
-                    if (kAblate && p.trace && ct == 0) p.trace[((int64_t)b * TB200_CHAIN_MAX_LAYERS + l) * 8 + 7] = spins;
+                    CH_CLK(l, 10);
+                    if (kAblate && p.trace && ct == 0) CH_SLOT(l, 7) = spins;
+#pragma unroll
                     for (int m = 0; m < M; ++m) {            // pass A: per-token absmax
                         float amax = 0.0f;
 #pragma unroll
-                        for (int c = 0; c < CACHE; ++c)
-                            if (c < tot && c / nks == m) {
+                        for (int u = 0; u < NKC; ++u)
+                            if (u < nu) {
 #pragma unroll
-                                for (int tt = 0; tt < 16; ++tt) amax = fmaxf(amax, fabsf(vc[c][tt]));
+                                for (int tt = 0; tt < 16; ++tt) amax = fmaxf(amax, fabsf(vc[m][u][tt]));
                             }
                         const uint32_t am = __reduce_max_sync(0xffffffffu, __float_as_uint(amax));
-                        if (lane == 0) red_f[m * 8 + warp] = __uint_as_float(am);
+                        if (lane == 0) red_f[(par * M + m) * CH_DOT_WARPS + warp] = __uint_as_float(am);
                     }
-                    asm volatile("bar.sync 1, %0;" ::"n"(CH_MMA_THREADS) : "memory");
-                    for (int m = 0; m < M; ++m) {            // pass B: quantise into the kperm image (zero beyond K), code sums
+                    asm volatile("bar.sync 1, %0;" ::"n"(CH_DOT_THREADS) : "memory");
+                    CH_CLK(l, 11);
+#pragma unroll
+                    for (int m = 0; m < M; ++m) {            // pass B: quantise into the image (zero beyond K), code sums
                         const float inv = token_scale(m);
                         int ls = 0;
 #pragma unroll
-                        for (int c = 0; c < CACHE; ++c)
-                            if (c < tot && c / nks == m) quantise_group(vc[c], inv, m, (c - m * nks) * 256 + ct, ls);
+                        for (int u = 0; u < NKC; ++u)
+                            if (u < nu) quantise_group(vc[m][u], inv, m, u * CH_DOT_THREADS + ct, ls);
                         ls = __reduce_add_sync(0xffffffffu, ls);
-                        if (lane == 0) red_i[m * 8 + warp] = ls;
+                        if (lane == 0) red_i[(par * M + m) * CH_DOT_WARPS + warp] = ls;
                     }
                 } else {
+#pragma unroll
                     for (int m = 0; m < M; ++m) {            // pass A (the data is fetched again in pass B: L2)
                         float amax = 0.0f;
-                        for (int u = 0; u < nks; ++u) {
+                        for (int u = 0; u < nu; ++u) {
                             float v[16];
                             uint32_t spins = 0;
-                            while (!fetch(m, u * 256 + ct, v)) { if (++spins > 20000000u) __trap(); }
+                            while (!fetch(m, u * CH_DOT_THREADS + ct, v)) { if (++spins > 20000000u) __trap(); }
 #pragma unroll
                             for (int tt = 0; tt < 16; ++tt) amax = fmaxf(amax, fabsf(v[tt]));
                         }
                         const uint32_t am = __reduce_max_sync(0xffffffffu, __float_as_uint(amax));
-                        if (lane == 0) red_f[m * 8 + warp] = __uint_as_float(am);
+                        if (lane == 0) red_f[(par * M + m) * CH_DOT_WARPS + warp] = __uint_as_float(am);
                     }
-                    asm volatile("bar.sync 1, %0;" ::"n"(CH_MMA_THREADS) : "memory");
+                    asm volatile("bar.sync 1, %0;" ::"n"(CH_DOT_THREADS) : "memory");
+                    CH_CLK(l, 11);
+#pragma unroll
                     for (int m = 0; m < M; ++m) {
                         const float inv = token_scale(m);
                         int ls = 0;
-                        for (int u = 0; u < nks; ++u) {
+                        for (int u = 0; u < nu; ++u) {
                             float v[16];
-                            (void)fetch(m, u * 256 + ct, v);           // verified in pass A
-                            quantise_group(v, inv, m, u * 256 + ct, ls);
+                            (void)fetch(m, u * CH_DOT_THREADS + ct, v);           // verified in pass A
+                            quantise_group(v, inv, m, u * CH_DOT_THREADS + ct, ls);
                         }
                         ls = __reduce_add_sync(0xffffffffu, ls);
-                        if (lane == 0) red_i[m * 8 + warp] = ls;
+                        if (lane == 0) red_i[(par * M + m) * CH_DOT_WARPS + warp] = ls;
                     }
                 }
-                // image, sx_sm and red_i (per-warp code sums, added up by the aux warps) are complete: every MMA warp passes
-                // this barrier before its first slot hand-off of the layer, which is what the aux warps wait for
-                asm volatile("bar.sync 1, %0;" ::"n"(CH_MMA_THREADS) : "memory");
-                load_b(0);
-                CH_STAMP(l, 2);
+                CH_CLK(l, 14);
+                // image complete for every warp (both teams read all of it); sx_sm and red_i (read by the aux warps) are ordered
+                // by this barrier + the first slot hand-off of the layer
+                asm volatile("bar.sync 1, %0;" ::"n"(CH_DOT_THREADS) : "memory");
+                load_x(0);
+                CH_CLK(l, 12);
+                tr_full = 0; tr_slot = 0;
             }
-            // ---------- one row block: team (n & 1) computes it, the other team only advances its ring position ----------
+            // ---------- one row block: team (n & 1) computes it (one K segment of every k-slice per warp), the other team only
+            // advances its ring position ----------
             const int nks = li.nks;
             if ((w.n & 1) == team) {
+                int rs[4][M];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                    for (int m = 0; m < M; ++m) rs[q][m] = 0;
 #pragma unroll 1
                 for (int k2 = 0; k2 < nks; ++k2) {
-                    if (nks > 1) load_b(k2);          // K > 4096: the fragments of this k-slice (a single slice stays in registers)
+                    if (nks > 1) load_x(k2);           // K > 4096: the activation words of this k-slice (a single slice stays in registers)
+                    const long long tw0 = kAblate && p.trace ? clock64() : 0;
                     mbar_wait(bar_full(s), ph);
-                    const uint8_t* seg = gbase + s * CH_TILE + sSeg;
-                    uint4 alo[2][2], ahi[2][2];
+                    if (kAblate && p.trace) tr_full += clock64() - tw0;
+                    const uint8_t* tile = gbase + s * CH_TILE;
+                    uint4 wv[4];
 #pragma unroll
-                    for (int j = 0; j < 2; ++j) {
-                        const uint8_t* sj = seg + j * (CH_ROWS * CH_SEG);
-                        alo[j][0] = *reinterpret_cast<const uint4*>(sj + phys0);
-                        ahi[j][0] = *reinterpret_cast<const uint4*>(sj + 8 * CH_SEG + phys0);
-                        alo[j][1] = *reinterpret_cast<const uint4*>(sj + phys1);
-                        ahi[j][1] = *reinterpret_cast<const uint4*>(sj + 8 * CH_SEG + phys1);
-                    }
+                    for (int q = 0; q < 4; ++q) wv[q] = *reinterpret_cast<const uint4*>(tile + woff[q]);
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_empty(s));            // the tile lives in registers now
+                    if (lane == 0) mbar_arrive(bar_empty(s));            // this warp's part of the tile lives in registers now
                     if (++s == stages) { s = 0; ph ^= 1u; }
 #pragma unroll
-                    for (int j = 0; j < 2; ++j)
+                    for (int q = 0; q < 4; ++q) {
+                        int a[4][M];
 #pragma unroll
-                        for (int pp = 0; pp < 2; ++pp) {
-                            const uint4 lo = alo[j][pp], hi = ahi[j][pp];
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int m = 0; m < M; ++m) a[i][m] = 0;
+                        const uint32_t wq4[4] = {wv[q].x, wv[q].y, wv[q].z, wv[q].w};
+#pragma unroll
+                        for (int jj = 0; jj < 4; ++jj)
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
-                                const uint32_t mk = 0x03030303u << (2 * i);
-                                imma_c(acc[j][i], lo.x & mk, hi.x & mk, lo.y & mk, hi.y & mk, b2[j][pp][i].x, b2[j][pp][i].y);
+                                const uint32_t mw = wq4[jj] & (0x03030303u << (2 * i));
+#pragma unroll
+                                for (int m = 0; m < M; ++m) {
+                                    const uint32_t xw = i == 0 ? xa[m][jj].x : i == 1 ? xa[m][jj].y : i == 2 ? xa[m][jj].z : xa[m][jj].w;
+                                    a[i][m] = dp4a_us(mw, xw, a[i][m]);
+                                }
                             }
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                const uint32_t mk = 0x03030303u << (2 * i);
-                                imma_c(acc[j][i], lo.z & mk, hi.z & mk, lo.w & mk, hi.w & mk, b2[j][pp][i].z, b2[j][pp][i].w);
-                            }
-                        }
+                        for (int m = 0; m < M; ++m) rs[q][m] += a[0][m] + (a[1][m] >> 2) + (a[2][m] >> 4) + (a[3][m] >> 6);   // exact: set i is a multiple of 4^i
+                    }
                 }
-                // recombine the four fields (exact: set i is a multiple of 4^i) and park this warp's K-partial
+                // sum over the eight chunk lanes, halving the number of live values at every step: lane ch ends with row
+                // r4 + 4 * (2 * (ch & 1) + ((ch >> 1) & 1)); the lanes with ch < 4 park this warp's K-partial
+                const bool o1 = ch & 1, o2 = ch & 2;
+                int fin[M];
+#pragma unroll
+                for (int m = 0; m < M; ++m) {
+                    const int s0 = __shfl_xor_sync(0xffffffffu, o1 ? rs[0][m] : rs[2][m], 1);
+                    const int s1 = __shfl_xor_sync(0xffffffffu, o1 ? rs[1][m] : rs[3][m], 1);
+                    const int k0 = (o1 ? rs[2][m] : rs[0][m]) + s0, k1 = (o1 ? rs[3][m] : rs[1][m]) + s1;
+                    const int s2 = __shfl_xor_sync(0xffffffffu, o2 ? k0 : k1, 2);
+                    int v = (o2 ? k1 : k0) + s2;
+                    v += __shfl_xor_sync(0xffffffffu, v, 4);
+                    fin[m] = v;
+                }
+                const long long tw1 = kAblate && p.trace ? clock64() : 0;
                 mbar_wait(bar_sempty(sq), spar ^ 1u);
-                uint32_t vr[4];
+                if (kAblate && p.trace) tr_slot += clock64() - tw1;
+                if (ch < 4) {
+                    const int row = r4 + 4 * (2 * (ch & 1) + ((ch >> 1) & 1));
+                    int* dst = slots + (size_t)sq * SLOT_INTS + (wq * CH_ROWS + row) * M;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    vr[e] = (uint32_t)((acc[0][0][e] + acc[1][0][e]) + ((acc[0][1][e] + acc[1][1][e]) >> 2) +
-                                       ((acc[0][2][e] + acc[1][2][e]) >> 4) + ((acc[0][3][e] + acc[1][3][e]) >> 6));
+                    for (int m = 0; m < M; ++m) dst[m] = fin[m];
                 }
-                slots[(size_t)sq * CH_SLOT_U4 + wq * 32 + lane] = make_uint4(vr[0], vr[1], vr[2], vr[3]);
-#pragma unroll
-                for (int j = 0; j < 2; ++j)
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) acc[j][i][e] = 0;
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar_sfull(sq));
-                CH_STAMP(w.l, 3);
+                CH_CLK(w.l, 13);
+                if (kAblate && p.trace && ct == 0) { CH_SLOT(w.l, 15) = tr_full; CH_SLOT(w.l, 16) = tr_slot; }
             } else {
                 s += nks;                                                // the other team's tiles
                 while (s >= stages) { s -= stages; ph ^= 1u; }
@@ -521,132 +646,15 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
             if (++sq == nslots) { sq = 0; spar ^= 1u; }
             w.next(lay, L, b, G);
         }
-    } else {
-        // ===================== reduction of the K-partials + fused epilogue (+ activation) =====================
-        const int a = warp - CH_WARP_AUX0;
-        const int g = lane >> 2, t = lane & 3;
-        if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");      // earlier kernels may still read out / the h buffers
-        const uint32_t gen = ld_acquire_u32(&ctrl->gen);
-        Walk w; w.start(lay, L, b);
-        while (w.l < L) {
-            if ((w.n % CH_AUX) == a) {
-                const LayerInfo& li = lay[w.l];
-                const int l = w.l;
-                const int sq_i = w.n % p.nslots;
-                const uint32_t spar = (uint32_t)(w.n / p.nslots) & 1u;
-                const int64_t row0 = (int64_t)w.rb * CH_ROWS + g, row1 = row0 + 8;
-                float sc0 = 1.0f, sc1 = 1.0f, bi0 = 0.0f, bi1 = 0.0f;         // requested before the wait for the partial sums
-                if (li.scale) { if (row0 < li.N) sc0 = __ldg(li.scale + row0); if (row1 < li.N) sc1 = __ldg(li.scale + row1); }
-                if (li.bias) { if (row0 < li.N) bi0 = __ldg(li.bias + row0); if (row1 < li.N) bi1 = __ldg(li.bias + row1); }
-                // scale / bias are read once per call (cold in L2) and their loads would queue behind the weight stream right
-                // when the layer's last row blocks wait for them: ask L2 for the same rows of the next two layers now
-                if (lane < 4) {
-                    const int l2 = l + 1 + (lane >> 1);
-                    if (l2 < L && w.rb < lay[l2].RB) {
-                        const float* ptr = (lane & 1) ? lay[l2].bias : lay[l2].scale;
-                        if (ptr) prefetch_l2(ptr + (int64_t)w.rb * CH_ROWS);
-                    }
-                }
-                mbar_wait(bar_sfull(sq_i), spar);
-                int vv[4] = {0, 0, 0, 0};
-                const uint4* sl = slots + (size_t)sq_i * CH_SLOT_U4 + lane;
-#pragma unroll
-                for (int wv = 0; wv < 4; ++wv) {
-                    const uint4 v = sl[wv * 32];
-                    vv[0] += (int)v.x; vv[1] += (int)v.y; vv[2] += (int)v.z; vv[3] += (int)v.w;
-                }
-                float sxv[2]; int sumq[2];
-#pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int tok = 2 * t + e;
-                    sxv[e] = 0.0f; sumq[e] = 0;
-                    if (tok < p.M) {
-                        sxv[e] = sx_sm[tok];
-                        const int4 a0 = *reinterpret_cast<const int4*>(red_i + tok * 8);
-                        const int4 a1 = *reinterpret_cast<const int4*>(red_i + tok * 8 + 4);
-                        sumq[e] = a0.x + a0.y + a0.z + a0.w + a1.x + a1.y + a1.z + a1.w;
-                    }
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_sempty(sq_i));                // partial sums and token scalars are in registers
-                // fragment: vv0 (row g, tok 2t), vv1 (row g, tok 2t+1), vv2 (row g+8, tok 2t), vv3 (row g+8, tok 2t+1)
-                float yv[4];
-#pragma unroll
-                for (int e4 = 0; e4 < 4; ++e4) {
-                    const int e = e4 & 1, hi = e4 >> 1;
-                    const int av = vv[e4] - sumq[e];
-                    const float tv = __fmul_rn((float)av, sxv[e]);
-                    float y = epilogue(tv, hi ? sc1 : sc0, hi ? bi1 : bi0, li.clip);
-                    // the activation function sees the value in the STORED (activation dtype) precision
-                    if (li.act == TB200_ACT_GELU_TANH) y = gelu_tanh(round_to<XT>(y));
-                    else if (li.act == TB200_ACT_RELU) y = fmaxf(y, 0.0f);
-                    yv[e4] = y;
-                }
-                CH_STAMP_AUX(l, 4);
-                if (li.hout) {
-                    // inter-layer activations as flagged 8-byte words {value(s) in the activation dtype, flag = generation}:
-                    // a single-copy-atomic store carries data and validity together, so no fence orders data before the counter
-                    const uint32_t want = gen + 1u;
-                    uint64_t* hw = reinterpret_cast<uint64_t*>(li.hout);
-                    if (sizeof(XT) == 4) {
-#pragma unroll
-                        for (int e4 = 0; e4 < 4; ++e4) {
-                            const int tok = 2 * t + (e4 & 1);
-                            const int64_t row = (e4 >> 1) ? row1 : row0;
-                            if (row < li.N && tok < p.M) {
-                                uint64_t* dst = hw + (int64_t)tok * li.pitch + row;
-                                for (int r = 0; r < p.replicas; ++r) st_relaxed_u64(dst + r * li.rep_stride, ((uint64_t)want << 32) | __float_as_uint(yv[e4]));
-                            }
-                        }
-                    } else {
-                        // a word holds two consecutive rows of one token: lanes g and g^1 exchange halves.  Even g stores
-                        // rows (g, g+1), odd g stores rows (g+7, g+8), for tokens 2t and 2t+1.
-                        const bool odd = g & 1;
-                        const float s0 = __shfl_xor_sync(0xffffffffu, odd ? yv[0] : yv[2], 4);
-                        const float s1 = __shfl_xor_sync(0xffffffffu, odd ? yv[1] : yv[3], 4);
-                        const int64_t rlo = odd ? row0 + 7 : row0;             // first (even) row of my word
-                        const float lo[2] = {odd ? s0 : yv[0], odd ? s1 : yv[1]};
-                        const float hi2[2] = {odd ? yv[2] : s0, odd ? yv[3] : s1};
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const int tok = 2 * t + e;
-                            if (rlo < li.N && tok < p.M) {
-                                const XT v0 = from_f32<XT>(lo[e]);
-                                const XT v1 = from_f32<XT>(rlo + 1 < li.N ? hi2[e] : 0.0f);
-                                const uint32_t pair = (uint32_t)*reinterpret_cast<const unsigned short*>(&v0) |
-                                                      ((uint32_t)*reinterpret_cast<const unsigned short*>(&v1) << 16);
-                                uint64_t* dst = hw + (int64_t)tok * li.pitch + (rlo >> 1);
-                                for (int r = 0; r < p.replicas; ++r) st_relaxed_u64(dst + r * li.rep_stride, ((uint64_t)want << 32) | pair);
-                            }
-                        }
-                    }
-                    __syncwarp();
-                    if (lane == 0) red_relaxed_add(&ctrl->counter[l * CH_CNT_STRIDE], 1u);     // hint for the pollers
-                } else {
-#pragma unroll
-                    for (int e4 = 0; e4 < 4; ++e4) {
-                        const int tok = 2 * t + (e4 & 1);
-                        const int64_t row = (e4 >> 1) ? row1 : row0;
-                        if (row < li.N && tok < p.M) {
-                            const int64_t o = (int64_t)tok * p.ldo + row;
-                            if (p.out_dtype == TB200_BF16) reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(yv[e4]);
-                            else if (p.out_dtype == TB200_F16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(yv[e4]);
-                            else reinterpret_cast<float*>(p.out)[o] = yv[e4];
-                        }
-                    }
-                }
-                CH_STAMP_AUX(l, 5);
-            }
-            w.next(lay, L, b, G);
-        }
     }
     // ---- the last CTA to finish advances the generation (counters are cumulative across calls, never reset) ----
-    __syncthreads();
+    asm volatile("bar.sync 2, %0;" ::"n"(CH_THREADS - 32) : "memory");     // every warp but the producer
     if (threadIdx.x == 0) {
         __threadfence();
         const uint32_t old = atomicAdd(&ctrl->done, 1u);
         if (old == (uint32_t)G - 1u) {
             ctrl->done = 0u;
+            ctrl->last_M = (uint32_t)M;
             __threadfence();
             atomicAdd(&ctrl->gen, 1u);
         }
@@ -657,9 +665,9 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
 static inline int64_t ch_round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 static inline int ch_nks(int64_t K) { return (int)((K + 4095) / 4096); }
 
-static size_t chain_smem(int n_layers, int stages, int nslots, uint32_t img_bytes) {
-    return 1024 + (size_t)stages * CH_TILE + ((img_bytes + 127u) & ~127u) + (size_t)nslots * CH_SLOT_U4 * 16 +
-           64 * 4 * 2 + 8 * 4 * 2 + (size_t)n_layers * sizeof(LayerInfo) + (2 * CH_MAX_STAGES + 2 * CH_MAX_SLOTS) * 8 + 64;
+static size_t chain_smem(int n_layers, int stages, int nslots, uint32_t img_bytes, int M) {
+    return 1024 + (size_t)stages * CH_TILE + ((img_bytes + 127u) & ~127u) + (size_t)nslots * CH_TEAM * CH_ROWS * M * 4 +
+           2 * (size_t)M * CH_DOT_WARPS * 4 * 2 + 16 * 4 + (size_t)n_layers * sizeof(LayerInfo) + (2 * CH_MAX_STAGES + 2 * CH_MAX_SLOTS) * 8 + 64;
 }
 
 }  // namespace tb200
@@ -716,25 +724,24 @@ extern "C" int tb200_chain_plan_build(const tb200_chain_layer* layers_in, int n_
         o.N = (int32_t)in.N; o.K = (int32_t)in.K; o.nks = ch_nks(in.K);
         o.row_blocks = (int32_t)((in.N + CH_ROWS - 1) / CH_ROWS);
         o.clip_val = fabsf(in.clip_val); o.act = in.act;
-        // inter-layer buffer: per token ceil(N / elements-per-word) flagged words {value(s), flag}, rows 16-byte aligned
-        o.h_pitch = (int32_t)ch_round_up((in.N + (act_elem_size == 4 ? 0 : 1)) / (act_elem_size == 4 ? 1 : 2), 2);
+        // inter-layer buffer: two sets (even / odd call) of M_max rows of N rounded up to whole 16-element groups
+        o.h_pitch = (int32_t)ch_round_up(in.N, CH_ROWS);
         o.h_off = off;
-        o.h_rep_stride = ch_round_up((int64_t)M_max * o.h_pitch * 8, 256) / 8;
-        if (l + 1 < n_layers) off += o.h_rep_stride * 8 * CH_REPLICAS;
+        o.h_set_stride = ch_round_up((int64_t)M_max * o.h_pitch * act_elem_size, 256);
+        if (l + 1 < n_layers) off += o.h_set_stride * 2;
         if (o.nks > max_nks) max_nks = o.nks;
         if (o.row_blocks > max_rb) max_rb = o.row_blocks;
     }
     hd->magic = CH_MAGIC; hd->n_layers = (uint32_t)n_layers;
     hd->max_nks = max_nks; hd->max_rb = max_rb; hd->M_max = (int32_t)M_max; hd->esz = act_elem_size;
     hd->ws_bytes = off;
-    hd->replicas = CH_REPLICAS;
     *workspace_bytes = (size_t)off;
     return TB200_OK;
 }
 
-template <typename XT>
-static int launch_chain(const ChainHeader* plan_dev, const ChainParams& p, int n_layers, int grid, size_t smem, cudaStream_t s) {
-    auto kern = gemv_chain_kernel<XT>;
+template <typename XT, int M>
+static int launch_chain(const ChainHeader* plan_dev, const ChainParams& p, int grid, size_t smem, cudaStream_t s) {
+    auto kern = gemv_chain_kernel<XT, M>;
     static SmemOptIn optin;
     TB_CUDA(ensure_dynamic_smem(kern, optin, smem));
     cudaLaunchConfig_t cfg = {};
@@ -750,6 +757,15 @@ static int launch_chain(const ChainHeader* plan_dev, const ChainParams& p, int n
     TB_CUDA(cudaLaunchKernelEx(&cfg, kern, plan_dev, p));
     TB_LAUNCH_CHECK();
     return TB200_OK;
+}
+template <typename XT>
+static int launch_chain_m(const ChainHeader* plan_dev, const ChainParams& p, int M, int grid, size_t smem, cudaStream_t s) {
+    switch (M) {
+        case 1: return launch_chain<XT, 1>(plan_dev, p, grid, smem, s);
+        case 2: return launch_chain<XT, 2>(plan_dev, p, grid, smem, s);
+        case 3: return launch_chain<XT, 3>(plan_dev, p, grid, smem, s);
+        default: return launch_chain<XT, 4>(plan_dev, p, grid, smem, s);
+    }
 }
 
 // plan_host: the blob tb200_chain_plan_build filled (read on the host for shapes); plan_dev: its device copy.
@@ -770,27 +786,26 @@ extern "C" int tb200_chain_forward(const void* plan_host, const void* plan_dev, 
     TB_REQUIRE((uintptr_t)plan_dev % 64 == 0 && (uintptr_t)workspace % 256 == 0, "chain_forward: plan_dev must be 64-byte and workspace 256-byte aligned");
     ChainParams p = {};
     p.x = x; p.ldx = ldx; p.out = out; p.ldo = ldo; p.out_dtype = out_dtype;
-    p.ws = (uint8_t*)workspace; p.M = (int)M;
+    p.ws = (uint8_t*)workspace;
     p.img_bytes = (uint32_t)(hd->max_nks * 4096 * (int)M);
     p.pdl = flags & TB200_FLAG_PDL;
     p.trace = kAblate ? (long long*)tb_knob("TB200_CHAIN_TRACE_PTR", 0) : nullptr;
-    p.inflight = (int)tb_knob("TB200_CHAIN_INFLIGHT", 4);
-    p.replicas = (int)tb_knob("TB200_CHAIN_REPLICAS", hd->replicas);
-    if (p.replicas < 1 || p.replicas > hd->replicas) p.replicas = hd->replicas;
+    p.gate = (int)tb_knob("TB200_CHAIN_GATE", 1);
     // ring depth: as many 16 KB stages as fit beside the image and the slots (bytes in flight per SM)
+    p.n_layers = L;
     p.nslots = 2 * CH_AUX;     // a multiple of the aux-warp count: slot q is always served by aux warp q % CH_AUX
     int st = CH_MAX_STAGES;
-    while (st > 2 && chain_smem(L, st, p.nslots, p.img_bytes) > 227 * 1024) --st;
-    if (chain_smem(L, st, p.nslots, p.img_bytes) > 227 * 1024) {
+    while (st > 2 && chain_smem(L, st, p.nslots, p.img_bytes, (int)M) > 227 * 1024) --st;
+    if (chain_smem(L, st, p.nslots, p.img_bytes, (int)M) > 227 * 1024) {
         set_error("chain_forward: M=%lld with K up to %d does not fit the shared-memory activation image", (long long)M, hd->max_nks * 4096);
         return TB200_ENOTSUP;
     }
     p.stages = st;
     const int grid = hd->max_rb < sm_count() ? hd->max_rb : sm_count();
-    const size_t smem = chain_smem(L, p.stages, p.nslots, p.img_bytes);
+    const size_t smem = chain_smem(L, p.stages, p.nslots, p.img_bytes, (int)M);
     switch (x_dtype) {
-        case TB200_F32:  return launch_chain<float>((const ChainHeader*)plan_dev, p, L, grid, smem, (cudaStream_t)stream);
-        case TB200_BF16: return launch_chain<__nv_bfloat16>((const ChainHeader*)plan_dev, p, L, grid, smem, (cudaStream_t)stream);
-        default:         return launch_chain<__half>((const ChainHeader*)plan_dev, p, L, grid, smem, (cudaStream_t)stream);
+        case TB200_F32:  return launch_chain_m<float>((const ChainHeader*)plan_dev, p, (int)M, grid, smem, (cudaStream_t)stream);
+        case TB200_BF16: return launch_chain_m<__nv_bfloat16>((const ChainHeader*)plan_dev, p, (int)M, grid, smem, (cudaStream_t)stream);
+        default:         return launch_chain_m<__half>((const ChainHeader*)plan_dev, p, (int)M, grid, smem, (cudaStream_t)stream);
     }
 }

@@ -436,7 +436,7 @@ class ChainPlan:
     bias [N] | None, clip_val, activation)`` with ``activation`` in {None, "gelu_new", "relu"}; every layer consumes the
     previous one's output (``K_l == N_{l-1}``).  The reference wires fc1 -> gelu_new -> fc2 this way
     (impl/tf/moondream/layers.py:32-43; the activation is applied after the clip, ternary.py:245-246).
-    The plan keeps references to the tensors it points to.  Decode shapes only: ``M <= 8`` tokens per call."""
+    The plan keeps references to the tensors it points to.  Decode shapes only: ``M <= 4`` tokens per call."""
 
     def __init__(self, layers, in_features: int, dtype=torch.bfloat16, max_tokens: int = L.CHAIN_MAX_M):
         assert 1 <= len(layers) <= L.CHAIN_MAX_LAYERS and 1 <= max_tokens <= L.CHAIN_MAX_M
@@ -467,21 +467,22 @@ class ChainPlan:
         self.n_layers = len(layers)
 
     def hidden(self, layer: int, M: int) -> torch.Tensor:
-        """The inter-layer activations the last call left in the workspace: output of ``layer`` (not the last one),
-        ``[M, N_layer]`` in the plan's dtype, decoded from the kernel's flagged 8-byte words {value(s), flag}.  For
-        parity tests."""
+        """The inter-layer activations the LAST call left in the workspace: output of ``layer`` (not the last one),
+        ``[M, N_layer]`` in the plan's dtype.  The kernel stores them bit-inverted (an all-zero element means "not written")
+        in the buffer set of the call's generation parity.  For parity tests."""
         import struct
         base = 64 + 192 * layer
         raw = bytes(self.plan_host[base + 128: base + 192].tolist())
         N, = struct.unpack_from("<i", raw, 16)
         pitch, = struct.unpack_from("<i", raw, 44)
-        off, = struct.unpack_from("<q", raw, 48)
-        words = self.workspace[off: off + M * pitch * 8].view(torch.int32).view(M, pitch, 2)
-        assert bool((words[:, : (N + 1) // 2 if self.dtype != torch.float32 else N, 1] == words[0, 0, 1]).all()), "stale flag"
-        vals = words[:, :, 0].contiguous()
-        if self.dtype == torch.float32:
-            return vals.view(torch.float32)[:, :N]
-        return vals.view(self.dtype).view(M, 2 * pitch)[:, :N]
+        off, set_stride = struct.unpack_from("<qq", raw, 48)
+        gen = int(self.workspace[:4].view(torch.int32).item())            # generation AFTER the call
+        esz = torch.empty((), dtype=self.dtype).element_size()
+        start = off + ((gen - 1) & 1) * set_stride
+        ity = torch.int32 if esz == 4 else torch.int16
+        enc = self.workspace[start: start + M * pitch * esz].view(ity).view(M, pitch)[:, :N]
+        assert bool((enc != 0).all()), "element not written"
+        return (~enc).view(self.dtype)
 
     def forward(self, x: torch.Tensor, out: torch.Tensor | None = None, out_dtype=None, pdl: bool = False) -> torch.Tensor:
         _cuda(x)

@@ -52,7 +52,7 @@ def check_chain(plan, cpu_layers, x, out, dtype):
         h_in = got
 
 
-@pytest.mark.parametrize("M", [1, 2, 3, 5, 8])
+@pytest.mark.parametrize("M", [1, 2, 3, 4])
 @pytest.mark.parametrize("dims,acts", [
     ((256, 512, 256), ("gelu_new", None)),                      # an MLP block
     ((1024, 4096, 1024), ("gelu_new", None)),
@@ -135,7 +135,7 @@ def test_chain_deep_stack_full_size(cuda):
     acts = ("gelu_new", None) * 8
     gpu, cpu = build(dims, acts, seed=7, cuda=cuda)
     plan = ops.ChainPlan(gpu, dims[0], torch.bfloat16)
-    for M in (1, 8):
+    for M in (1, 4):
         x = torch.randn(M, dims[0], generator=torch.Generator().manual_seed(M)).bfloat16().to(cuda)
         out = plan.forward(x)
         check_chain(plan, cpu, x, out, torch.bfloat16)

@@ -57,7 +57,7 @@ def main():
     with torch.cuda.stream(st):
         for (d, f, n) in ((4096, 11008, args.mlps), (2048, 8192, min(64, 2 * args.mlps))):
             layers = build_stack(d, f, n, dev, d + f)
-            for M in (1, 8):
+            for M in (1, 2, 4):
                 x = torch.randn(M, d, device=dev, dtype=torch.bfloat16)
                 plan = ops.ChainPlan(layers, d, torch.bfloat16, max_tokens=M)
                 out = torch.empty(M, d, device=dev, dtype=torch.bfloat16)
