@@ -149,3 +149,56 @@ def test_chain_rejects_bad_arguments(cuda):
     plan = ops.ChainPlan(gpu, 256, torch.bfloat16)
     with pytest.raises(TernaryB200Error):
         plan.forward(torch.zeros(9, 256, dtype=torch.bfloat16, device=cuda))
+
+
+# ---- the module-level API: ChainedLinears / TernaryMLP (ternary_vllm_b200/blocks.py) ----
+def _mlp(cuda, d, f, seed):
+    import ternary_vllm_b200 as tb
+    torch.manual_seed(seed)
+    fc1, fc2 = tb.ScaledTernaryLinear(d, f).to(cuda), tb.ScaledTernaryLinear(f, d).to(cuda)
+    fc1.scale.data.fill_(1.0 / d ** 0.5)
+    fc2.scale.data.fill_(1.0 / f ** 0.5)
+    return tb.TernaryMLP(fc1, fc2, "gelu_new").eval()
+
+
+@pytest.mark.parametrize("M", [1, 3])
+def test_mlp_module_matches_oracle_and_layerwise(cuda, M):
+    d, f = 512, 1536
+    mlp = _mlp(cuda, d, f, 5)
+    x = torch.randn(M, d, generator=torch.Generator().manual_seed(2)).bfloat16().to(cuda)
+    with torch.no_grad():
+        y = mlp(x)                                   # one persistent launch
+        h = torch.nn.functional.gelu(mlp.fc1(x), approximate="tanh")
+        y2 = mlp.fc2(h)                              # layer by layer through the drop-in layers
+    cpu = [(ref_int8.codes_of(l.weights.detach().cpu().numpy()), l.scale.detach().cpu().numpy(), l.bias.detach().cpu().numpy(),
+            l.maxval, a) for l, a in zip(mlp.layers, mlp.activations)]
+    plan = mlp._plan(x.dtype, x.device)
+    check_chain(plan, cpu, x, y, torch.bfloat16)
+    # CUDA tanhf in the kernel vs torch's gelu: the hidden bf16 values may differ by an ulp on a few elements
+    err = (y.float() - y2.float()).abs().max().item()
+    assert err <= 0.02 * max(1.0, y2.float().abs().max().item())
+
+
+def test_mlp_module_repacks_and_falls_back(cuda):
+    d, f = 256, 512
+    mlp = _mlp(cuda, d, f, 7)
+    x = torch.randn(2, d, generator=torch.Generator().manual_seed(3)).bfloat16().to(cuda)
+    with torch.no_grad():
+        y0 = mlp(x).clone()
+        mlp.fc1.weights.data[:] = torch.randn(f, d, generator=torch.Generator().manual_seed(9)).clip(-1, 1).to(cuda)   # the reference's write idiom
+        y1 = mlp(x)
+        assert not torch.equal(y0, y1)
+        cpu = [(ref_int8.codes_of(l.weights.detach().cpu().numpy()), l.scale.detach().cpu().numpy(), l.bias.detach().cpu().numpy(),
+                l.maxval, a) for l, a in zip(mlp.layers, mlp.activations)]
+        check_chain(mlp._plan(x.dtype, x.device), cpu, x, y1, torch.bfloat16)
+        # more tokens than the chain kernel serves: layer-by-layer path, same module
+        xb = torch.randn(40, d, generator=torch.Generator().manual_seed(4)).bfloat16().to(cuda)
+        yb = mlp(xb)
+        assert yb.shape == (40, d)
+        ref = mlp.fc2(torch.nn.functional.gelu(mlp.fc1(xb), approximate="tanh"))
+        assert torch.equal(yb, ref)
+    # training: autograd path (fake-quant STE), gradients reach the latent weights
+    mlp.train()
+    xt = torch.randn(2, d, device=cuda)
+    mlp(xt).sum().backward()
+    assert mlp.fc1.weights.grad is not None and mlp.fc2.weights.grad is not None
