@@ -114,27 +114,67 @@ def _cpu_case(K, N, M):
     return _CPU_DATA[key]
 
 
-def cpu_forward_sample(cases, iters, warm):
-    """Times the oracle's restatement of ScaledTernaryLinear.forward (binary/modules.py:101-109,
-    including the per-call re-ternarisation the reference performs) on the host cores.
-    One layer per case.  Returns (bytes, seconds, per-case list)."""
+def cpu_forward_sample(cases, iters, warm, kind="c1"):
+    """Times the reference forward on the host cores, one layer per case; per-case time = MEDIAN of `iters` runs after
+    `warm` warm-ups.  kind "c1": the oracle's restatement of ScaledTernaryLinear.forward as shipped
+    (binary/modules.py:101-109, INCLUDING the per-call re-ternarisation of the latent weights); kind "c2": the same
+    forward with the weights ternarised once outside the timed region (F.linear(x, q) * scale + bias, clip) -- the fair
+    matmul-only baseline.  Returns (bytes, seconds, per-case list)."""
     import torch
     from oracle import ref_modules as om
     torch.set_num_threads(os.cpu_count() or 1)
     total_b, total_t, per = 0.0, 0.0, []
     for (K, N, M) in cases:
         W, x, scale, bias = _cpu_case(K, N, M)
+        if kind == "c2":
+            q = om.ternary_codes(W).to(torch.float32)
+            fn = lambda: om.packed_ternary_matmul(x, q, scale, bias, 100.0)
+        else:
+            fn = lambda: om.scaled_linear_forward(x.clone(), W, scale, bias, 100.0, "ternary")
         for _ in range(warm):
-            om.scaled_linear_forward(x.clone(), W, scale, bias, 100.0, "ternary")
-        t0 = time.perf_counter()
+            fn()
+        ts = []
         for _ in range(iters):
-            om.scaled_linear_forward(x.clone(), W, scale, bias, 100.0, "ternary")
-        dt = (time.perf_counter() - t0) / iters
+            t0 = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t0)
+        dt = statistics.median(ts)
         b = algorithmic_bytes(K, N, M)
         per.append({"K": K, "N": N, "M": M, "ms": dt * 1e3, "gbs": b / dt / 1e9, "tokens_per_s": M / dt})
         total_b += b
         total_t += dt
     return total_b, total_t, per
+
+
+def cpu_other_baselines(iters=5, warm=2):
+    """the reference's own micro-benchmark `ternary_mm` at 1024^2 next to torch.matmul
+    (matrix_mul_tests.py:6-41) and the weight-prep baseline linear_to_quantized(..., "ternary") on 4096 x 11008
+    (binary/modules.py:275-298), oracle ports on the host cores, median of `iters` after `warm` warm-ups."""
+    import torch
+    from oracle import ref_modules as om
+    torch.set_num_threads(os.cpu_count() or 1)
+
+    def med(fn, n_it=iters, n_warm=warm):
+        for _ in range(n_warm):
+            fn()
+        ts = []
+        for _ in range(n_it):
+            t0 = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t0)
+        return statistics.median(ts)
+    g = torch.Generator().manual_seed(5)
+    m = torch.randn(1024, 1024, generator=g)
+    tm = torch.randint(-1, 2, (1024, 1024), generator=g).float()
+    t_tmm = med(lambda: om.ternary_mm(m, tm))
+    t_mm = med(lambda: torch.matmul(m, tm.T))
+    W = torch.randn(11008, 4096, generator=g) * 0.02
+    t_init = med(lambda: om.ternary_init(W, "uniform"), n_it=max(3, iters - 2), n_warm=1)
+    return {"c3_ternary_mm_1024": {"ms": t_tmm * 1e3, "dense_matmul_ms": t_mm * 1e3,
+                                   "what": "ternary_mm (matrix_mul_tests.py:29-37) vs torch.matmul, 1024x1024 fp32"},
+            "c4_linear_to_quantized_ternary_4096x11008": {"ms": t_init * 1e3, "gbs_one_pass": 4096 * 11008 * 4 / t_init / 1e9,
+                                                          "what": "ternary branch of linear_to_quantized (binary/modules.py:275-298): "
+                                                                  "10-iteration thresholded mean + latent rescale, uniform scale, fp32"}}
 
 
 def run_reference(args):
@@ -308,6 +348,7 @@ def run_b200(args):
             b = algorithmic_bytes(K, N, M)
             per_case.append({"K": K, "N": N, "M": M, "layers": R, "us_per_layer": t * 1e6, "us_per_call": t_call * 1e6,
                              "launches_per_call": nl, "gbs": b / t / 1e9, "frac_hbm_measured": b / t / 1e9 / pk["hbm_gbs"],
+                             "frac_hbm_spec_8TBs": b / t / 1e9 / 8000.0,
                              "tokens_per_s": M / t,
                              "chain": {"us_per_layer": t_chain / R * 1e6, "launches_per_layer": nlc / R,
                                        "gbs": b / (t_chain / R) / 1e9,
@@ -330,11 +371,18 @@ def run_b200(args):
     # ---- CPU baseline: bounded sample on this box's host cores ----
     cb = None
     if not args.no_cpu:
-        b, t, per = cpu_forward_sample(cases, 2, 1)
+        b, t, per = cpu_forward_sample(cases, 5, 2, "c1")
+        b2, t2, per2 = cpu_forward_sample(cases, 5, 2, "c2")
         cb = {"value": b / t / 1e9, "unit": "GB/s", "cores": torch.get_num_threads(), "kind": "port",
-              "sample": "one layer per sweep case, 1 warm-up + 2 timed forwards each (oracle port of the reference "
-                        "forward incl. per-call re-ternarisation, torch CPU fp32)",
-              "cases": per}
+              "sample": "C1: one layer per sweep case, median of 5 timed forwards after 2 warm-ups each (oracle port of the "
+                        "reference forward incl. its per-call re-ternarisation, torch CPU fp32)",
+              "cases": per,
+              "c2_pre_ternarised": {"value": b2 / t2 / 1e9, "unit": "GB/s", "cases": per2,
+                                    "what": "F.linear(x, q) * scale + bias, clip with q ternarised once (matmul-only baseline), "
+                                            "same cases, median of 5 after 2 warm-ups"},
+              "gpu_over_c1": {"device": value / (b / t / 1e9), "e2e": e2e["value"] / (b / t / 1e9)},
+              "gpu_over_c2": {"device": value / (b2 / t2 / 1e9), "e2e": e2e["value"] / (b2 / t2 / 1e9)}}
+        cb.update(cpu_other_baselines())
 
     line = {
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": 1, "steps": args.steps, "warmup": max(3, args.warmup),
@@ -343,7 +391,8 @@ def run_b200(args):
         "config": CONFIG_N1, "tokens_per_s": step_tokens * args.steps / (ms * 1e-3),
         "frac_hbm_measured": value / pk["hbm_gbs"], "clocks": clocks,
         "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
-        "cases": per_case, "roofline": roofline, "gemm": gemm, "vit_l14": None if args.no_gemm else run_vit(dev),
+        "cases": per_case, "roofline": roofline, "mlp_chain": None if args.no_extra else run_mlp(dev, pk),
+        "prep": None if args.no_extra else run_prep(dev, pk), "gemm": gemm, "vit_l14": None if args.no_gemm else run_vit(dev),
         "cpu_baseline": cb,
     }
     print(json.dumps(line))
@@ -391,6 +440,14 @@ def run_e2e(args, lib, dev, rings, cases, step_bytes):
 
     for _ in range(3):
         step()
+    # the outputs this timing is about: the host-buffer call must reproduce the device-resident call bit for bit
+    from ternary_vllm_b200 import ops
+    for c in (cases[0], cases[-1]):
+        ring = rings[c[:2]]
+        want = ops.gemv_stream(hx[c].to(dev), ring.packed, ring.scale, ring.bias, 100.0)
+        torch.cuda.synchronize()
+        if not torch.equal(want.cpu(), hy[c]):
+            raise RuntimeError(f"e2e: tb200_gemv_stream_host output differs from the device-resident call for case {c}")
     steps = max(3, min(args.steps, 20))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
@@ -450,6 +507,142 @@ def run_vit(dev):
     return rows
 
 
+def _timed_flush(fn, flush, reps=10):
+    """Median device time of fn() with L2 flushed (256 MB memset) before every timed call."""
+    import torch
+    ts = []
+    for _ in range(reps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1) * 1e-3)
+    return statistics.median(ts)
+
+
+def run_prep(dev, pk):
+    """north_star subsystem (1) and (2) as standalone kernels: weight prep (quantize_pack, ternary_init, clip_latent) on a
+    4096 x 11008 fp32 latent matrix and the per-token int8 activation quantiser, in GB/s of ALGORITHMIC bytes against the
+    measured HBM rate.  ternary_init streams the matrix 12 times (mean, 10 thresholded means, rescale) and writes it once;
+    the matrix (180 MB) exceeds L2, so every pass is an HBM pass."""
+    import torch
+    from ternary_vllm_b200 import ops
+    g = torch.Generator(device=dev).manual_seed(21)
+    N, K = 11008, 4096
+    W = torch.randn(N, K, generator=g, device=dev) * 0.02
+    flush = torch.empty(int(256e6), dtype=torch.uint8, device=dev)
+    rows = []
+
+    def add(name, fn, nbytes, note=None):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        t = _timed_flush(fn, flush)
+        r = {"kernel": name, "us": t * 1e6, "algorithmic_bytes": nbytes, "gbs": nbytes / t / 1e9,
+             "frac_hbm_measured": nbytes / t / 1e9 / pk["hbm_gbs"], "frac_hbm_spec_8TBs": nbytes / t / 1e9 / 8000.0}
+        if note:
+            r["note"] = note
+        rows.append(r)
+    Wc = W.clip(-1, 1)
+    add("quantize_pack fp32 4096x11008 (tb200_quantize_pack)", lambda: ops.quantize_pack(Wc, "ternary"), N * K * 4 + N * K // 4)
+    Wb = Wc.bfloat16()
+    add("quantize_pack bf16 4096x11008", lambda: ops.quantize_pack(Wb, "ternary"), N * K * 2 + N * K // 4)
+    Wl = (W * 60).contiguous()
+    add("clip_latent fp32 4096x11008 (tb200_clip_latent)", lambda: ops.clip_latent_(Wl), 2 * N * K * 4)
+    add("ternary_init uniform fp32 4096x11008 (tb200_ternary_init)", lambda: ops.ternary_init(W, per_row=False), 13 * N * K * 4,
+        "12 reads + 1 write of the matrix (11 reductions with a grid-wide dependency between them)")
+    add("ternary_init per-row fp32 4096x11008", lambda: ops.ternary_init(W, per_row=True), 2 * N * K * 4,
+        "one CTA keeps a row on chip for all 11 passes: 1 read + 1 write")
+    for (M, Kx) in ((4096, 4096), (8224, 1024), (8224, 4096)):
+        x = torch.randn(M, Kx, generator=g, device=dev, dtype=torch.bfloat16)
+        add(f"quant_act_i8 bf16 {M}x{Kx} (tb200_quant_act_i8, kperm)", lambda: ops.quant_act_i8(x, kperm=True), M * Kx * 3 + M * 8)
+    return rows
+
+
+def run_mlp(dev, pk):
+    """DEPENDENT layers through the module API (TernaryMLP / ChainedLinears -> tb200_chain_forward): a
+    stack of MLP blocks d -> f -> gelu_new -> d whose packed weights exceed L2, (a) as ONE chain call over the whole
+    stack, (b) as one call per MLP block (what a decoder does: attention / residual / norm sit between the blocks), calls
+    joined by programmatic dependent launch, (c) as one launch per layer (the round-1 `chain`) -- all as CUDA graphs."""
+    import torch
+    import ternary_vllm_b200 as tb
+    from ternary_vllm_b200 import ops
+    st = torch.cuda.Stream(dev)
+    rows = []
+
+    def time_graph(fn, reps):
+        fn()
+        st.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=st):
+            fn()
+        for _ in range(3):
+            gr.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        st.synchronize()
+        e0.record(st)
+        for _ in range(reps):
+            gr.replay()
+        e1.record(st)
+        st.synchronize()
+        return e0.elapsed_time(e1) * 1e-3 / reps
+    with torch.cuda.stream(st), torch.no_grad():
+        for (d, f, n) in ((4096, 11008, 16), (2048, 8192, 40)):
+            torch.manual_seed(d + f)
+            blocks = []
+            for _ in range(n):
+                with torch.device(dev):                             # parameters are born on the GPU
+                    fc1, fc2 = tb.ScaledTernaryLinear(d, f), tb.ScaledTernaryLinear(f, d)
+                fc1.scale.data.fill_(1.0 / math.sqrt(d))
+                fc2.scale.data.fill_(1.0 / math.sqrt(f))
+                for l in (fc1, fc2):
+                    l.freeze(release_latent=True)                   # deployment form: packed weights only
+                blocks.append(tb.TernaryMLP(fc1, fc2, "gelu_new").eval())
+            whole = tb.ChainedLinears([l for b_ in blocks for l in b_.layers], [a for b_ in blocks for a in b_.activations]).eval()
+            for M in (1, 4):
+                x = torch.randn(M, d, device=dev, dtype=torch.bfloat16)
+                nbytes = n * (algorithmic_bytes(d, f, M) + algorithmic_bytes(f, d, M))
+
+                def per_block():
+                    y = x
+                    for b_ in blocks:
+                        y = b_(y, pdl=True)
+                    return y
+
+                def per_layer():
+                    y = x
+                    for b_ in blocks:
+                        y = torch.nn.functional.gelu(b_.fc1(y), approximate="tanh")
+                        y = b_.fc2(y)
+                    return y
+                t1 = time_graph(lambda: whole(x), 20)
+                t2 = time_graph(per_block, 10)
+                t3 = time_graph(per_layer, 5)
+                mk = lambda t: {"us_per_layer": t / (2 * n) * 1e6, "gbs": nbytes / t / 1e9, "frac_hbm_measured": nbytes / t / 1e9 / pk["hbm_gbs"],
+                                "tokens_per_s_per_block": M / (t / n)}
+                rows.append({"d": d, "f": f, "blocks": n, "layers": 2 * n, "M": M, "packed_MB": n * 2 * d * f / 4 / 1e6,
+                             "one_chain_call": mk(t1), "call_per_mlp_block_pdl": mk(t2), "launch_per_layer": mk(t3),
+                             "api": "ternary_vllm_b200.TernaryMLP / ChainedLinears (tb200_chain_forward)"})
+            del blocks, whole
+            torch.cuda.empty_cache()
+    return rows
+
+
+def int8_peak(seconds=2.0):
+    """Measured tcgen05 kind::i8 issue-rate ceiling of this GPU (tools/microbench/umma_i8_rate.cu, built by build())."""
+    import subprocess
+    exe = os.path.join(ROOT, "tools", "microbench", "umma_i8_rate.bin")
+    if not os.path.exists(exe):
+        return None
+    try:
+        out = subprocess.run([exe, "--seconds", str(seconds)], capture_output=True, text=True, timeout=120)
+        return json.loads(out.stdout.strip().splitlines()[-1])
+    except Exception as e:          # the roofline then falls back to the spec figure, and says so
+        return {"error": repr(e)}
+
+
 def run_gemm(dev, pk, M=4096, K=4096, N=11008):
     import torch
     from ternary_vllm_b200 import ops
@@ -496,13 +689,44 @@ def run_gemm(dev, pk, M=4096, K=4096, N=11008):
     ops_ = 2.0 * M * N * K
     mm, al = statistics.median(t_mm) * 1e-3, statistics.median(t_all) * 1e-3
     tops = ops_ / mm / 1e12
+    # sustained: >= 2 s of back-to-back launches with the clock sampler on (the burst figure above is ten isolated launches)
+    sampler = ClockSampler(dev.index or 0)
+    n_sus = max(50, int(2.2 / mm))
+    torch.cuda.synchronize()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n_sus):
+        ops.gemm_i8(q, s, sq, K, packed, scale, bias, 100.0, out=out)
+    e1.record()
+    torch.cuda.synchronize()
+    sus_clocks = sampler.stop()
+    t_sus = e0.elapsed_time(e1) * 1e-3
+    tops_sus = ops_ * n_sus / t_sus / 1e12
+    pkq = int8_peak()
+    peak_burst = peak_sus = None
+    if pkq and "ts_n192" in pkq:
+        peak_burst = max(pkq[k]["tops_burst"] for k in ("ss_n256", "ss_n192", "ts_n192"))
+        peak_sus = max(pkq[k]["tops_sustained"] for k in ("ss_n256", "ts_n192"))
+    roof = {"bound": "tensor", "achieved": tops, "unit": "TOP/s",
+            "peak": peak_burst or 4500.0, "frac": tops / (peak_burst or 4500.0),
+            "peak_source": ("measured: tools/microbench/umma_i8_rate.cu, best burst rate of tcgen05.mma kind::i8 issued back to back on all SMs"
+                            if peak_burst else "spec: dense int8 4.5 POPS (microbenchmark binary missing)"),
+            "frac_of_spec_4500": tops / 4500.0, "frac_of_2x_measured_bf16": tops / (2 * pk["bf16_tflops"]),
+            "traffic": GEMM_TRAFFIC_BYTES}
     return {"workload": f"configs[2] prefill GEMM M={M} K={K} N={N}, int8 activations, tcgen05 kind::i8 (weights through TMEM)",
             "ms_gemm": mm * 1e3, "ms_quant_plus_gemm": al * 1e3, "tops": tops, "tops_incl_act_quant": ops_ / al / 1e12,
             "tokens_per_s": M / al,
-            "roofline": {"bound": "tensor", "achieved": tops, "peak": 4500.0, "unit": "TOP/s", "frac": tops / 4500.0,
-                         "peak_source": "spec: dense int8 4.5 POPS (no measured int8 peak in MEASURED_PEAKS.json)",
-                         "frac_of_2x_measured_bf16": tops / (2 * pk["bf16_tflops"]), "traffic": None},
-            "l2_policy": "L2 flushed (256 MB memset) between timed iterations"}
+            "sustained": {"tops": tops_sus, "seconds": t_sus, "launches": n_sus, "clocks": sus_clocks,
+                          "frac_of_measured_sustained_int8": (tops_sus / peak_sus) if peak_sus else None,
+                          "frac_of_spec_4500": tops_sus / 4500.0},
+            "int8_peak": pkq, "roofline": roof,
+            "l2_policy": "L2 flushed (256 MB memset) between timed iterations (burst); none for the sustained run (operands 62 MB + 90 MB output)"}
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of umma_ts_kernel on M=4096 K=4096 N=11008 from the ncu capture under profiles/
+# (None until that capture exists)
+GEMM_TRAFFIC_BYTES = None
 
 
 def main():
@@ -513,6 +737,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-gemm", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the mlp_chain and prep blocks")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

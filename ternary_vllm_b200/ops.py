@@ -232,14 +232,18 @@ def gemv_f32(x, packed, scale, bias, clip_val):
     return out
 
 
-def gemm_i8(q_x, s_x, sum_qx, K, packed, scale, bias, clip_val, out_dtype=torch.bfloat16, debug=False):
+def gemm_i8(q_x, s_x, sum_qx, K, packed, scale, bias, clip_val, out_dtype=torch.bfloat16, debug=False, out=None):
     """tcgen05 GEMM on pre-quantised (kperm=1) activations.  ``debug`` also returns acc i32 [M,N]."""
     _cuda(q_x, s_x, sum_qx, packed, scale, bias)
     M = q_x.shape[0]
     N = packed.shape[0]
     scale = _f32_or_none(scale, N, q_x.device)
     bias = _f32_or_none(bias, N, q_x.device)
-    out = torch.empty((M, N), dtype=out_dtype, device=q_x.device)
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=q_x.device)
+    else:
+        assert out.shape == (M, N) and out.stride(1) == 1
+        out_dtype = out.dtype
     acc = torch.empty((M, N), dtype=torch.int32, device=q_x.device) if debug else None
     with torch.cuda.device(q_x.device):
         L.check(L.lib().tb200_gemm_i8(q_x.data_ptr(), q_x.stride(0), s_x.data_ptr(), sum_qx.data_ptr(), M, K,
