@@ -601,7 +601,9 @@ def run_mlp(dev, pk):
                     l.freeze(release_latent=True)                   # deployment form: packed weights only
                 blocks.append(tb.TernaryMLP(fc1, fc2, "gelu_new").eval())
             whole = tb.ChainedLinears([l for b_ in blocks for l in b_.layers], [a for b_ in blocks for a in b_.activations]).eval()
-            for M in (1, 4):
+            for m_ in blocks + [whole]:
+                m_.chain_max_tokens = 8                              # measure the chain kernel at every M (the default routes M > 2 layer by layer)
+            for M in (1, 8):
                 x = torch.randn(M, d, device=dev, dtype=torch.bfloat16)
                 nbytes = n * (algorithmic_bytes(d, f, M) + algorithmic_bytes(f, d, M))
 

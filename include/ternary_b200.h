@@ -221,7 +221,7 @@ int tb200_gemv_stream_host(const void* x_host, int x_dtype, int64_t M, int64_t K
 #define TB200_ACT_GELU_TANH 1 /* gelu_new / keras gelu(approximate=True): 0.5x(1+tanh(sqrt(2/pi)(x+0.044715x^3))) */
 #define TB200_ACT_RELU      2
 #define TB200_CHAIN_MAX_LAYERS 128
-#define TB200_CHAIN_MAX_M 4
+#define TB200_CHAIN_MAX_M 8
 #define TB200_CHAIN_CTRL_BYTES 16640 /* control block at the start of the workspace: 128 B + one 128-byte line per layer */
 typedef struct tb200_chain_layer {
     const uint8_t* packed;   /* [N, ld_packed] format C, device */

@@ -19,7 +19,7 @@ FMT_A, FMT_B, FMT_C = 0, 1, 2
 GEMV_MAX_M = 32
 FLAG_PDL = 1
 ACT_NONE, ACT_GELU_TANH, ACT_RELU = 0, 1, 2
-CHAIN_MAX_M, CHAIN_MAX_LAYERS = 4, 128
+CHAIN_MAX_M, CHAIN_MAX_LAYERS = 8, 128
 
 
 class ChainLayerDesc(C.Structure):

@@ -4,7 +4,7 @@
 (impl/tf/moondream/ternary.py:245-246, 298-299; utils/conversion.py:185-196).
 
 ``ChainedLinears`` keeps that wiring and picks the launch form per call:
-  * decode (M <= ops.L.CHAIN_MAX_M tokens, no autograd): ONE persistent launch for the whole chain
+  * decode (M <= ``chain_max_tokens`` tokens, default 2, no autograd): ONE persistent launch for the whole chain
     (``tb200_chain_forward``): weights stream across the layer boundaries, activations are re-quantised to int8 inside
     the kernel, the activation function runs in the producing layer's epilogue;
   * anything else: layer by layer through the layers' own forward (GEMV / tcgen05 GEMM, or the fake-quant training
@@ -54,6 +54,9 @@ class ChainedLinears(nn.Module):
         self.layers = nn.ModuleList(layers)
         self.activations = activations
         self._plans = {}            # (dtype, device) -> (key, ChainPlan)
+        # every CTA of the chain kernel re-quantises all M activation rows of a layer for itself (~2 us per token and layer), so
+        # above two tokens the layer-by-layer launches win (tools/chain_bench.py); the kernel itself serves up to CHAIN_MAX_M
+        self.chain_max_tokens = 2
 
     # -- plan cache: rebuilt when any layer re-packs (the plan holds raw pointers into the packed buffers) --
     def _plan(self, dtype, device):
@@ -79,7 +82,7 @@ class ChainedLinears(nn.Module):
         if len(self.layers) > ops.L.CHAIN_MAX_LAYERS or x.dtype not in (torch.bfloat16, torch.float16, torch.float32):
             return False
         M = x.numel() // max(1, x.shape[-1])
-        if M < 1 or M > ops.L.CHAIN_MAX_M:
+        if M < 1 or M > self.chain_max_tokens:
             return False
         for l in self.layers:
             if not l.act_quant or (l._needs_autograd(x) and not l._frozen) or (l.training and not l._has_scale):

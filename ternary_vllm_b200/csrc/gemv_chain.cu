@@ -31,7 +31,7 @@ constexpr int CH_WARP_PRODUCER = CH_DOT_WARPS, CH_WARP_AUX0 = CH_DOT_WARPS + 1;
 constexpr int CH_THREADS = (CH_DOT_WARPS + 1 + CH_AUX) * 32;
 constexpr int CH_DOT_THREADS = CH_DOT_WARPS * 32;
 constexpr int CH_MAX_STAGES = 12, CH_MAX_SLOTS = 8;
-constexpr int CH_CACHE = 3;                        // 16-element groups a thread keeps in registers between its two passes
+constexpr int CH_CACHE_WORDS = 16;                 // raw 32-bit words of activations a thread keeps in registers between its two passes
 constexpr uint32_t CH_MAGIC = 0x7b200c43u;
 
 // device-side layer descriptor inside the plan blob (192 bytes, 64-byte aligned: the tensor map is used in place)
@@ -66,6 +66,7 @@ struct ChainParams {
     uint32_t img_bytes;
     int pdl;
     int gate;             // 1: one thread per CTA waits for the layer's row-block counter before the data words are read
+    int dbg;              // experiment build only: 1 no IMMAs, 2 no LOP3 (unmasked operands), 4 no weight LDS
     long long* trace;     // experiment build only: per CTA and layer, time stamps (tools/chain_trace.py)
 };
 __device__ __forceinline__ long long chain_gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
@@ -85,11 +86,29 @@ struct LayerInfo {
     float clip; int act, pitch, one_box;
 };
 
-__device__ __forceinline__ int dp4a_us(uint32_t a_u8, uint32_t b_s8, int c) {
-    int d;
-    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_u8), "r"(b_s8), "r"(c));
-    return d;
+__device__ __forceinline__ void imma_u8s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
+// shared-memory accesses through 32-bit addresses kept in ordinary registers.  The addresses are made OPAQUE to the compiler
+// (keep_reg) once per kernel: otherwise it rematerialises every shared-memory base from scratch at each use -- an
+// S2UR SR_CgaCtaId + ~10 dependent uniform-datapath instructions per mbarrier / LDS address inside the per-tile loop, which
+// measured ~600 cycles per 16 KB tile with the dot products compiled out (tools/chain_ablate.sh).
+__device__ __forceinline__ void keep_reg(uint32_t& v) { asm volatile("" : "+r"(v)); }
+__device__ __forceinline__ void keep_reg(int& v) { asm volatile("" : "+r"(v)); }
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ int lds32(uint32_t a) {
+    int v;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
     uint32_t v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -179,9 +198,10 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
     uint8_t* gbase = smem_dyn + (base - smem_u32(smem_dyn));
-    // ring[stages][16 KB] | image[M][groups] uint4 | slots[nslots][8 warps][16 rows][M] int | red_f[2][M][16] | red_i[2][M][16] |
+    // ring[stages][16 KB] | image[M][groups] uint4 | slots[nslots][16 warps][16 rows][MP] int | red_f[2][M][16] | red_i[2][M][16] |
     // sx[2][8] | layers | barriers
-    constexpr int SLOT_INTS = CH_TEAM * CH_ROWS * M;
+    constexpr int MP = M | 1;                                   // odd token pitch of a slot row: conflict-free reads
+    constexpr int SLOT_INTS = CH_TEAM * CH_ROWS * MP;
     const uint32_t sRing = base;
     uint4* img = reinterpret_cast<uint4*>(gbase + (size_t)p.stages * CH_TILE);
     int* slots = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(img) + ((p.img_bytes + 127u) & ~127u));
@@ -189,7 +209,7 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
     int* red_i = reinterpret_cast<int*>(red_f + 2 * M * CH_DOT_WARPS);
     float* sx_sm = reinterpret_cast<float*>(red_i + 2 * M * CH_DOT_WARPS);
     LayerInfo* lay = reinterpret_cast<LayerInfo*>(sx_sm + 16);
-    const int L = p.n_layers;                 // from the parameter bank: rematerialised for free (read from the plan it was spilled)
+    const int L = p.n_layers;
     uint64_t* bars = reinterpret_cast<uint64_t*>(lay + L);
     const uint32_t sBar = smem_u32(bars);
     auto bar_full = [&](int s) { return sBar + 8u * s; };
@@ -251,6 +271,10 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
         // lane -> row (lane & 15); the two half-warps add four warps' partials each, then take alternate tokens
         const int a = warp - CH_WARP_AUX0;
         const int row_l = lane & 15, half = lane >> 4;
+        uint32_t a_bar = sBar;                                                                        // see keep_reg
+        uint32_t a_sl = smem_u32(slots) + 4u * ((half * (CH_TEAM / 2) * CH_ROWS + row_l) * MP);  // this lane's partials in slot 0
+        int nslots_a = p.nslots;
+        keep_reg(a_bar); keep_reg(a_sl); keep_reg(nslots_a);
         if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");      // earlier kernels may still read out / the h buffers
         const uint32_t gen = ld_acquire_u32(&ctrl->gen);
         const int set = (int)(gen & 1u);
@@ -260,8 +284,8 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
             if ((w.n % CH_AUX) == a) {
                 const LayerInfo& li = lay[w.l];
                 const int l = w.l, par = l & 1;
-                const int sq_i = w.n % p.nslots;
-                const uint32_t spar = (uint32_t)(w.n / p.nslots) & 1u;
+                const int sq_i = w.n % nslots_a;
+                const uint32_t spar = (uint32_t)(w.n / nslots_a) & 1u;
                 const int64_t row = (int64_t)w.rb * CH_ROWS + row_l;
                 float sc = 1.0f, bi = 0.0f;                               // requested before the wait for the partial sums
                 if (li.scale && row < li.N) sc = __ldg(li.scale + row);
@@ -276,15 +300,15 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
                     }
                 }
                 CH_CLK_AUX(l, 17);
-                mbar_wait(bar_sfull(sq_i), spar);
+                mbar_wait(a_bar + 8u * (2 * CH_MAX_STAGES + sq_i), spar);
                 CH_CLK_AUX(l, 18);
-                const int* sl = slots + (size_t)sq_i * SLOT_INTS + (half * 4 * CH_ROWS + row_l) * M;
+                const uint32_t sl = a_sl + 4u * (sq_i * SLOT_INTS);
                 int tot[M]; float sxv[M]; int sumq[M];
 #pragma unroll
                 for (int m = 0; m < M; ++m) {
                     int v = 0;
 #pragma unroll
-                    for (int wv = 0; wv < 4; ++wv) v += sl[wv * CH_ROWS * M + m];
+                    for (int wv = 0; wv < CH_TEAM / 2; ++wv) v += lds32(sl + 4u * (wv * CH_ROWS * MP + m));
                     tot[m] = v;
                     sxv[m] = sx_sm[par * 8 + m];
                     int sq = 0;
@@ -296,7 +320,7 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
                     sumq[m] = sq;
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar_sempty(sq_i));                // partial sums and token scalars are in registers
+                if (lane == 0) mbar_arrive(a_bar + 8u * (2 * CH_MAX_STAGES + CH_MAX_SLOTS + sq_i));   // partial sums and token scalars are in registers
                 float yv[M];
 #pragma unroll
                 for (int m = 0; m < M; ++m) {
@@ -347,39 +371,41 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
     } else {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
         // ===================== activation image of every layer + dot products =====================
-        // Two teams of eight warps take alternate row blocks.  In a team, warp q owns 128-byte K segment q of every tile (512
-        // weights of each of the 16 rows); lane (r4, ch) owns 16-byte chunk ch of rows r4, r4+4, r4+8, r4+12.  The 64 int8
-        // activations that chunk multiplies stay in registers for the whole layer (K <= 4096), so a tile costs 4 LDS.128 +
-        // 64 LOP3 + 64 M IDP.4A per lane: 2-bit field i of every packed byte is masked in place (value code * 4^i) and dotted
-        // with the matching activation bytes; the four field sums are recombined exactly with shifts.  IDP.4A and LOP3 issue
-        // on different pipes (tools/microbench/int_rates.cu: 3.0-3.2 warp instructions/clk/SM for the mix with >= 16 warps;
-        // the legacy IMMA path computes eight token columns whatever M is and tops out at 0.5 IMMA/clk/SM).
+        // Two teams of eight warps take alternate row blocks, so that one team's per-row-block latencies (barrier waits, the
+        // recombination, the slot hand-off) overlap the other team's MMAs.  In a team, warp wq owns 128-byte K segment wq of
+        // every tile (512 weights of each of the 16 rows).  Lane (g, t) holds the mma.sync.m16n8k32 A fragments of rows g and
+        // g + 8: 2-bit field i of every packed byte is masked IN PLACE (value code * 4^i) and multiplied with the int8
+        // activations that meet it -- four accumulator sets, recombined exactly with shifts at the end of the row block.  The
+        // B fragments (token = g, zero for g >= M) of a whole k-slice stay in registers.  A tile costs a warp 4 LDS.128 + 64 LOP3 + 16 IMMA whatever M is.
         const int ct = threadIdx.x;                          // 0..511
-        const int r4 = lane >> 3, ch = lane & 7;
+        const int g = lane >> 2, t = lane & 3;
         const int team = warp >> 3, wq = warp & 7;
-        const int stages = p.stages, nslots = p.nslots;
+        int stages = p.stages, nslots = p.nslots;
+        keep_reg(stages); keep_reg(nslots);
+        // shared-memory addresses of this thread, computed ONCE (see keep_reg)
+        uint32_t a_bar = sBar;                                                                   // mbarriers
+        uint32_t a_w = base + wq * (CH_ROWS * CH_SEG) + g * CH_SEG;                               // row g of this warp's segment in stage 0
+        uint32_t a_slot = smem_u32(slots) + 4u * ((wq * CH_ROWS + g) * MP + 2 * t);               // partial sums in slot 0
+        uint32_t a_img = smem_u32(img) + 16u * (wq * 32 + 2 * t);                                 // image words of token 0, k-slice 0
+        keep_reg(a_bar); keep_reg(a_w); keep_reg(a_slot); keep_reg(a_img);
+        const uint32_t sw0 = (uint32_t)((2 * t) ^ g) << 4, sw1 = (uint32_t)((2 * t + 1) ^ g) << 4;   // SWIZZLE_128B: chunk ^ (row & 7)
         if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");      // x (and the control block) come from earlier kernels
         const uint32_t gen = ld_acquire_u32(&ctrl->gen);
         const int set = (int)(gen & 1u);
-        int s = 0; uint32_t ph = 0;                          // weight ring (global tile sequence of this CTA)
-        int sq = 0; uint32_t spar = 0;                       // slot ring
-        uint4 xa[M][4];                                      // activation words of this lane's chunk, current k-slice
-        // byte offsets of this lane's four weight chunks inside a tile (SWIZZLE_128B: chunk ^ (row & 7))
-        uint32_t woff[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int row = r4 + 4 * q;
-            woff[q] = wq * (CH_ROWS * CH_SEG) + row * CH_SEG + ((ch ^ (row & 7)) << 4);
-        }
+        int sq = 0; uint32_t spar = 0;                       // slot ring (every row block of the CTA takes the next slot)
+        uint4 bq[2][4];                                      // image words of packed words 0..3 of this lane's two chunks: .x/.y/.z/.w = field 0..3
         int cur = -1, ngroups = 0;
         long long tr_full = 0, tr_slot = 0;                  // experiment build: cycles this thread waited for tiles / for a slot
         Walk w; w.start(lay, L, b);
-        auto load_x = [&](int ks) {
+        auto load_b = [&](int ks) {
 #pragma unroll
-            for (int m = 0; m < M; ++m)
+            for (int pp = 0; pp < 2; ++pp)
 #pragma unroll
-                for (int jj = 0; jj < 4; ++jj) xa[m][jj] = img[m * ngroups + ks * 256 + wq * 32 + jj * 8 + ch];
+                for (int j = 0; j < 4; ++j)
+                    bq[pp][j] = g < M ? lds128(a_img + 16u * (g * ngroups + ks * 256 + j * 8 + pp)) : make_uint4(0u, 0u, 0u, 0u);
         };
+        int s = 0; uint32_t ph = 0;                          // weight ring (global tile sequence of this CTA)
+        constexpr int RW = 4 * (int)sizeof(XT);              // 32-bit words per 16-element group (8 or 16)
         while (w.l < L) {
             const LayerInfo& li = lay[w.l];
             if (w.l != cur) {
@@ -411,57 +437,71 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
                     }
                 }
                 CH_CLK(l, 9);
-                // one 16-element group of token m as fp32 (zero beyond K).  Layer 0 reads the caller's plain activations;
-                // later layers read what the previous layer's epilogue stored (inverted bits, zero = not written yet): a group
-                // with a missing element is simply fetched again.
-                auto fetch = [&](int m, int gi, float (&v)[16]) -> bool {
+                // one 16-element group of token m as PLAIN bits of the activation dtype (zero beyond K).  Layer 0 reads the
+                // caller's activations; later layers read what the previous layer's epilogue stored (inverted bits, zero = not
+                // written yet): a group with a missing element is simply fetched again.
+                auto fetch = [&](int m, int gi, uint32_t (&r)[RW]) -> bool {
                     if (16 * gi >= K) {
 #pragma unroll
-                        for (int tt = 0; tt < 16; ++tt) v[tt] = 0.0f;
+                        for (int j = 0; j < RW; ++j) r[j] = 0u;
                         return true;
                     }
                     if (l == 0) {
                         const XT* src = xin + (int64_t)m * p.ldx + 16 * (int64_t)gi;
                         if (vec0 && 16 * gi + 16 <= K) {
-                            constexpr int NV = sizeof(XT) == 4 ? 4 : 2;
 #pragma unroll
-                            for (int j = 0; j < NV; ++j) {
-                                const uint4 r = ld_cg_u4(reinterpret_cast<const uint4*>(src) + j);
-                                const XT* e = reinterpret_cast<const XT*>(&r);
-#pragma unroll
-                                for (int tt = 0; tt < 16 / NV; ++tt) v[j * (16 / NV) + tt] = to_f32(e[tt]);
+                            for (int j = 0; j < RW / 4; ++j) {
+                                const uint4 q4 = ld_cg_u4(reinterpret_cast<const uint4*>(src) + j);
+                                r[4 * j] = q4.x; r[4 * j + 1] = q4.y; r[4 * j + 2] = q4.z; r[4 * j + 3] = q4.w;
                             }
                         } else {
 #pragma unroll
-                            for (int tt = 0; tt < 16; ++tt) v[tt] = (16 * gi + tt < K) ? to_f32(ld_cg_elem<XT>(src + tt)) : 0.0f;
+                            for (int j = 0; j < RW; ++j) r[j] = 0u;
+#pragma unroll
+                            for (int tt = 0; tt < 16; ++tt)
+                                if (16 * gi + tt < K) {
+                                    const XT e = ld_cg_elem<XT>(src + tt);
+                                    if (sizeof(XT) == 4) r[tt * RW / 16] = *reinterpret_cast<const uint32_t*>(&e);
+                                    else r[tt * RW / 16] |= (uint32_t)(*reinterpret_cast<const unsigned short*>(&e)) << (16 * (tt & 1));
+                                }
                         }
                         return true;
                     }
                     const uint8_t* src = hin + (int64_t)m * pitch_b + (int64_t)gi * (16 * sizeof(XT));
                     uint32_t miss = 0;
-                    if (sizeof(XT) == 2) {
-                        uint32_t r[8];
-                        ld_relaxed_256(src, r);
+#pragma unroll
+                    for (int h = 0; h < RW / 8; ++h) {
+                        uint32_t q8[8];
+                        ld_relaxed_256(src + 32 * h, q8);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
-                            miss |= (r[j] - 0x00010001u) & ~r[j] & 0x80008000u;      // a 16-bit lane that is zero
-                            const uint32_t wbits = ~r[j];
-                            const XT* e = reinterpret_cast<const XT*>(&wbits);
-                            v[2 * j] = to_f32(e[0]); v[2 * j + 1] = to_f32(e[1]);
-                        }
-                    } else {
-#pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            uint32_t r[8];
-                            ld_relaxed_256(src + 32 * h, r);
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) { miss |= (uint32_t)(r[j] == 0u); v[8 * h + j] = __uint_as_float(~r[j]); }
+                            if (sizeof(XT) == 2) miss |= (q8[j] - 0x00010001u) & ~q8[j] & 0x80008000u;      // a 16-bit lane that is zero
+                            else miss |= (uint32_t)(q8[j] == 0u);
+                            r[8 * h + j] = ~q8[j];
                         }
                     }
                     return miss == 0u;
                 };
-                auto quantise_group = [&](const float (&v)[16], float inv, int m, int gi, int& ls) {
+                auto to_f32v = [&](const uint32_t (&r)[RW], float (&v)[16]) {
+#pragma unroll
+                    for (int tt = 0; tt < 16; ++tt) {
+                        if (sizeof(XT) == 4) v[tt] = __uint_as_float(r[tt * RW / 16]);
+                        else {
+                            const unsigned short hb = (unsigned short)(r[tt * RW / 16] >> (16 * (tt & 1)));
+                            v[tt] = to_f32(*reinterpret_cast<const XT*>(&hb));
+                        }
+                    }
+                };
+                auto group_amax = [&](const uint32_t (&r)[RW]) -> float {
+                    float v[16]; to_f32v(r, v);
+                    float am = 0.0f;
+#pragma unroll
+                    for (int tt = 0; tt < 16; ++tt) am = fmaxf(am, fabsf(v[tt]));
+                    return am;
+                };
+                auto quantise_group = [&](const uint32_t (&r)[RW], float inv, int m, int gi, int& ls) {
                     if (gi >= ngroups) return;    // beyond the image (odd number of 256-group slices)
+                    float v[16]; to_f32v(r, v);
                     uint32_t qb[16];              // low byte = two's-complement int8 code (rint via the 1.5 * 2^23 trick)
 #pragma unroll
                     for (int tt = 0; tt < 16; ++tt) {
@@ -489,155 +529,149 @@ gemv_chain_kernel(const ChainHeader* __restrict__ plan, const ChainParams p) {
                 };
                 // NOTE: register arrays below are indexed with compile-time constants only.  With ~225 KB of the SM carved out as
                 // shared memory there is practically no L1 left, so a local-memory (stack) array costs an L2 round trip per access.
-                constexpr int NKC = CH_CACHE / M > 0 ? CH_CACHE / M : 1;   // 512-group slices per token whose groups fit the register cache
-                if (nu <= NKC) {
-                    float vc[M][NKC][16];
-                    // all loads of the thread are issued before the first use (ONE L2 round trip), and again until every element is there
-                    uint32_t spins = 0;
-                    bool ok;
-                    do {
-                        ok = true;
+                constexpr int NKC = CH_CACHE_WORDS / (M * RW) > 4 ? 4 : CH_CACHE_WORDS / (M * RW);   // 512-group slices per token whose raw words fit the register cache
+                bool cached = false;
+                if constexpr (NKC > 0) {
+                    if (nu <= NKC) {
+                        cached = true;
+                        uint32_t rc[M][NKC][RW];
+                        // all loads of the thread are issued before the first use (ONE L2 round trip), and again until every element is there
+                        uint32_t spins = 0;
+                        bool ok;
+                        do {
+                            ok = true;
 #pragma unroll
-                        for (int m = 0; m < M; ++m)
+                            for (int m = 0; m < M; ++m)
+#pragma unroll
+                                for (int u = 0; u < NKC; ++u)
+                                    if (u < nu) ok = fetch(m, u * CH_DOT_THREADS + ct, rc[m][u]) && ok;
+                            if (!ok && ++spins > 20000000u) __trap();
+                        } while (!ok);
+                        CH_CLK(l, 10);
+                        if (kAblate && p.trace && ct == 0) CH_SLOT(l, 7) = spins;
+#pragma unroll
+                        for (int m = 0; m < M; ++m) {            // pass A: per-token absmax
+                            float amax = 0.0f;
 #pragma unroll
                             for (int u = 0; u < NKC; ++u)
-                                if (u < nu) ok = fetch(m, u * CH_DOT_THREADS + ct, vc[m][u]) && ok;
-                        if (!ok && ++spins > 20000000u) __trap();
-                    } while (!ok);
-                    CH_CLK(l, 10);
-                    if (kAblate && p.trace && ct == 0) CH_SLOT(l, 7) = spins;
+                                if (u < nu) amax = fmaxf(amax, group_amax(rc[m][u]));
+                            const uint32_t am = __reduce_max_sync(0xffffffffu, __float_as_uint(amax));
+                            if (lane == 0) red_f[(par * M + m) * CH_DOT_WARPS + warp] = __uint_as_float(am);
+                        }
+                        asm volatile("bar.sync 1, %0;" ::"n"(CH_DOT_THREADS) : "memory");
+                        CH_CLK(l, 11);
 #pragma unroll
-                    for (int m = 0; m < M; ++m) {            // pass A: per-token absmax
-                        float amax = 0.0f;
+                        for (int m = 0; m < M; ++m) {            // pass B: quantise into the image (zero beyond K), code sums
+                            const float inv = token_scale(m);
+                            int ls = 0;
 #pragma unroll
-                        for (int u = 0; u < NKC; ++u)
-                            if (u < nu) {
-#pragma unroll
-                                for (int tt = 0; tt < 16; ++tt) amax = fmaxf(amax, fabsf(vc[m][u][tt]));
-                            }
-                        const uint32_t am = __reduce_max_sync(0xffffffffu, __float_as_uint(amax));
-                        if (lane == 0) red_f[(par * M + m) * CH_DOT_WARPS + warp] = __uint_as_float(am);
+                            for (int u = 0; u < NKC; ++u)
+                                if (u < nu) quantise_group(rc[m][u], inv, m, u * CH_DOT_THREADS + ct, ls);
+                            ls = __reduce_add_sync(0xffffffffu, ls);
+                            if (lane == 0) red_i[(par * M + m) * CH_DOT_WARPS + warp] = ls;
+                        }
                     }
-                    asm volatile("bar.sync 1, %0;" ::"n"(CH_DOT_THREADS) : "memory");
-                    CH_CLK(l, 11);
-#pragma unroll
-                    for (int m = 0; m < M; ++m) {            // pass B: quantise into the image (zero beyond K), code sums
-                        const float inv = token_scale(m);
-                        int ls = 0;
-#pragma unroll
-                        for (int u = 0; u < NKC; ++u)
-                            if (u < nu) quantise_group(vc[m][u], inv, m, u * CH_DOT_THREADS + ct, ls);
-                        ls = __reduce_add_sync(0xffffffffu, ls);
-                        if (lane == 0) red_i[(par * M + m) * CH_DOT_WARPS + warp] = ls;
-                    }
-                } else {
-#pragma unroll
+                }
+                if (!cached) {
+#pragma unroll 1
                     for (int m = 0; m < M; ++m) {            // pass A (the data is fetched again in pass B: L2)
                         float amax = 0.0f;
                         for (int u = 0; u < nu; ++u) {
-                            float v[16];
+                            uint32_t r[RW];
                             uint32_t spins = 0;
-                            while (!fetch(m, u * CH_DOT_THREADS + ct, v)) { if (++spins > 20000000u) __trap(); }
-#pragma unroll
-                            for (int tt = 0; tt < 16; ++tt) amax = fmaxf(amax, fabsf(v[tt]));
+                            while (!fetch(m, u * CH_DOT_THREADS + ct, r)) { if (++spins > 20000000u) __trap(); }
+                            amax = fmaxf(amax, group_amax(r));
                         }
                         const uint32_t am = __reduce_max_sync(0xffffffffu, __float_as_uint(amax));
                         if (lane == 0) red_f[(par * M + m) * CH_DOT_WARPS + warp] = __uint_as_float(am);
                     }
                     asm volatile("bar.sync 1, %0;" ::"n"(CH_DOT_THREADS) : "memory");
                     CH_CLK(l, 11);
-#pragma unroll
+#pragma unroll 1
                     for (int m = 0; m < M; ++m) {
                         const float inv = token_scale(m);
                         int ls = 0;
                         for (int u = 0; u < nu; ++u) {
-                            float v[16];
-                            (void)fetch(m, u * CH_DOT_THREADS + ct, v);           // verified in pass A
-                            quantise_group(v, inv, m, u * CH_DOT_THREADS + ct, ls);
+                            uint32_t r[RW];
+                            (void)fetch(m, u * CH_DOT_THREADS + ct, r);           // verified in pass A
+                            quantise_group(r, inv, m, u * CH_DOT_THREADS + ct, ls);
                         }
                         ls = __reduce_add_sync(0xffffffffu, ls);
                         if (lane == 0) red_i[(par * M + m) * CH_DOT_WARPS + warp] = ls;
                     }
                 }
                 CH_CLK(l, 14);
-                // image complete for every warp (both teams read all of it); sx_sm and red_i (read by the aux warps) are ordered
-                // by this barrier + the first slot hand-off of the layer
+                // image complete for every warp; sx_sm and red_i (read by the aux warps) are ordered by this barrier + the first
+                // slot hand-off of the layer
                 asm volatile("bar.sync 1, %0;" ::"n"(CH_DOT_THREADS) : "memory");
-                load_x(0);
+                load_b(0);
                 CH_CLK(l, 12);
                 tr_full = 0; tr_slot = 0;
             }
-            // ---------- one row block: team (n & 1) computes it (one K segment of every k-slice per warp), the other team only
-            // advances its ring position ----------
+            // ---------- one row block: team (n & 1) computes it (one K segment of every k-slice per warp) ----------
             const int nks = li.nks;
             if ((w.n & 1) == team) {
-                int rs[4][M];
+                const int rbi = (w.rb - b) / G;                      // index of this row block among the CTA's blocks of the layer
+                const int tsl = rbi < 3 ? (rbi < 2 ? 1 + 3 * rbi : 21) : -1;
+                if (kAblate && p.trace && ct == 0 && tsl >= 0) CH_SLOT(w.l, tsl) = clock64();
+                int acc[4][4];
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
+                for (int i = 0; i < 4; ++i)
 #pragma unroll
-                    for (int m = 0; m < M; ++m) rs[q][m] = 0;
+                    for (int e = 0; e < 4; ++e) acc[i][e] = 0;
 #pragma unroll 1
                 for (int k2 = 0; k2 < nks; ++k2) {
-                    if (nks > 1) load_x(k2);           // K > 4096: the activation words of this k-slice (a single slice stays in registers)
                     const long long tw0 = kAblate && p.trace ? clock64() : 0;
-                    mbar_wait(bar_full(s), ph);
+                    mbar_wait(a_bar + 8u * s, ph);
                     if (kAblate && p.trace) tr_full += clock64() - tw0;
-                    const uint8_t* tile = gbase + s * CH_TILE;
-                    uint4 wv[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) wv[q] = *reinterpret_cast<const uint4*>(tile + woff[q]);
+                    const uint32_t aw = a_w + s * CH_TILE;
+                    uint4 lo0 = make_uint4(aw, s, ph, 3u), hi0 = lo0, lo1 = lo0, hi1 = lo0;
+                    if (!(kAblate && (p.dbg & 4))) {
+                        lo0 = lds128(aw + sw0); hi0 = lds128(aw + 8 * CH_SEG + sw0);
+                        lo1 = lds128(aw + sw1); hi1 = lds128(aw + 8 * CH_SEG + sw1);
+                    }
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_empty(s));            // this warp's part of the tile lives in registers now
+                    if (lane == 0) mbar_arrive(a_bar + 8u * (CH_MAX_STAGES + s));   // this warp's part of the tile lives in registers now
                     if (++s == stages) { s = 0; ph ^= 1u; }
+                    if (nks > 1) load_b(k2);           // K > 4096: the activation words of this k-slice (a single slice stays in registers)
+                    if (kAblate && (p.dbg & 1)) {
+                        acc[0][0] += (int)(lo0.x ^ hi0.y ^ lo1.z ^ hi1.w);
+                    } else {
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        int a[4][M];
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-#pragma unroll
-                            for (int m = 0; m < M; ++m) a[i][m] = 0;
-                        const uint32_t wq4[4] = {wv[q].x, wv[q].y, wv[q].z, wv[q].w};
-#pragma unroll
-                        for (int jj = 0; jj < 4; ++jj)
+                        for (int pp = 0; pp < 2; ++pp) {
+                            const uint4 lo = pp ? lo1 : lo0, hi = pp ? hi1 : hi0;
 #pragma unroll
                             for (int i = 0; i < 4; ++i) {
-                                const uint32_t mw = wq4[jj] & (0x03030303u << (2 * i));
-#pragma unroll
-                                for (int m = 0; m < M; ++m) {
-                                    const uint32_t xw = i == 0 ? xa[m][jj].x : i == 1 ? xa[m][jj].y : i == 2 ? xa[m][jj].z : xa[m][jj].w;
-                                    a[i][m] = dp4a_us(mw, xw, a[i][m]);
-                                }
+                                const uint32_t mk = 0x03030303u << (2 * i);
+                                const uint32_t b0 = i == 0 ? bq[pp][0].x : i == 1 ? bq[pp][0].y : i == 2 ? bq[pp][0].z : bq[pp][0].w;
+                                const uint32_t b1 = i == 0 ? bq[pp][1].x : i == 1 ? bq[pp][1].y : i == 2 ? bq[pp][1].z : bq[pp][1].w;
+                                imma_u8s8(acc[i], lo.x & mk, hi.x & mk, lo.y & mk, hi.y & mk, b0, b1);
                             }
 #pragma unroll
-                        for (int m = 0; m < M; ++m) rs[q][m] += a[0][m] + (a[1][m] >> 2) + (a[2][m] >> 4) + (a[3][m] >> 6);   // exact: set i is a multiple of 4^i
+                            for (int i = 0; i < 4; ++i) {
+                                const uint32_t mk = 0x03030303u << (2 * i);
+                                const uint32_t b2 = i == 0 ? bq[pp][2].x : i == 1 ? bq[pp][2].y : i == 2 ? bq[pp][2].z : bq[pp][2].w;
+                                const uint32_t b3 = i == 0 ? bq[pp][3].x : i == 1 ? bq[pp][3].y : i == 2 ? bq[pp][3].z : bq[pp][3].w;
+                                imma_u8s8(acc[i], lo.z & mk, hi.z & mk, lo.w & mk, hi.w & mk, b2, b3);
+                            }
+                        }
                     }
                 }
-                // sum over the eight chunk lanes, halving the number of live values at every step: lane ch ends with row
-                // r4 + 4 * (2 * (ch & 1) + ((ch >> 1) & 1)); the lanes with ch < 4 park this warp's K-partial
-                const bool o1 = ch & 1, o2 = ch & 2;
-                int fin[M];
+                // exact recombination: accumulator set i is a multiple of 4^i.  Lane (g, t) holds rows g / g + 8, tokens 2t / 2t + 1
+                int fin[4];
 #pragma unroll
-                for (int m = 0; m < M; ++m) {
-                    const int s0 = __shfl_xor_sync(0xffffffffu, o1 ? rs[0][m] : rs[2][m], 1);
-                    const int s1 = __shfl_xor_sync(0xffffffffu, o1 ? rs[1][m] : rs[3][m], 1);
-                    const int k0 = (o1 ? rs[2][m] : rs[0][m]) + s0, k1 = (o1 ? rs[3][m] : rs[1][m]) + s1;
-                    const int s2 = __shfl_xor_sync(0xffffffffu, o2 ? k0 : k1, 2);
-                    int v = (o2 ? k1 : k0) + s2;
-                    v += __shfl_xor_sync(0xffffffffu, v, 4);
-                    fin[m] = v;
-                }
+                for (int e = 0; e < 4; ++e) fin[e] = acc[0][e] + (acc[1][e] >> 2) + (acc[2][e] >> 4) + (acc[3][e] >> 6);
+                if (kAblate && p.trace && ct == 0 && tsl >= 0) CH_SLOT(w.l, tsl + 1) = clock64() + (fin[0] & 0);
                 const long long tw1 = kAblate && p.trace ? clock64() : 0;
-                mbar_wait(bar_sempty(sq), spar ^ 1u);
+                mbar_wait(a_bar + 8u * (2 * CH_MAX_STAGES + CH_MAX_SLOTS + sq), spar ^ 1u);
                 if (kAblate && p.trace) tr_slot += clock64() - tw1;
-                if (ch < 4) {
-                    const int row = r4 + 4 * (2 * (ch & 1) + ((ch >> 1) & 1));
-                    int* dst = slots + (size_t)sq * SLOT_INTS + (wq * CH_ROWS + row) * M;
-#pragma unroll
-                    for (int m = 0; m < M; ++m) dst[m] = fin[m];
-                }
+                const uint32_t dst = a_slot + 4u * (sq * SLOT_INTS);
+                if (2 * t < M) { sts32(dst, fin[0]); sts32(dst + 4u * (8 * MP), fin[2]); }
+                if (2 * t + 1 < M) { sts32(dst + 4u, fin[1]); sts32(dst + 4u * (8 * MP + 1), fin[3]); }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar_sfull(sq));
+                if (lane == 0) mbar_arrive(a_bar + 8u * (2 * CH_MAX_STAGES + sq));
                 CH_CLK(w.l, 13);
+                if (kAblate && p.trace && ct == 0 && tsl >= 0) CH_SLOT(w.l, tsl + 2) = clock64();
                 if (kAblate && p.trace && ct == 0) { CH_SLOT(w.l, 15) = tr_full; CH_SLOT(w.l, 16) = tr_slot; }
             } else {
                 s += nks;                                                // the other team's tiles
@@ -666,7 +700,7 @@ static inline int64_t ch_round_up(int64_t v, int64_t a) { return (v + a - 1) / a
 static inline int ch_nks(int64_t K) { return (int)((K + 4095) / 4096); }
 
 static size_t chain_smem(int n_layers, int stages, int nslots, uint32_t img_bytes, int M) {
-    return 1024 + (size_t)stages * CH_TILE + ((img_bytes + 127u) & ~127u) + (size_t)nslots * CH_TEAM * CH_ROWS * M * 4 +
+    return 1024 + (size_t)stages * CH_TILE + ((img_bytes + 127u) & ~127u) + (size_t)nslots * CH_TEAM * CH_ROWS * (M | 1) * 4 +
            2 * (size_t)M * CH_DOT_WARPS * 4 * 2 + 16 * 4 + (size_t)n_layers * sizeof(LayerInfo) + (2 * CH_MAX_STAGES + 2 * CH_MAX_SLOTS) * 8 + 64;
 }
 
@@ -764,7 +798,11 @@ static int launch_chain_m(const ChainHeader* plan_dev, const ChainParams& p, int
         case 1: return launch_chain<XT, 1>(plan_dev, p, grid, smem, s);
         case 2: return launch_chain<XT, 2>(plan_dev, p, grid, smem, s);
         case 3: return launch_chain<XT, 3>(plan_dev, p, grid, smem, s);
-        default: return launch_chain<XT, 4>(plan_dev, p, grid, smem, s);
+        case 4: return launch_chain<XT, 4>(plan_dev, p, grid, smem, s);
+        case 5: return launch_chain<XT, 5>(plan_dev, p, grid, smem, s);
+        case 6: return launch_chain<XT, 6>(plan_dev, p, grid, smem, s);
+        case 7: return launch_chain<XT, 7>(plan_dev, p, grid, smem, s);
+        default: return launch_chain<XT, 8>(plan_dev, p, grid, smem, s);
     }
 }
 
@@ -791,9 +829,10 @@ extern "C" int tb200_chain_forward(const void* plan_host, const void* plan_dev, 
     p.pdl = flags & TB200_FLAG_PDL;
     p.trace = kAblate ? (long long*)tb_knob("TB200_CHAIN_TRACE_PTR", 0) : nullptr;
     p.gate = (int)tb_knob("TB200_CHAIN_GATE", 1);
+    p.dbg = kAblate ? (int)tb_knob("TB200_CHAIN_DBG", 0) : 0;
     // ring depth: as many 16 KB stages as fit beside the image and the slots (bytes in flight per SM)
     p.n_layers = L;
-    p.nslots = 2 * CH_AUX;     // a multiple of the aux-warp count: slot q is always served by aux warp q % CH_AUX
+    p.nslots = M <= 4 ? 2 * CH_AUX : CH_AUX;     // a multiple of the aux-warp count: slot q is always served by aux warp q % CH_AUX
     int st = CH_MAX_STAGES;
     while (st > 2 && chain_smem(L, st, p.nslots, p.img_bytes, (int)M) > 227 * 1024) --st;
     if (chain_smem(L, st, p.nslots, p.img_bytes, (int)M) > 227 * 1024) {

@@ -440,7 +440,7 @@ class ChainPlan:
     bias [N] | None, clip_val, activation)`` with ``activation`` in {None, "gelu_new", "relu"}; every layer consumes the
     previous one's output (``K_l == N_{l-1}``).  The reference wires fc1 -> gelu_new -> fc2 this way
     (impl/tf/moondream/layers.py:32-43; the activation is applied after the clip, ternary.py:245-246).
-    The plan keeps references to the tensors it points to.  Decode shapes only: ``M <= 4`` tokens per call."""
+    The plan keeps references to the tensors it points to.  Decode shapes only: ``M <= 8`` tokens per call."""
 
     def __init__(self, layers, in_features: int, dtype=torch.bfloat16, max_tokens: int = L.CHAIN_MAX_M):
         assert 1 <= len(layers) <= L.CHAIN_MAX_LAYERS and 1 <= max_tokens <= L.CHAIN_MAX_M

@@ -52,7 +52,7 @@ def check_chain(plan, cpu_layers, x, out, dtype):
         h_in = got
 
 
-@pytest.mark.parametrize("M", [1, 2, 3, 4])
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 5, 7, 8])
 @pytest.mark.parametrize("dims,acts", [
     ((256, 512, 256), ("gelu_new", None)),                      # an MLP block
     ((1024, 4096, 1024), ("gelu_new", None)),
@@ -165,6 +165,7 @@ def _mlp(cuda, d, f, seed):
 def test_mlp_module_matches_oracle_and_layerwise(cuda, M):
     d, f = 512, 1536
     mlp = _mlp(cuda, d, f, 5)
+    mlp.chain_max_tokens = 8
     x = torch.randn(M, d, generator=torch.Generator().manual_seed(2)).bfloat16().to(cuda)
     with torch.no_grad():
         y = mlp(x)                                   # one persistent launch

@@ -50,19 +50,24 @@ def time_graph(fn, stream, reps):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mlps", type=int, default=32)
+    ap.add_argument("--fast", action="store_true", help="only the one-call form, 4096/11008 stack")
+    ap.add_argument("--tokens", type=int, nargs="*", default=[1, 2, 4, 8])
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     st = torch.cuda.Stream(dev)
     rows = []
     with torch.cuda.stream(st):
-        for (d, f, n) in ((4096, 11008, args.mlps), (2048, 8192, min(64, 2 * args.mlps))):
+        for (d, f, n) in ((4096, 11008, args.mlps), (2048, 8192, min(64, 2 * args.mlps)))[: 1 if args.fast else 2]:
             layers = build_stack(d, f, n, dev, d + f)
-            for M in (1, 2, 4):
+            for M in args.tokens:
                 x = torch.randn(M, d, device=dev, dtype=torch.bfloat16)
                 plan = ops.ChainPlan(layers, d, torch.bfloat16, max_tokens=M)
                 out = torch.empty(M, d, device=dev, dtype=torch.bfloat16)
                 t = time_graph(lambda: plan.forward(x, out=out), st, 20)
                 b = n * (alg_bytes(d, f, M) + alg_bytes(f, d, M))
+                if args.fast:
+                    print(json.dumps({"d": d, "f": f, "M": M, "one_call_us_per_layer": t / (2 * n) * 1e6, "one_call_gbs": b / t / 1e9}), flush=True)
+                    continue
                 # the same stack as one chain call PER MLP block (2 layers), calls chained with PDL
                 plans = [ops.ChainPlan(layers[2 * i: 2 * i + 2], d, torch.bfloat16, max_tokens=M) for i in range(n)]
                 bufs = [torch.empty(M, d, device=dev, dtype=torch.bfloat16) for _ in range(2)]

@@ -34,6 +34,8 @@ for l in range(2 * n):
     ok = v[:, 8] > 0
     md = lambda a, c: np.median(v[ok, a] - v[ok, c])
     print(f"{l:3d}  {md(9, 8):6.0f} | {md(10, 9):6.0f} | {md(11, 10):6.0f} | {md(14, 11):6.0f} | {md(12, 14):6.0f} | {md(13, 12):6.0f} ({np.median(v[ok, 15]):6.0f}, {np.median(v[ok, 16]):6.0f}) || {md(18, 17):6.0f} | {md(19, 18):6.0f} | {md(20, 19):6.0f}   aux done after mma {md(20, 13):6.0f}")
+    rb = " ".join(f"[{np.median(v[ok, a + 1] - v[ok, a]):5.0f} {np.median(v[ok, a + 2] - v[ok, a + 1]):5.0f}]" for a in (1, 4, 21))
+    print(f"      row blocks 0-2 [dot products incl. tile wait, slot hand-off]: {rb}   first block starts {np.median(v[ok, 1] - v[ok, 12]):5.0f} after load_b")
     continue
     print(f"{l:3d} "
           f"{md(18, 17):6.0f} | {md(19, 18):6.0f} | {md(20, 19):6.0f}   aux done after mma {md(20, 13):6.0f}")
