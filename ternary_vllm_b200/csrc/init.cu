@@ -85,6 +85,135 @@ ternary_init_row_kernel(const T* __restrict__ W, int64_t K, int iters,
     if (threadIdx.x == 0) scale[n] = m;
 }
 
+// ---- fast paths (rows of at most 4096 elements, 4-element vectors aligned): the row lives in REGISTERS ----
+// A thread owns up to four 4-element vectors (element index 4 * (t + 256 j) + e: coalesced 16 / 8 byte loads, all issued
+// before the first use).  Per-thread partial sums are fp32 over <= 16 values added as a balanced tree (relative error
+// <= 4 * 2^-24, far inside the 2e-6 contract of DESIGN.md section 2); everything ACROSS threads, rows and CTAs stays fp64 in a fixed order.
+template <typename T>
+__device__ __forceinline__ void load_vec4(const T* p, float (&v)[4]) {
+    if (sizeof(T) == 4) {
+        const float4 f = __ldg(reinterpret_cast<const float4*>(p));
+        v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+    } else {
+        const uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
+        const T* e = reinterpret_cast<const T*>(&u);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] = to_f32(e[i]);
+    }
+}
+__device__ __forceinline__ void block_sum2(double& s, long long& c, double* shd, long long* shl) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); c += __shfl_xor_sync(0xffffffffu, c, o); }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+    __syncthreads();
+    if (l == 0) { shd[w] = s; shl[w] = c; }
+    __syncthreads();
+    double ts = 0.0; long long tc = 0;
+    for (int i = 0; i < nw; ++i) { ts += shd[i]; tc += shl[i]; }   // fixed order -> deterministic
+    s = ts; c = tc;
+}
+// masked partial sum / count over the thread's register-resident vectors (balanced tree per vector, then across vectors)
+template <typename T>
+__device__ __forceinline__ void masked_partial(const float (&w)[4][4], int nv, float m, bool masked, bool first, float& ps, int& pc) {
+    float vs[4]; pc = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float a[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float av = fabsf(w[j][e]);
+            const bool on = j < nv && (!masked || kmeans_mask<T>(av, m, first));
+            a[e] = on ? av : 0.0f;
+            pc += on ? 1 : 0;
+        }
+        vs[j] = (a[0] + a[1]) + (a[2] + a[3]);
+    }
+    ps = (vs[0] + vs[1]) + (vs[2] + vs[3]);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+ternary_init_row_fast_kernel(const T* __restrict__ W, int64_t K, int iters, float* __restrict__ latent, float* __restrict__ scale) {
+    __shared__ double shd[8];
+    __shared__ long long shl[8];
+    const int64_t n = blockIdx.x;
+    const T* wr = W + n * K;
+    const int nvec = (int)(K >> 2);
+    float w[4][4]; int nv = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int v = threadIdx.x + 256 * j;
+        if (v < nvec) { load_vec4<T>(wr + 4 * v, w[j]); nv = j + 1; }
+        else { w[j][0] = w[j][1] = w[j][2] = w[j][3] = 0.0f; }
+    }
+    float ps; int pc;
+    masked_partial<T>(w, nv, 0.0f, false, false, ps, pc);
+    double s = (double)ps; long long c = pc;
+    block_sum2(s, c, shd, shl);
+    float m = to_f32(from_f32<T>((float)(s / (double)K)));       // mean keeps the dtype
+    for (int it = 0; it < iters; ++it) {
+        masked_partial<T>(w, nv, m, true, it == 0, ps, pc);
+        s = (double)ps; c = pc;
+        block_sum2(s, c, shd, shl);
+        m = __fdiv_rn((float)s, (float)c);                         // 0/0 -> NaN like the reference
+    }
+    const float inv = __fdiv_rn(1.0f, m);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int v = threadIdx.x + 256 * j;
+        if (v < nvec) {
+            float4 o; float* oe = reinterpret_cast<float*>(&o);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { const float x = __fmul_rn(w[j][e], inv); oe[e] = x != x ? x : fminf(fmaxf(x, -1.0f), 1.0f); }
+            *reinterpret_cast<float4*>(latent + n * K + 4 * v) = o;
+        }
+    }
+    if (threadIdx.x == 0) scale[n] = m;
+}
+
+// uniform variant, one pass: row partial (phase 0: sum|w|, phase 1: masked sum / count with m = *ws.m) and, in the LAST CTA
+// to finish (ticket counter behind ws.m), the ordered finalise over all rows -- one launch per pass instead of two
+template <typename T>
+__global__ void __launch_bounds__(256)
+ternary_pass_fast_kernel(const T* __restrict__ W, int64_t K, void* wsp, int64_t N, int phase, int first) {
+    __shared__ double shd[8];
+    __shared__ long long shl[8];
+    __shared__ unsigned last;
+    InitWs ws = carve(wsp, N);
+    unsigned* ticket = reinterpret_cast<unsigned*>(ws.m + 1);
+    const int64_t n = blockIdx.x;
+    const T* wr = W + n * K;
+    const int nvec = (int)(K >> 2);
+    float w[4][4]; int nv = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int v = threadIdx.x + 256 * j;
+        if (v < nvec) { load_vec4<T>(wr + 4 * v, w[j]); nv = j + 1; }
+        else { w[j][0] = w[j][1] = w[j][2] = w[j][3] = 0.0f; }
+    }
+    const float m = phase ? *ws.m : 0.0f;
+    float ps; int pc;
+    masked_partial<T>(w, nv, m, phase != 0, first != 0, ps, pc);
+    double s = (double)ps; long long c = pc;
+    block_sum2(s, c, shd, shl);
+    if (threadIdx.x == 0) {
+        ws.sum[n] = s; ws.cnt[n] = c;
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == (unsigned)(N - 1);
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    s = 0.0; c = 0;
+    for (int64_t i = threadIdx.x; i < N; i += blockDim.x) { s += __ldcg(ws.sum + i); c += __ldcg(ws.cnt + i); }
+    block_sum2(s, c, shd, shl);
+    if (threadIdx.x == 0) {
+        if (!phase) *ws.m = to_f32(from_f32<T>((float)(s / (double)c)));
+        else        *ws.m = __fdiv_rn((float)s, (float)c);
+        *ticket = 0u;
+    }
+}
+
 // tensor-wide ("uniform") variant: row partials + a single-CTA ordered finalise per iteration.
 // phase 0: sum|w| ; phase 1: masked sum/count with m = *ws.m
 template <typename T>
@@ -136,6 +265,26 @@ ternary_latent_uniform_kernel(const T* __restrict__ W, int64_t N, int64_t K, con
         latent[i] = v != v ? v : fminf(fmaxf(v, -1.0f), 1.0f);
         if (i < N) scale[i] = m;
     }
+}
+
+// 4 elements per thread and step (aligned, numel % 4 == 0): 16 / 8 byte loads, 16-byte stores
+template <typename T>
+__global__ void __launch_bounds__(256)
+ternary_latent_uniform_vec_kernel(const T* __restrict__ W, int64_t N, int64_t K, const void* wsp,
+                                  float* __restrict__ latent, float* __restrict__ scale) {
+    InitWs ws = carve(const_cast<void*>(wsp), N);
+    const float m = *ws.m;
+    const float inv = __fdiv_rn(1.0f, m);
+    const int64_t nvec = (N * K) >> 2, stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec; i += stride) {
+        float v[4]; load_vec4<T>(W + 4 * i, v);
+        float4 o; float* oe = reinterpret_cast<float*>(&o);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { const float x = __fmul_rn(v[e], inv); oe[e] = x != x ? x : fminf(fmaxf(x, -1.0f), 1.0f); }
+        *reinterpret_cast<float4*>(latent + 4 * i) = o;
+        if (i < N) scale[i] = m;
+    }
+    for (int64_t i = nvec + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < N; i += stride) scale[i] = m;
 }
 
 // binary / binary01 (modules.py:193-266): row partial sums of positive and negative parts
@@ -201,7 +350,7 @@ using namespace tb200;
 
 extern "C" size_t tb200_ternary_init_workspace(int64_t N) {
     if (N < 0) N = 0;
-    return (size_t)N * (2 * sizeof(double) + sizeof(long long)) + 64;
+    return (size_t)N * (2 * sizeof(double) + sizeof(long long)) + 64;   // + m (float) and the last-CTA ticket behind it
 }
 
 extern "C" int tb200_ternary_init(const void* W, int dtype, int64_t N, int64_t K, int per_row, int iters,
@@ -212,15 +361,37 @@ extern "C" int tb200_ternary_init(const void* W, int dtype, int64_t N, int64_t K
     TB_REQUIRE(iters >= 0, "ternary_init: iters < 0");
     TB_REQUIRE(dtype_ok(dtype), "ternary_init: bad dtype %d", dtype);
     cudaStream_t s = (cudaStream_t)stream;
+    const size_t es = dtype_size(dtype);
+    // register-resident fast paths: rows of <= 4096 elements, whole 4-element vectors, 16 / 8 byte aligned rows
+    const bool fast = K <= 4096 && K % 4 == 0 && (uintptr_t)W % (4 * es) == 0 && (uintptr_t)latent % 16 == 0;
     if (per_row) {
-        TB_DISPATCH_DTYPE(dtype, T,
-            (ternary_init_row_kernel<T><<<(unsigned)N, 256, 0, s>>>((const T*)W, K, iters, latent, scale)));
+        TB_DISPATCH_DTYPE(dtype, T, {
+            if (fast) ternary_init_row_fast_kernel<T><<<(unsigned)N, 256, 0, s>>>((const T*)W, K, iters, latent, scale);
+            else ternary_init_row_kernel<T><<<(unsigned)N, 256, 0, s>>>((const T*)W, K, iters, latent, scale);
+        });
         TB_LAUNCH_CHECK();
         return TB200_OK;
     }
     TB_REQUIRE(workspace, "ternary_init: uniform mode needs a workspace");
     int64_t tot = N * K;
     int g = (int)((tot + 255) / 256 < (int64_t)sm_count() * 8 ? (tot + 255) / 256 : (int64_t)sm_count() * 8);
+    if (fast) {
+        InitWs ws = carve(workspace, N);
+        TB_CUDA(cudaMemsetAsync(ws.m + 1, 0, sizeof(unsigned), s));          // the last-CTA ticket
+        TB_DISPATCH_DTYPE(dtype, T, {
+            ternary_pass_fast_kernel<T><<<(unsigned)N, 256, 0, s>>>((const T*)W, K, workspace, N, 0, 0);
+            TB_LAUNCH_CHECK();
+            for (int it = 0; it < iters; ++it) {
+                ternary_pass_fast_kernel<T><<<(unsigned)N, 256, 0, s>>>((const T*)W, K, workspace, N, 1, it == 0);
+                TB_LAUNCH_CHECK();
+            }
+            const int64_t nvec = tot >> 2;
+            const int gv = (int)((nvec + 255) / 256 < (int64_t)sm_count() * 8 ? (nvec + 255) / 256 : (int64_t)sm_count() * 8);
+            ternary_latent_uniform_vec_kernel<T><<<gv, 256, 0, s>>>((const T*)W, N, K, workspace, latent, scale);
+            TB_LAUNCH_CHECK();
+        });
+        return TB200_OK;
+    }
     TB_DISPATCH_DTYPE(dtype, T, {
         ternary_partial_kernel<T><<<(unsigned)N, 256, 0, s>>>((const T*)W, K, workspace, N, 0, 0);
         TB_LAUNCH_CHECK();

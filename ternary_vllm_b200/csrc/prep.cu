@@ -59,6 +59,42 @@ quantize_pack_kernel(const T* __restrict__ w, int64_t K, int64_t ldw,
     }
 }
 
+// Fast path (rows of whole 16-byte units, aligned): a thread turns 16 input bytes (4 fp32 weights -> 1 packed byte,
+// 8 bf16 / f16 weights -> 2 packed bytes) per step and works on FOUR steps at once: the four 16-byte loads of a thread are
+// issued before the first use (the single-load loop above leaves the memory system with one request per thread in flight:
+// 61 % of the measured HBM rate for fp32 rows, 39 % for 16-bit rows).  Consecutive lanes read consecutive 16-byte units.
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256)
+quantize_pack_vec_kernel(const T* __restrict__ w, int64_t K, int64_t ldw, uint8_t* __restrict__ packed, int64_t ld_packed) {
+    constexpr int EPU = 16 / (int)sizeof(T);           // elements per unit: 4 or 8
+    constexpr int BPU = EPU / 4;                        // packed bytes per unit: 1 or 2
+    const int64_t n = blockIdx.x;
+    const uint4* wr = reinterpret_cast<const uint4*>(w + n * ldw);
+    uint8_t* pr = packed + n * ld_packed;
+    const int units = (int)(K / EPU);
+    for (int u0 = threadIdx.x; u0 < units; u0 += 4 * 256) {
+        uint4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int u = u0 + 256 * j;
+            v[j] = u < units ? __ldg(wr + u) : make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int u = u0 + 256 * j;
+            if (u >= units) continue;
+            const T* e = reinterpret_cast<const T*>(&v[j]);
+            uint32_t word = 0;
+#pragma unroll
+            for (int i = 0; i < EPU; ++i) word |= quant_code<MODE>(to_f32(e[i])) << (2 * i);
+            if (BPU == 1) pr[u] = (uint8_t)word;
+            else *reinterpret_cast<uint16_t*>(pr + 2 * u) = (uint16_t)word;
+        }
+    }
+    // row padding up to the pitch: code 1 (value 0)
+    for (int64_t b = (K >> 2) + threadIdx.x; b < ld_packed; b += 256) pr[b] = 0x55u;
+}
+
 // unpack format C -> int8 values (code - 1); thread per packed byte
 __global__ void __launch_bounds__(256)
 unpack_kernel(const uint8_t* __restrict__ packed, int64_t ld_packed, int64_t N, int64_t K,
@@ -159,6 +195,32 @@ clip_kernel(T* __restrict__ w, int64_t numel) {
     }
 }
 
+// 16 bytes per thread and step, four steps in flight (aligned buffers; the tail goes through clip_kernel)
+template <typename T>
+__global__ void __launch_bounds__(256)
+clip_vec_kernel(T* __restrict__ w, int64_t nvec) {
+    constexpr int EPV = 16 / (int)sizeof(T);
+    uint4* p = reinterpret_cast<uint4*>(w);
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < nvec; i0 += 4 * stride) {
+        uint4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { const int64_t i = i0 + j * stride; if (i < nvec) v[j] = p[i]; }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int64_t i = i0 + j * stride;
+            if (i >= nvec) continue;
+            T* e = reinterpret_cast<T*>(&v[j]);
+#pragma unroll
+            for (int k = 0; k < EPV; ++k) {
+                const float x = to_f32(e[k]);
+                e[k] = from_f32<T>(x != x ? x : fminf(fmaxf(x, -1.0f), 1.0f));   // torch.clip propagates NaN
+            }
+            p[i] = v[j];
+        }
+    }
+}
+
 static inline int grid_for(int64_t total, int threads) {
     int64_t g = (total + threads - 1) / threads;
     int64_t cap = (int64_t)sm_count() * 8;
@@ -188,8 +250,12 @@ extern "C" int tb200_quantize_pack(const void* w, int dtype, int64_t N, int64_t 
     // 4-element vector loads (16 B fp32 / 8 B bf16,fp16) need base and row pitch aligned to them
     const bool vec_ok = ((uintptr_t)w % (4 * es) == 0) && ((ldw * es) % (4 * es) == 0);
     dim3 grid((unsigned)N), block(256);
+    // whole 16-byte units per row, 16-byte aligned rows, 2-byte aligned packed rows, no code dump: the vector kernel
+    const bool fast = !codes_out && K > 0 && (K * es) % 16 == 0 && (uintptr_t)w % 16 == 0 && (ldw * es) % 16 == 0 &&
+                      (uintptr_t)packed % 2 == 0 && ld_packed % 2 == 0;
 #define LAUNCH_QP(T, MODE) \
-    quantize_pack_kernel<T, MODE><<<grid, block, 0, s>>>((const T*)w, K, ldw, packed, ld_packed, codes_out, vec_ok)
+    do { if (fast) quantize_pack_vec_kernel<T, MODE><<<grid, block, 0, s>>>((const T*)w, K, ldw, packed, ld_packed); \
+         else quantize_pack_kernel<T, MODE><<<grid, block, 0, s>>>((const T*)w, K, ldw, packed, ld_packed, codes_out, vec_ok); } while (0)
     TB_DISPATCH_DTYPE(dtype, T,
         if (mode == TB200_Q_TERNARY) LAUNCH_QP(T, TB200_Q_TERNARY);
         else if (mode == TB200_Q_SIGN) LAUNCH_QP(T, TB200_Q_SIGN);
@@ -241,8 +307,14 @@ extern "C" int tb200_clip_latent(void* w, int dtype, int64_t numel, void* stream
     TB_REQUIRE(w || numel == 0, "clip_latent: null pointer");
     TB_REQUIRE(dtype_ok(dtype), "clip_latent: bad dtype %d", dtype);
     if (numel <= 0) return TB200_OK;
-    TB_DISPATCH_DTYPE(dtype, T,
-        (clip_kernel<T><<<grid_for(numel, 256), 256, 0, (cudaStream_t)stream>>>((T*)w, numel)));
+    const size_t es = dtype_size(dtype);
+    const int64_t epv = 16 / (int64_t)es;
+    const int64_t nvec = ((uintptr_t)w % 16 == 0) ? numel / epv : 0;
+    TB_DISPATCH_DTYPE(dtype, T, {
+        if (nvec > 0) clip_vec_kernel<T><<<grid_for((nvec + 3) / 4, 256), 256, 0, (cudaStream_t)stream>>>((T*)w, nvec);
+        if (numel - nvec * epv > 0)
+            clip_kernel<T><<<grid_for(numel - nvec * epv, 256), 256, 0, (cudaStream_t)stream>>>((T*)w + nvec * epv, numel - nvec * epv);
+    });
     TB_LAUNCH_CHECK();
     return TB200_OK;
 }
