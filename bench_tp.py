@@ -175,6 +175,81 @@ def run_tp(args, metric):
                           "us_per_layer_nccl_all_gather_eager": t_nccl * 1e6})
         del layers
 
+    # ---- strong scaling: the FIXED N=1 rings (64 / 67 layers), every layer N-sharded: total work does not grow with the ranks.
+    # A rank's shards of a ring fall below its L2 at 4 / 8 ranks, so L2 is flushed (256 MB memset) before every timed call.
+    flush = torch.empty(int(256e6), dtype=torch.uint8, device=dev)
+    strong = []
+    for c in cases:
+        K, N, M = c
+        R0 = ring_len[(K, N)] // world
+        st0 = streams[(K, N)]
+        sub = TPShardedStream(st0.packed[:R0], st0.scale[:R0], st0.bias[:R0], K, N, 100.0, max_tokens=32)
+        x0 = xs[c][:R0]
+        for _ in range(2):
+            sub(x0, alias_ok=True)
+        ts = []
+        for _ in range(5):
+            flush.zero_()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            sub(x0, alias_ok=True)
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ts.append(float(t.item()))
+        t = sorted(ts)[len(ts) // 2] * 1e-3
+        b = algorithmic_bytes(K, N, M) * R0
+        strong.append({"K": K, "N": N, "M": M, "layers": R0, "us_per_call": t * 1e6, "gbs": b / t / 1e9, "tokens_per_s": M * R0 / t,
+                       "l2_policy": "L2 flushed (256 MB memset) before every timed call; eager launch + barrier"})
+        del sub
+
+    # ---- prefill (configs[4]: M = 4096 tokens, N-sharded): quantiser + tcgen05 GEMM per shard, then the gather --
+    # (a) fused: the GEMM epilogue's TMA tile stores write the shard into every rank's buffer over NVLink + one barrier;
+    # (b) baseline: local GEMM, then NCCL all_gather_into_tensor + the re-layout of the rank-major result to [M, N]
+    prefill = []
+    Mp = 4096
+    xp = {}
+    for (K, N) in CHAIN_SHAPES:
+        st0 = streams[(K, N)]
+        x = xp.setdefault(K, torch.randn(Mp, K, device=dev, dtype=torch.bfloat16))
+        dist.broadcast(x, 0)
+        lay_f = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0).enable_peer_gather(Mp)
+        lay_n = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0)
+
+        def t_of(fn, reps=5):
+            fn()
+            ts = []
+            for _ in range(reps):
+                flush.zero_()
+                dist.barrier()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                fn()
+                e1.record()
+                torch.cuda.synchronize()
+                tt = torch.tensor([e0.elapsed_time(e1)], device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                ts.append(float(tt.item()))
+            return sorted(ts)[len(ts) // 2] * 1e-3
+        with torch.no_grad():
+            t_fused = t_of(lambda: lay_f(x, alias_ok=True))
+            t_local = t_of(lambda: lay_n.local_forward(x))
+            yl = lay_n.local_forward(x)
+            t_gather = t_of(lambda: lay_n.gather(yl))
+            t_nccl = t_of(lambda: lay_n(x))
+        ops_ = 2.0 * Mp * N * K
+        prefill.append({"K": K, "N": N, "M": Mp, "us_fused_peer_gather": t_fused * 1e6, "tops_fused": ops_ / t_fused / 1e12,
+                        "us_local_gemm_only": t_local * 1e6, "us_nccl_all_gather_plus_relayout": t_gather * 1e6,
+                        "us_local_gemm_then_nccl": t_nccl * 1e6, "tops_nccl": ops_ / t_nccl / 1e12,
+                        "tokens_per_s_fused": Mp / t_fused,
+                        "gather_bytes_received_per_rank": Mp * N * 2 * (world - 1) // world})
+        del lay_f, lay_n
+        torch.cuda.empty_cache()
+
     # end to end: pinned host activations in, full gathered outputs back to pinned host memory, per case
     hx = {c: torch.randn(ring_len[c[:2]], c[2], c[0], dtype=torch.bfloat16).pin_memory() for c in cases}
     hy = {c: torch.empty(ring_len[c[:2]], c[2], c[1], dtype=torch.bfloat16).pin_memory() for c in cases} if rank == 0 else {}
@@ -212,7 +287,7 @@ def run_tp(args, metric):
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
                     "api": "TPShardedStream.forward per sweep case on pinned host activations (every rank copies x in; "
                            "rank 0 copies the full gathered output back to pinned host memory)"},
-            "cases": per_case, "tp_cases": tp_cases, "chain": chain,
+            "cases": per_case, "tp_cases": tp_cases, "chain": chain, "strong_scaling": strong, "prefill_tp": prefill,
             "roofline": {"bound": "hbm", "achieved": value, "peak": pk["hbm_gbs"] * world, "unit": "GB/s",
                          "frac": value / (pk["hbm_gbs"] * world), "traffic": None, "peak_source": pk["source"],
                          "note": "aggregate over ranks (peak = ranks x measured copy rate); per-rank kernel as in the N=1 line"},

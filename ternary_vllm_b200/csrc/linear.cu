@@ -1,7 +1,7 @@
 // linear.cu — whole-layer entry points: shape dispatch (GEMV vs tcgen05 GEMM) and the
 // host-buffer end-to-end call.  Mirrors ScaledTernaryLinear.forward (binary/modules.py:101-109).
 #include <cstdlib>
-#include "common.cuh"
+#include "umma.cuh"
 
 namespace tb200 {
 static inline int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
@@ -80,7 +80,9 @@ extern "C" int tb200_linear_forward_host(const void* x_host, int x_dtype, int64_
 // Tensor-parallel decode layer with the all-gather fused into the GEMV epilogue: this rank's [M, N_local]
 // output block is stored straight into every rank's [M, ldo] buffer through peer-mapped (NVLink) pointers.
 // out_peers[r] = address, in rank r's buffer, of element (0, first column of THIS rank's block).  The caller
-// issues a cross-rank barrier afterwards (ternary_vllm_b200.parallel).  M <= 32 only.
+// issues a cross-rank barrier afterwards (ternary_vllm_b200.parallel).  More than 32 tokens (prefill): activation
+// quantiser + the tcgen05 GEMM, whose epilogue hands every 32-token x 128-channel output tile to ONE TMA tile store per
+// rank (the all-gather of the [M, N_local] shards costs no extra pass over the output and no NCCL call).
 extern "C" int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
                                        const uint8_t* packed, int64_t ld_packed, int64_t N_local,
                                        const float* scale, const float* bias, float clip_val,
@@ -89,7 +91,6 @@ extern "C" int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, in
     TB_DEVICE_OR_RETURN();
     if (M == 0 || N_local == 0) return TB200_OK;
     TB_REQUIRE(x && packed && out_peers && n_peers >= 1 && n_peers <= 8, "linear_forward_tp: bad peer list");
-    TB_REQUIRE(M <= TB200_GEMV_MAX_M, "linear_forward_tp: M=%lld > %d tokens is not fused (gather with NCCL instead)", (long long)M, TB200_GEMV_MAX_M);
     TB_REQUIRE(K > 0 && ldx >= K && ldo >= N_local, "linear_forward_tp: bad shape");
     const int64_t kc = (K + 63) / 64;
     TB_REQUIRE(ld_packed % 16 == 0 && ld_packed >= kc * 16 && (uintptr_t)packed % 16 == 0, "linear_forward_tp: bad packed layout");
@@ -101,6 +102,18 @@ extern "C" int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, in
     LinearWs ws = carve_ws(workspace, M, K);
     int rc = tb200_quant_act_i8(x, x_dtype, M, K, ldx, ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, TB200_QLAYOUT_GEMM, stream);
     if (rc) return rc;
+    if (M > TB200_GEMV_MAX_M) {
+        TB_REQUIRE(dtype_ok(out_dtype), "linear_forward_tp: bad out dtype");
+        UmmaParams p = {};
+        p.s_x = ws.s_x; p.sum_qx = ws.sum_qx; p.scale = scale; p.bias = bias;
+        p.out = out_peers[0]; p.ldo = ldo; p.acc_out = nullptr;
+        p.M = M; p.N = N_local; p.K = K; p.clip_val = fabsf(clip_val);
+        p.layers = 1; p.stride_act_rows = M; p.stride_sb = 0; p.stride_out = 0;
+        p.n_peers = n_peers;
+        for (int r = 0; r < n_peers; ++r) p.peers[r] = out_peers[r];
+        p.pdl = 1;                                  // launched directly behind the quantiser
+        return gemm_ts_launch(ws.q_x, ws.ldq, packed, ld_packed, p, out_dtype, (cudaStream_t)stream);
+    }
     return gemv_q_impl(ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, M, K, packed, ld_packed, N_local, scale, bias, clip_val,
                        out_peers[0], out_dtype, ldo, nullptr, TB200_FLAG_PDL, stream, out_peers, n_peers);
 }

@@ -98,9 +98,9 @@ class TPShardedLinear(nn.Module):
     # -- fused gather over NVLink peer memory (decode shapes) -------------------------------------------
     def enable_peer_gather(self, max_tokens: int = 32, dtype=torch.bfloat16):
         """Allocate two symmetric (peer-mapped) output buffers [max_tokens, world*n_shard] and exchange their
-        addresses.  Afterwards ``forward`` for <= 32 tokens runs ``tb200_linear_forward_tp``: the GEMV epilogue
-        stores this rank's column block into every rank's buffer, then ONE cross-rank barrier replaces the
-        NCCL all-gather.  Buffers alternate per call, so a peer may start the next call while this rank's
+        addresses.  Afterwards ``forward`` for <= ``max_tokens`` tokens runs ``tb200_linear_forward_tp``: the GEMV
+        epilogue (<= 32 tokens) or the tcgen05 GEMM's epilogue (prefill: TMA tile stores) writes this rank's column block
+        into every rank's buffer, then ONE cross-rank barrier replaces the NCCL all-gather.  Buffers alternate per call, so a peer may start the next call while this rank's
         consumers still read the previous result."""
         import torch.distributed._symmetric_memory as symm_mem
 
@@ -148,7 +148,7 @@ class TPShardedLinear(nn.Module):
     def uses_peer_gather(self, x2: torch.Tensor) -> bool:
         """Path choice of ``forward``: depends only on rank-uniform facts (never on this rank's shard size), so all
         ranks issue the same collective."""
-        return bool(getattr(self, "_peer_bufs", None)) and x2.shape[0] <= min(self._peer_tokens, L.GEMV_MAX_M) \
+        return bool(getattr(self, "_peer_bufs", None)) and x2.shape[0] <= self._peer_tokens \
             and x2.is_cuda and x2.dtype == self._peer_dtype
 
     def forward(self, x: torch.Tensor, alias_ok: bool = False) -> torch.Tensor:

@@ -153,3 +153,38 @@ def test_vit_l14_shapes(cuda, K, N):
     assert torch.equal(acc_v, acc[-32:])
     y = ops.ternary_matmul(x.to(cuda).reshape(32, 257, K), packed, None, None, 1e9)
     assert y.shape == (32, 257, N) and torch.isfinite(y).all()
+
+
+@pytest.mark.parametrize("M,N,K,world", [(300, 1000, 1024, 2), (513, 704, 4096, 3), (40, 256, 512, 4)])
+def test_prefill_tp_peer_stores_single_device(cuda, M, N, K, world):
+    """tb200_linear_forward_tp for MORE than 32 tokens on ONE device: every 'rank' runs quantiser + tcgen05 GEMM on its row
+    block and its epilogue stores the tile into `world` local stand-ins for the peer buffers (TMA tile stores, ragged last
+    shard, column offsets); every buffer must equal the unsharded tb200_linear_forward output bit for bit."""
+    import ctypes
+
+    from ternary_vllm_b200 import _lib as L
+    from ternary_vllm_b200.parallel import shard_rows, shard_size
+
+    g = torch.Generator().manual_seed(M + N + K)
+    W = torch.randn(N, K, generator=g).clip(-1, 1).to(cuda)
+    x = torch.randn(M, K, generator=g).bfloat16().to(cuda)
+    scale = (torch.rand(N, generator=g) / K ** 0.5).to(cuda)
+    bias = torch.randn(N, generator=g).to(cuda)
+    packed = ops.quantize_pack(W, "ternary")
+    want = ops.ternary_matmul(x, packed, scale, bias, 100.0)
+    n_shard = shard_size(N, world)
+    ld = world * n_shard
+    bufs = [torch.full((M, ld), float("nan"), dtype=torch.bfloat16, device=cuda) for _ in range(world)]
+    ws = torch.empty(L.lib().tb200_linear_workspace(M, K), dtype=torch.uint8, device=cuda)
+    for rank in range(world):
+        a, b = shard_rows(N, world, rank)
+        if b <= a:
+            continue
+        ptrs = (ctypes.c_void_p * world)(*[buf.data_ptr() + rank * n_shard * 2 for buf in bufs])
+        pk, sc, bi = packed[a:b].contiguous(), scale[a:b].contiguous(), bias[a:b].contiguous()
+        L.check(L.lib().tb200_linear_forward_tp(x.data_ptr(), L.TB200_BF16, M, K, K, pk.data_ptr(), pk.stride(0), b - a,
+                                                sc.data_ptr(), bi.data_ptr(), 100.0, ptrs, world, L.TB200_BF16, ld,
+                                                ws.data_ptr(), torch.cuda.current_stream().cuda_stream), "linear_forward_tp")
+    torch.cuda.synchronize()
+    for buf in bufs:
+        assert torch.equal(buf[:, :N], want)

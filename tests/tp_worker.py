@@ -34,6 +34,7 @@ for (K, N) in ((4096, 11008), (11008, 4096), (1024, 1000), (256, 16 * (world - 1
     layer.scale.data.fill_(1.0 / K ** 0.5)
     tp = TPShardedLinear.from_layer(layer)
     tp_peer = TPShardedLinear.from_layer(layer).enable_peer_gather(32)
+    tp_pre = TPShardedLinear.from_layer(layer).enable_peer_gather(320)     # prefill through the tcgen05 GEMM's TMA peer stores
     for M in (1, 8, 32, 300):
         x = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
         dist.broadcast(x, 0)
@@ -42,10 +43,12 @@ for (K, N) in ((4096, 11008), (11008, 4096), (1024, 1000), (256, 16 * (world - 1
             y1 = tp(x)
             y2 = tp_peer(x)                                # M <= 32: fused gather (fresh tensor); M = 300: NCCL
             y3 = tp_peer(x, alias_ok=True).clone()         # second buffer, aliased form
+            y4 = tp_pre(x)                                 # every M through the fused gather (M = 300: GEMM epilogue)
         torch.cuda.synchronize()
-        good = torch.equal(want, y1) and torch.equal(want, y2) and torch.equal(want, y3)
+        good = torch.equal(want, y1) and torch.equal(want, y2) and torch.equal(want, y3) and torch.equal(want, y4)
         ok = ok and good
-        say(f"K={K} N={N} M={M}: nccl {torch.equal(want, y1)} peer {torch.equal(want, y2)} peer2 {torch.equal(want, y3)}")
+        say(f"K={K} N={N} M={M}: nccl {torch.equal(want, y1)} peer {torch.equal(want, y2)} peer2 {torch.equal(want, y3)} "
+            f"peer-any-M {torch.equal(want, y4)}")
 
 # list form: ONE tb200_gemv_stream_tp call + one barrier for R layers vs the unsharded tb200_gemv_stream
 for (K, N, R) in ((4096, 11008, 5), (1024, 1000, 3), (11008, 4096, 2)):
