@@ -89,6 +89,21 @@ int tb200_unpack_format(const uint8_t* packed, int64_t N, int64_t K, int fmt,
 /* Replaces clip_binary_weights (binary/utils.py:74-77): in-place clip(w, -1, 1). */
 int tb200_clip_latent(void* w, int dtype, int64_t numel, void* stream);
 
+/* ---- optimiser-side helpers of the smooth-binary training loop (binary/modules.py:149-176, train.py:296-297) ----
+ * compute_and_set_biobjective_gradient(model) = for every parameter gradient tb200_sumsq_accumulate(grad, .., 0, norm_g_sq),
+ * for every smooth-binary weight tensor tb200_sumsq_accumulate(weights, .., 1, norm_bg_sq)  (|-sign(w)|^2 = #nonzero),
+ * then tb200_biobjective_apply per gradient.  The accumulators are device doubles the caller zeroes; nothing is read back
+ * to the host.  `workspace`: tb200_train_workspace() bytes, 8-byte aligned, ZERO before the first call. */
+size_t tb200_train_workspace(void);
+int tb200_sumsq_accumulate(const void* x, int dtype, int64_t numel, int count_nonzero, double* acc,
+                           void* workspace, void* stream);
+/* In place on `grad` [numel].  weights != NULL: the layer is smooth-binary and `grad` is its weights.grad:
+ *   grad <- (((grad / n_g + -sign(w) / n_bg) * (n_g + n_bg)) * 0.5 / n_g) * (n_g + n_bg)      (modules.py:166-176: the
+ *   reference rescales the blended gradient once more in its per-parameter loop);  weights == NULL (any other parameter):
+ *   grad <- (grad / n_g) * (n_g + n_bg).  n_g == 0 leaves the rescale out (`if norm_g > 0.0 else`), n_bg == 0 zeroes its term. */
+int tb200_biobjective_apply(void* grad, const void* weights, int dtype, int64_t numel, const double* norm_g_sq,
+                            const double* norm_bg_sq, void* stream);
+
 /* Replaces the ternary branch of linear_to_quantized (binary/modules.py:275-298):
  * thresholded-mean ("k-means") scale, `iters` refinements, then latent = clip(W/m, +-1).
  * per_row=0: one scale for the tensor ("uniform"), broadcast into scale[N];

@@ -10,6 +10,7 @@ from .modules import (  # noqa: F401
     sign_ste, step_ste, tri_step_ste, sign_ste_sat, step_ste_sat,
     linear_to_quantized, compute_and_set_biobjective_gradient, compute_smooth_binary_stats,
 )
+from .checkpoint import load_safetensors_packed, export_packed  # noqa: F401
 from .blocks import ChainedLinears, TernaryMLP  # noqa: F401
 from .utils import quantize_moondream, clip_binary_weights, quantized_size_bits  # noqa: F401
 

@@ -60,6 +60,9 @@ SIGNATURES = {
     "tb200_pack_format": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp]),
     "tb200_unpack_format": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp]),
     "tb200_clip_latent": (_i32, [_vp, _i32, _i64, _vp]),
+    "tb200_train_workspace": (C.c_size_t, []),
+    "tb200_sumsq_accumulate": (_i32, [_vp, _i32, _i64, _i32, _vp, _vp, _vp]),
+    "tb200_biobjective_apply": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp]),
     "tb200_ternary_init_workspace": (_sz, [_i64]),
     "tb200_ternary_init": (_i32, [_vp, _i32, _i64, _i64, _i32, _i32, _vp, _vp, _vp, _vp]),
     "tb200_binary_init": (_i32, [_vp, _i32, _i64, _i64, _i32, _i32, _f32, _i32, _vp, _vp, _vp, _vp]),

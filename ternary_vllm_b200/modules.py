@@ -300,10 +300,56 @@ QUANT_CLASSES = (ScaledBinaryLinear, ScaledBinary01Linear, ScaledTernaryLinear, 
 
 
 # --------------------------------------------------------------------------- training helpers
+def _biobjective_fused(model: nn.Module) -> bool:
+    """GPU form of compute_and_set_biobjective_gradient: one reduction launch per gradient / smooth-binary weight tensor
+    into two device accumulators, then one in-place launch per gradient (``tb200_sumsq_accumulate`` /
+    ``tb200_biobjective_apply``); no host synchronisation.  Returns False (nothing touched) unless every tensor involved is
+    a contiguous CUDA tensor of a supported dtype on one device with the standard ``-sign(weights)`` binarisation gradient."""
+    grads, smooth = [], []
+    dev = None
+    for mod in model.modules():
+        is_smooth = hasattr(mod, "compute_binarization_gradient")
+        if is_smooth and type(mod).compute_binarization_gradient is not SmoothlyBinarizedLinear.compute_binarization_gradient:
+            return False
+        for name, p in mod.named_parameters(recurse=False):
+            if is_smooth and name == "weights":
+                if p.grad is None:
+                    return False
+                smooth.append(p)
+            if p.grad is not None:
+                grads.append((p, is_smooth and name == "weights"))
+        if is_smooth and not any(n == "weights" for n, _ in mod.named_parameters(recurse=False)):
+            return False
+    if not grads:
+        return False
+    for p, _ in grads:
+        g = p.grad
+        if not (g.is_cuda and g.is_contiguous() and p.is_contiguous() and g.dtype == p.dtype
+                and g.dtype in (torch.float32, torch.bfloat16, torch.float16)):
+            return False
+        if dev is None:
+            dev = g.device
+        if g.device != dev or p.device != dev:
+            return False
+    acc = torch.zeros(2, dtype=torch.float64, device=dev)
+    ng_sq, nbg_sq = acc[0], acc[1]
+    for p, _ in grads:
+        ops.sumsq_accumulate_(ng_sq, p.grad)
+    for p in smooth:
+        ops.sumsq_accumulate_(nbg_sq, torch.Tensor.data.__get__(p) if isinstance(p, TrackedParameter) else p.data, count_nonzero=True)
+    for p, is_w in grads:
+        w = (torch.Tensor.data.__get__(p) if isinstance(p, TrackedParameter) else p.data) if is_w else None
+        ops.biobjective_apply_(p.grad, w, ng_sq, nbg_sq)
+    return True
+
+
 @torch.no_grad()
 def compute_and_set_biobjective_gradient(model: nn.Module):
     """binary/modules.py:149-176: blend the task gradient with the binarisation gradient
-    ``-sign(w)`` at equal global norm.  (Training-side helper; reductions run as torch ops.)"""
+    ``-sign(w)`` at equal global norm.  CUDA gradients take the fused kernels (``_biobjective_fused``); anything else the
+    reference's formulation in torch ops below."""
+    if _biobjective_fused(model):
+        return
     norm_g_sq = 0.0
     norm_bg_sq = 0.0
     bgs = {}

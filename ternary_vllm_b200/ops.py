@@ -116,6 +116,37 @@ def clip_latent_(w: torch.Tensor) -> torch.Tensor:
     return w
 
 
+_train_ws: dict = {}
+
+
+def _train_workspace(device) -> torch.Tensor:
+    ws = _train_ws.get(device.index)
+    if ws is None:
+        ws = _train_ws[device.index] = torch.zeros(L.lib().tb200_train_workspace(), dtype=torch.uint8, device=device)
+    return ws
+
+
+def sumsq_accumulate_(acc: torch.Tensor, x: torch.Tensor, count_nonzero: bool = False) -> torch.Tensor:
+    """``acc (0-dim float64, CUDA) += sum(x**2)`` or ``+= count_nonzero(x)`` (= ``sum(sign(x)**2)``), deterministic
+    (``tb200_sumsq_accumulate``); no host synchronisation."""
+    _cuda(acc, x)
+    assert acc.dtype == torch.float64 and acc.numel() == 1 and x.is_contiguous()
+    with torch.cuda.device(x.device):
+        L.check(L.lib().tb200_sumsq_accumulate(x.data_ptr(), _dt(x), x.numel(), int(count_nonzero), acc.data_ptr(),
+                                               _train_workspace(x.device).data_ptr(), _stream(x)), "sumsq_accumulate")
+    return acc
+
+
+def biobjective_apply_(grad: torch.Tensor, weights, norm_g_sq: torch.Tensor, norm_bg_sq: torch.Tensor) -> torch.Tensor:
+    """In-place blend / rescale of one gradient tensor (``tb200_biobjective_apply``, binary/modules.py:166-176)."""
+    _cuda(grad, weights, norm_g_sq, norm_bg_sq)
+    assert grad.is_contiguous() and (weights is None or (weights.is_contiguous() and weights.dtype == grad.dtype and weights.numel() == grad.numel()))
+    with torch.cuda.device(grad.device):
+        L.check(L.lib().tb200_biobjective_apply(grad.data_ptr(), _ptr(weights), _dt(grad), grad.numel(), norm_g_sq.data_ptr(),
+                                                norm_bg_sq.data_ptr(), _stream(grad)), "biobjective_apply")
+    return grad
+
+
 def ternary_init(weight: torch.Tensor, per_row: bool, iters: int = 10):
     """Ternary branch of linear_to_quantized (binary/modules.py:275-298) -> (latent f32, scale f32)."""
     _cuda(weight)

@@ -296,3 +296,107 @@ def test_second_device_if_present(cuda):
     with pytest.raises(tb.TernaryB200Error):
         a.freeze()
         a(torch.randn(1, 4096, dtype=torch.bfloat16, device="cuda:1"))
+
+
+# ---- checkpoint path: load by parameter name straight into packed form; export of formats A / B / C ----
+def _tiny_model(dev):
+    import ternary_vllm_b200 as tb
+    torch.manual_seed(4)
+    m = torch.nn.Sequential()
+    m.add_module("ln", torch.nn.LayerNorm(96))
+    m.add_module("fc1", tb.ScaledTernaryLinear(96, 200))
+    m.add_module("fc2", tb.ScaledBinaryLinear(200, 64))
+    m.add_module("head", torch.nn.Linear(64, 10))
+    return m.to(dev)
+
+
+def test_load_safetensors_packed_matches_reference_loading(cuda, tmp_path):
+    from safetensors.torch import save_file
+
+    from ternary_vllm_b200.checkpoint import load_safetensors_packed
+    src = _tiny_model("cpu")
+    for p in src.parameters():
+        p.data = torch.randn_like(p) * 0.7
+    path = tmp_path / "model.safetensors"
+    save_file({k: v.detach().clone() for k, v in src.named_parameters()}, str(path))
+    # the reference's way (convert.py:72-79): p.data[:] = v on a model that keeps its latent weights
+    ref = _tiny_model(cuda)
+    from safetensors import safe_open
+    with safe_open(str(path), "pt") as f:
+        for name, p in ref.named_parameters():
+            p.data[:] = f.get_tensor(name)
+    # packed loading: no latent weights stay resident
+    m = _tiny_model(cuda)
+    stats = load_safetensors_packed(m, path)
+    assert stats["packed_layers"] == 2 and stats["copied"] == 2 + 2 + 2 + 2 and not stats["missing"]
+    assert m.fc1.weights.numel() == 0 and m.fc2.weights.numel() == 0 and m.fc1._frozen and m.fc2._frozen
+    assert torch.equal(m.fc1.packed_weights(), ref.fc1.packed_weights()) and torch.equal(m.fc2.packed_weights(), ref.fc2.packed_weights())
+    x = torch.randn(5, 96, device=cuda)
+    with torch.no_grad():
+        assert torch.equal(m(x), ref(x))
+    # the frozen model round-trips through state_dict (packed buffers are persistent once frozen)
+    m2 = _tiny_model(cuda)
+    m2.load_state_dict(m.state_dict())
+    with torch.no_grad():
+        assert torch.equal(m2(x), ref(x))
+    # keep the latent weights instead
+    m3 = _tiny_model(cuda)
+    load_safetensors_packed(m3, path, release_latent=False)
+    assert torch.equal(m3.fc1.weights.detach().cpu(), src.fc1.weights.detach())
+    with torch.no_grad():
+        assert torch.equal(m3(x), ref(x))
+    with pytest.raises(KeyError):
+        save_file({"ln.weight": torch.ones(96)}, str(tmp_path / "partial.safetensors"))
+        load_safetensors_packed(_tiny_model(cuda), tmp_path / "partial.safetensors")
+
+
+@pytest.mark.parametrize("fmt", ["A", "B", "C"])
+def test_export_packed_formats(cuda, fmt):
+    from oracle import ref_packing as rp
+    from ternary_vllm_b200.checkpoint import export_packed
+    m = _tiny_model(cuda)
+    out = export_packed(m, fmt)
+    assert set(out) == {"fc1", "fc2"}
+    for name, layer in (("fc1", m.fc1), ("fc2", m.fc2)):
+        codes = layer.codes().cpu().numpy()
+        want = {"A": lambda c: rp.pack_A(c.reshape(-1)), "B": lambda c: rp.pack_B(c.reshape(-1)), "C": rp.pack_C}[fmt](codes)
+        got = out[name]["packed"].numpy()
+        assert got.dtype == np.uint8 and np.array_equal(got.reshape(-1), np.asarray(want).reshape(-1))
+        assert out[name]["clip_val"] == layer.maxval and out[name]["shape"] == (layer.out_features, layer.in_features)
+
+
+# ---- fused training helpers: compute_and_set_biobjective_gradient on the GPU ----
+def test_biobjective_gradient_fused_golden(cuda, golden):
+    from ternary_vllm_b200 import modules as tbm
+    torch.manual_seed(7)
+    net = nn.Sequential(tb.SmoothlyBinarizedLinear(12, 8), nn.Linear(8, 4)).to(cuda)
+    net[0].weights.data = torch.from_numpy(golden["bio_w0"]).clone().to(cuda)
+    g_in = torch.from_numpy(golden["bio_g_in"]).to(cuda)
+    off = 0
+    for p in net.parameters():
+        p.grad = g_in[off:off + p.numel()].reshape(p.shape).clone()
+        off += p.numel()
+    before = ops.launch_count()
+    assert tbm._biobjective_fused(net)                       # the CUDA kernels, not the torch formulation
+    assert ops.launch_count() - before == 4 + 1 + 4          # 4 gradient norms, 1 sign count, 4 in-place updates
+    got = torch.cat([p.grad.flatten() for p in net.parameters()]).cpu().numpy()
+    assert np.allclose(got, golden["bio_g_out"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("zero_g", [False, True])
+def test_biobjective_gradient_fused_matches_torch_formulation(cuda, zero_g):
+    """Large tensors (vector path + tail, several CTAs), incl. the norm_g == 0 branch, against the oracle restatement."""
+    torch.manual_seed(11)
+    net = nn.Sequential(tb.SmoothlyBinarizedLinear(1000, 777), nn.LayerNorm(777), tb.SmoothlyBinarizedLinear(777, 33, bias=False)).to(cuda)
+    for p in net.parameters():
+        p.grad = torch.zeros_like(p) if zero_g else torch.randn_like(p) * 0.01
+    net[0].weights.data[0, :5] = 0.0                          # sign(0) = 0 entries
+    smooth_w = [net[0].weights.detach().cpu(), net[2].weights.detach().cpu()]
+    smooth_g = [net[0].weights.grad.cpu().clone(), net[2].weights.grad.cpu().clone()]
+    others = [p.grad.cpu().clone() for n, p in net.named_parameters() if not n.endswith("weights")]
+    want_s, want_o = om.biobjective_gradients(smooth_w, smooth_g, others)
+    tb.compute_and_set_biobjective_gradient(net)
+    got_s = [net[0].weights.grad.cpu(), net[2].weights.grad.cpu()]
+    got_o = [p.grad.cpu() for n, p in net.named_parameters() if not n.endswith("weights")]
+    for a, b in zip(got_s + got_o, list(want_s) + list(want_o)):
+        assert torch.allclose(a, b, rtol=2e-5, atol=1e-9), (a - b).abs().max()
