@@ -6,6 +6,7 @@ from torch import nn
 
 import ternary_vllm_b200 as tb
 from oracle import ref_int8, ref_modules as om
+from ternary_vllm_b200 import ops
 
 pytestmark = pytest.mark.gpu
 
