@@ -89,6 +89,24 @@ int tb200_unpack_format(const uint8_t* packed, int64_t N, int64_t K, int fmt,
 /* Replaces clip_binary_weights (binary/utils.py:74-77): in-place clip(w, -1, 1). */
 int tb200_clip_latent(void* w, int dtype, int64_t numel, void* stream);
 
+/* ---- 1-bit packed weights for the two-valued layers (ScaledBinaryLinear, ScaledBinary01Linear, SmoothlyBinarizedLinear:
+ * binary/modules.py:55-90,112-146; one bit per weight as binary/utils.py:42-45 accounts them) ----
+ * Format B1: [N, ld1] uint8, bit (k & 7) of byte k >> 3 of row n = (w[n,k] >= 0) (sign_ste and step_ste decide alike,
+ * -0.0 -> 1); value = 2 bit - 1 (binary01 = 0) or bit (binary01 = 1); ld1 = tb200_b1_pitch(K) = 16 * ceil(K / 128), padding 0. */
+int64_t tb200_b1_pitch(int64_t K);
+int tb200_quantize_pack_b1(const void* w, int dtype, int64_t N, int64_t K, int64_t ldw, uint8_t* packed, int64_t ld1,
+                           void* stream);
+/* B1 -> the 2-bit format C (codes value + 1, pad code 1), row pitch ld2 (even, >= ceil(K/4)): feeds tb200_linear_forward /
+ * tb200_gemm_i8 for more than 8 tokens. */
+int tb200_expand_b1(const uint8_t* packed1, int64_t ld1, int64_t N, int64_t K, int binary01, uint8_t* packed2, int64_t ld2,
+                    void* stream);
+/* Decode GEMV on B1 weights, M <= TB200_GEMV_FUSED_M tokens, on the outputs of tb200_quant_act_i8(..., TB200_QLAYOUT_NATURAL)
+ * (q_x [M, ldq] int8 with ldq % 16 == 0, s_x, sum_qx):  out = clip(((2 - binary01) * sum_k bit q - (1 - binary01) * sum_qx)
+ * * s_x * scale + bias).  flags: TB200_FLAG_PDL when launched directly behind the quantiser. */
+int tb200_gemv_b1(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx, int64_t M, int64_t K,
+                  const uint8_t* packed1, int64_t ld1, int64_t N, const float* scale, const float* bias, float clip_val,
+                  int binary01, void* out, int out_dtype, int64_t ldo, int flags, void* stream);
+
 /* ---- optimiser-side helpers of the smooth-binary training loop (binary/modules.py:149-176, train.py:296-297) ----
  * compute_and_set_biobjective_gradient(model) = for every parameter gradient tb200_sumsq_accumulate(grad, .., 0, norm_g_sq),
  * for every smooth-binary weight tensor tb200_sumsq_accumulate(weights, .., 1, norm_bg_sq)  (|-sign(w)|^2 = #nonzero),

@@ -17,6 +17,7 @@ TB200_F32, TB200_BF16, TB200_F16 = 0, 1, 2
 Q_TERNARY, Q_SIGN, Q_STEP = 0, 1, 2
 FMT_A, FMT_B, FMT_C = 0, 1, 2
 GEMV_MAX_M = 32
+GEMV_FUSED_M = 8          # TB200_GEMV_FUSED_M: tokens per pass of the decode GEMVs
 FLAG_PDL = 1
 ACT_NONE, ACT_GELU_TANH, ACT_RELU = 0, 1, 2
 CHAIN_MAX_M, CHAIN_MAX_LAYERS = 8, 128
@@ -60,6 +61,10 @@ SIGNATURES = {
     "tb200_pack_format": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp]),
     "tb200_unpack_format": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp]),
     "tb200_clip_latent": (_i32, [_vp, _i32, _i64, _vp]),
+    "tb200_b1_pitch": (_i64, [_i64]),
+    "tb200_quantize_pack_b1": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _vp]),
+    "tb200_expand_b1": (_i32, [_vp, _i64, _i64, _i64, _i32, _vp, _i64, _vp]),
+    "tb200_gemv_b1": (_i32, [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, C.c_float, _i32, _vp, _i32, _i64, _i32, _vp]),
     "tb200_train_workspace": (C.c_size_t, []),
     "tb200_sumsq_accumulate": (_i32, [_vp, _i32, _i64, _i32, _vp, _vp, _vp]),
     "tb200_biobjective_apply": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp]),

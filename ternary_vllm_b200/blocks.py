@@ -85,7 +85,7 @@ class ChainedLinears(nn.Module):
         if M < 1 or M > self.chain_max_tokens:
             return False
         for l in self.layers:
-            if not l.act_quant or (l._needs_autograd(x) and not l._frozen) or (l.training and not l._has_scale):
+            if l.pack_bits != 2 or not l.act_quant or (l._needs_autograd(x) and not l._frozen) or (l.training and not l._has_scale):
                 return False
         return True
 

@@ -58,7 +58,8 @@ def load_safetensors_packed(model: nn.Module, path, device=None, release_latent:
                 raise ValueError(f"{name}: checkpoint shape {tuple(v.shape)} != layer shape {(owner.out_features, owner.in_features)}")
             w = v.to(dev, non_blocking=True)
             stats["bytes_latent_peak"] = max(stats["bytes_latent_peak"], w.numel() * w.element_size())
-            owner._packed = ops.quantize_pack(w.contiguous(), owner._mode)       # the only pass over the latent weights
+            # the only pass over the latent weights
+            owner._packed = ops.quantize_pack_b1(w.contiguous()) if owner.pack_bits == 1 else ops.quantize_pack(w.contiguous(), owner._mode)
             owner._packed_key = None
             owner._frozen = True
             owner._non_persistent_buffers_set.discard("_packed")
@@ -67,7 +68,7 @@ def load_safetensors_packed(model: nn.Module, path, device=None, release_latent:
                 owner._released = True
             else:
                 p.data[:] = w.to(p.dtype)
-                owner._packed_key = owner._key()
+                owner._packed_key = owner._key() + (owner.pack_bits,)
             del w, v
             stats["packed_layers"] += 1
             stats["bytes_packed"] += owner._packed.numel()

@@ -128,6 +128,9 @@ class _PackedQuantLinear(nn.Module):
             self.scale = nn.Parameter(torch.full((out_features,), 1.0))
         self.maxval = abs(max_val)
         self.act_quant = True
+        # bits per packed weight: 2 (format C, every kernel) or -- two-valued layers only -- 1 (format B1: half the HBM bytes
+        # of a decode GEMV; binary/utils.py:42-45 accounts these layers at one bit).  Change it with set_pack_bits().
+        self.pack_bits = 2
         # the packed weights are a BUFFER: they follow .to()/.cuda() with the module; not part of the state dict (the
         # reference's checkpoint keys are weights / bias / scale only) until freeze() makes them the deployed form
         self.register_buffer("_packed", None, persistent=False)
@@ -157,15 +160,28 @@ class _PackedQuantLinear(nn.Module):
         if "_packed" in self._buffers:
             self._non_persistent_buffers_set.add("_packed")
 
+    def set_pack_bits(self, bits: int):
+        """1: store the (two-valued) weights at one bit each (format B1, ``tb200_gemv_b1``); 2: the default format C."""
+        if bits not in (1, 2) or (bits == 1 and self._mode == "ternary"):
+            raise ValueError("pack_bits must be 2, or 1 for a binary / binary01 layer")
+        if bits != self.pack_bits:
+            if self._released:
+                raise TernaryB200Error("latent weights were released; the layer cannot be re-packed at another width")
+            self.pack_bits = bits
+            self._packed_key = None
+            self._packed = None
+        return self
+
     def packed_weights(self) -> torch.Tensor:
-        """uint8 ``[out_features, pitch]`` in the reference's format C; rebuilt when stale."""
+        """uint8 ``[out_features, pitch]`` in the reference's format C (or B1 when ``pack_bits == 1``); rebuilt when stale."""
         if self._frozen and self._packed is not None:
             return self._packed
-        key = self._key()
+        key = self._key() + (self.pack_bits,)
         if self._packed is None or self._packed_key != key:
             if self._released:
                 raise TernaryB200Error("latent weights were released; the packed weights are missing")
-            self._packed = ops.quantize_pack(torch.Tensor.data.__get__(self.weights), self._mode)
+            w = torch.Tensor.data.__get__(self.weights)
+            self._packed = ops.quantize_pack_b1(w) if self.pack_bits == 1 else ops.quantize_pack(w, self._mode)
             self._packed_key = key
         return self._packed
 
@@ -188,6 +204,12 @@ class _PackedQuantLinear(nn.Module):
             self._packed = torch.empty_like(pk, device=self.weights.device if self._packed is None else self._packed.device)
             self._frozen = True
             self._non_persistent_buffers_set.discard("_packed")
+            # the checkpoint does not name the packing width: the row pitch tells (formats B1 and C differ for K > 64)
+            p1, p2 = ops.b1_pitch(self.in_features), ops.packed_pitch(self.in_features)
+            if pk.shape[-1] == p1 and p1 != p2 and self._mode != "ternary":
+                self.pack_bits = 1
+            elif pk.shape[-1] == p2 and p1 != p2:
+                self.pack_bits = 2
             w = state_dict.get(prefix + "weights")
             if w is not None and w.numel() == 0:
                 self.weights = nn.Parameter(torch.empty(0, device=self._packed.device), requires_grad=False)
@@ -196,7 +218,10 @@ class _PackedQuantLinear(nn.Module):
 
     def codes(self) -> torch.Tensor:
         """int8 ``[out_features, in_features]`` quantised weights (ops.unpack_ternary)."""
-        return ops.unpack(self.packed_weights(), self.in_features)
+        pw = self.packed_weights()
+        if self.pack_bits == 1:
+            pw = ops.expand_b1(pw, self.in_features, self._mode == "binary01")
+        return ops.unpack(pw, self.in_features)
 
     # -- forward ---------------------------------------------------------------------------
     def _needs_autograd(self, x) -> bool:
@@ -223,6 +248,11 @@ class _PackedQuantLinear(nn.Module):
         if pw.device != x.device:
             raise TernaryB200Error(f"packed weights live on {pw.device} but the input is on {x.device}; move the "
                                    "layer with .to() (the packed buffer follows the module)")
+        if self.pack_bits == 1:
+            if not self.act_quant:
+                pw = ops.expand_b1(pw, self.in_features, self._mode == "binary01")
+            else:
+                return ops.binary_matmul(x, pw, self.in_features, scale, self.bias, self.maxval, self._mode == "binary01")
         if not self.act_quant:
             x2 = x.reshape(-1, x.shape[-1])
             if x2.shape[0] > ops.L.GEMV_MAX_M:

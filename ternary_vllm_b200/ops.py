@@ -414,6 +414,66 @@ def launch_count() -> int:
     return int(L.lib().tb200_launch_count())
 
 
+# ------------------------------------------------------------------ 1-bit packed weights (binary / binary01 layers)
+def b1_pitch(K: int) -> int:
+    return int(L.lib().tb200_b1_pitch(K))
+
+
+def quantize_pack_b1(w: torch.Tensor) -> torch.Tensor:
+    """Latent weights ``[N, K]`` -> format B1 ``[N, 16 * ceil(K/128)]`` uint8: bit ``k & 7`` of byte ``k >> 3`` is
+    ``w[n, k] >= 0`` (sign_ste / step_ste, binary/modules.py:5-18)."""
+    _cuda(w)
+    assert w.dim() == 2
+    w = w.detach()
+    if w.stride(1) != 1:
+        w = w.contiguous()
+    N, K = w.shape
+    out = torch.empty((N, b1_pitch(K)), dtype=torch.uint8, device=w.device)
+    with torch.cuda.device(w.device):
+        L.check(L.lib().tb200_quantize_pack_b1(w.data_ptr(), _dt(w), N, K, w.stride(0), out.data_ptr(), out.stride(0), _stream(w)),
+                "quantize_pack_b1")
+    return out
+
+
+def expand_b1(packed1: torch.Tensor, K: int, binary01: bool) -> torch.Tensor:
+    """B1 -> the 2-bit format C ``[N, packed_pitch(K)]`` (codes value + 1) the 2-bit kernels read."""
+    _cuda(packed1)
+    N = packed1.shape[0]
+    out = torch.empty((N, packed_pitch(K)), dtype=torch.uint8, device=packed1.device)
+    with torch.cuda.device(packed1.device):
+        L.check(L.lib().tb200_expand_b1(packed1.data_ptr(), packed1.stride(0), N, K, int(binary01), out.data_ptr(), out.stride(0),
+                                        _stream(packed1)), "expand_b1")
+    return out
+
+
+def binary_matmul(x: torch.Tensor, pw1: torch.Tensor, K: int, scale, bias, clip_val: float, binary01: bool, out_dtype=None,
+                  debug=False):
+    """The layer forward on 1-bit weights: ``clip((x @ W^T) * scale + bias)`` with ``W = 2 bit - 1`` (binary) or ``bit``
+    (binary01).  Up to 8 tokens: activation quantiser + ``tb200_gemv_b1`` (half the weight bytes of the 2-bit GEMV); more:
+    the weights are expanded to format C on the fly and go through ``tb200_linear_forward`` (tcgen05 GEMM)."""
+    _cuda(x, pw1, scale, bias)
+    assert x.shape[-1] == K and pw1.dtype == torch.uint8 and pw1.dim() == 2 and pw1.stride(1) == 1
+    N = pw1.shape[0]
+    x2 = x.reshape(-1, K)
+    if x2.stride(-1) != 1:
+        x2 = x2.contiguous()
+    M = x2.shape[0]
+    out_dtype = out_dtype or x.dtype
+    scale = _f32_or_none(scale, N, x.device)
+    bias = _f32_or_none(bias, N, x.device)
+    if M > L.GEMV_FUSED_M:
+        y = ternary_matmul(x2, expand_b1(pw1, K, binary01), scale, bias, clip_val, out_dtype=out_dtype)
+        return y.reshape(*x.shape[:-1], N)
+    out = torch.empty((M, N), dtype=out_dtype, device=x.device)
+    if M > 0:
+        q, s, sq = quant_act_i8(x2, layout=0)
+        with torch.cuda.device(x.device):
+            L.check(L.lib().tb200_gemv_b1(q.data_ptr(), q.stride(0), s.data_ptr(), sq.data_ptr(), M, K, pw1.data_ptr(), pw1.stride(0), N,
+                                          _ptr(scale), _ptr(bias), float(clip_val), int(binary01), out.data_ptr(), _DT[out_dtype],
+                                          out.stride(0), L.FLAG_PDL, _stream(x)), "gemv_b1")
+    return out.reshape(*x.shape[:-1], N)
+
+
 # ------------------------------------------------------------------ torch.library registration (SURVEY.md §8b)
 # The C-ABI calls above are invisible to torch.compile / export; the ops below wrap them as opaque custom ops with
 # shape-only ("fake") implementations, so a compiled model keeps the layer as ONE node instead of graph-breaking.
