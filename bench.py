@@ -392,7 +392,7 @@ def run_b200(args):
         "frac_hbm_measured": value / pk["hbm_gbs"], "clocks": clocks,
         "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
         "cases": per_case, "roofline": roofline, "mlp_chain": None if args.no_extra else run_mlp(dev, pk),
-        "prep": None if args.no_extra else run_prep(dev, pk), "gemm": gemm, "vit_l14": None if args.no_gemm else run_vit(dev),
+        "prep": None if args.no_extra else run_prep(dev, pk), "binary_1bit": None if args.no_extra else run_binary_1bit(dev, pk), "gemm": gemm, "vit_l14": None if args.no_gemm else run_vit(dev),
         "cpu_baseline": cb,
     }
     print(json.dumps(line))
@@ -629,6 +629,64 @@ def run_mlp(dev, pk):
                              "api": "ternary_vllm_b200.TernaryMLP / ChainedLinears (tb200_chain_forward)"})
             del blocks, whole
             torch.cuda.empty_cache()
+    return rows
+
+
+def run_binary_1bit(dev, pk):
+    """a ring of binary (+-1) 4096 x 11008 layers (packed bytes > 2 x L2 in both formats) as a chain of
+    per-layer calls, the 2-bit format C (tb200_gemv, PDL) next to the 1-bit format B1 (tb200_gemv_b1_fused, PDL):
+    the same integer sums from half the weight bytes."""
+    import torch
+    from ternary_vllm_b200 import ops, _lib as L
+    K, N, R = 4096, 11008, 96
+    g = torch.Generator(device=dev).manual_seed(5)
+    p2, p1 = [], []
+    for _ in range(R):
+        W = torch.randn(N, K, generator=g, device=dev)
+        p2.append(ops.quantize_pack(W, "binary"))
+        p1.append(ops.quantize_pack_b1(W))
+    del W
+    scale = torch.full((N,), 1.0 / math.sqrt(K), device=dev)
+    bias = torch.randn(N, generator=g, device=dev)
+    st = torch.cuda.Stream(dev)
+    rows = []
+    with torch.cuda.stream(st), torch.no_grad():
+        for M in (1, 2):
+            x = torch.randn(M, K, generator=g, device=dev, dtype=torch.bfloat16)
+            out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+
+            def two_bit():
+                for r in range(R):
+                    ops.gemv(x, p2[r], scale, bias, 100.0, pdl=True, out=out)
+
+            def one_bit():
+                for r in range(R):
+                    L.check(L.lib().tb200_gemv_b1_fused(x.data_ptr(), L.TB200_BF16, M, K, K, p1[r].data_ptr(), p1[r].stride(0), N,
+                                                        scale.data_ptr(), bias.data_ptr(), 100.0, 0, out.data_ptr(), L.TB200_BF16, N,
+                                                        L.FLAG_PDL, st.cuda_stream), "gemv_b1_fused")
+            res = {}
+            for name, fn, wbytes in (("two_bit_format_c", two_bit, N * K / 4), ("one_bit_format_b1", one_bit, N * K / 8)):
+                fn()
+                st.synchronize()
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr, stream=st):
+                    fn()
+                for _ in range(3):
+                    gr.replay()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                st.synchronize()
+                e0.record(st)
+                for _ in range(10):
+                    gr.replay()
+                e1.record(st)
+                st.synchronize()
+                t = e0.elapsed_time(e1) * 1e-3 / 10 / R
+                b = wbytes + M * K * 2 + M * N * 2 + N * 8
+                res[name] = {"us_per_layer": t * 1e6, "tokens_per_s": M / t, "algorithmic_bytes_per_layer": b, "gbs": b / t / 1e9,
+                             "frac_hbm_measured": b / t / 1e9 / pk["hbm_gbs"]}
+            res.update({"K": K, "N": N, "M": M, "layers": R, "api": "chain of per-layer calls under one CUDA graph, PDL between launches",
+                        "speedup_one_bit": res["two_bit_format_c"]["us_per_layer"] / res["one_bit_format_b1"]["us_per_layer"]})
+            rows.append(res)
     return rows
 
 

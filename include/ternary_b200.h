@@ -103,6 +103,11 @@ int tb200_expand_b1(const uint8_t* packed1, int64_t ld1, int64_t N, int64_t K, i
 /* Decode GEMV on B1 weights, M <= TB200_GEMV_FUSED_M tokens, on the outputs of tb200_quant_act_i8(..., TB200_QLAYOUT_NATURAL)
  * (q_x [M, ldq] int8 with ldq % 16 == 0, s_x, sum_qx):  out = clip(((2 - binary01) * sum_k bit q - (1 - binary01) * sum_qx)
  * * s_x * scale + bias).  flags: TB200_FLAG_PDL when launched directly behind the quantiser. */
+/* The same for M <= 2 tokens straight from x [M, ldx] (bf16 / f16 / f32): the activation quantisation runs in the kernel's
+ * prologue, ONE launch per layer (the form ScaledBinaryLinear.forward takes at pack_bits == 1). */
+int tb200_gemv_b1_fused(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, const uint8_t* packed1, int64_t ld1,
+                        int64_t N, const float* scale, const float* bias, float clip_val, int binary01, void* out,
+                        int out_dtype, int64_t ldo, int flags, void* stream);
 int tb200_gemv_b1(const int8_t* q_x, int64_t ldq, const float* s_x, const int32_t* sum_qx, int64_t M, int64_t K,
                   const uint8_t* packed1, int64_t ld1, int64_t N, const float* scale, const float* bias, float clip_val,
                   int binary01, void* out, int out_dtype, int64_t ldo, int flags, void* stream);

@@ -64,6 +64,7 @@ SIGNATURES = {
     "tb200_b1_pitch": (_i64, [_i64]),
     "tb200_quantize_pack_b1": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _vp]),
     "tb200_expand_b1": (_i32, [_vp, _i64, _i64, _i64, _i32, _vp, _i64, _vp]),
+    "tb200_gemv_b1_fused": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, C.c_float, _i32, _vp, _i32, _i64, _i32, _vp]),
     "tb200_gemv_b1": (_i32, [_vp, _i64, _vp, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _vp, C.c_float, _i32, _vp, _i32, _i64, _i32, _vp]),
     "tb200_train_workspace": (C.c_size_t, []),
     "tb200_sumsq_accumulate": (_i32, [_vp, _i32, _i64, _i32, _vp, _vp, _vp]),

@@ -446,11 +446,15 @@ def expand_b1(packed1: torch.Tensor, K: int, binary01: bool) -> torch.Tensor:
     return out
 
 
+B1_GEMV_MAX_M = 2
+
+
 def binary_matmul(x: torch.Tensor, pw1: torch.Tensor, K: int, scale, bias, clip_val: float, binary01: bool, out_dtype=None,
-                  debug=False):
+                  force_b1: bool = False, pdl: bool = False):
     """The layer forward on 1-bit weights: ``clip((x @ W^T) * scale + bias)`` with ``W = 2 bit - 1`` (binary) or ``bit``
-    (binary01).  Up to 8 tokens: activation quantiser + ``tb200_gemv_b1`` (half the weight bytes of the 2-bit GEMV); more:
-    the weights are expanded to format C on the fly and go through ``tb200_linear_forward`` (tcgen05 GEMM)."""
+    (binary01).  Up to 2 tokens: ONE launch of ``tb200_gemv_b1_fused`` (half the weight bytes of the 2-bit GEMV); more: the
+    weights are expanded to format C on the fly and go through ``tb200_linear_forward``.  ``force_b1`` (tests): quantiser +
+    ``tb200_gemv_b1`` for up to 8 tokens."""
     _cuda(x, pw1, scale, bias)
     assert x.shape[-1] == K and pw1.dtype == torch.uint8 and pw1.dim() == 2 and pw1.stride(1) == 1
     N = pw1.shape[0]
@@ -461,11 +465,18 @@ def binary_matmul(x: torch.Tensor, pw1: torch.Tensor, K: int, scale, bias, clip_
     out_dtype = out_dtype or x.dtype
     scale = _f32_or_none(scale, N, x.device)
     bias = _f32_or_none(bias, N, x.device)
-    if M > L.GEMV_FUSED_M:
+    if M > B1_GEMV_MAX_M and not force_b1:
+        # dp4a computes one token per instruction (mma.sync eight): above two tokens the 2-bit kernels win even after the
+        # expansion pass
         y = ternary_matmul(x2, expand_b1(pw1, K, binary01), scale, bias, clip_val, out_dtype=out_dtype)
         return y.reshape(*x.shape[:-1], N)
     out = torch.empty((M, N), dtype=out_dtype, device=x.device)
-    if M > 0:
+    if 0 < M <= 2 and not force_b1:
+        with torch.cuda.device(x.device):
+            L.check(L.lib().tb200_gemv_b1_fused(x2.data_ptr(), _dt(x2), M, K, x2.stride(0), pw1.data_ptr(), pw1.stride(0), N,
+                                                _ptr(scale), _ptr(bias), float(clip_val), int(binary01), out.data_ptr(),
+                                                _DT[out_dtype], out.stride(0), L.FLAG_PDL if pdl else 0, _stream(x)), "gemv_b1_fused")
+    elif M > 0:
         q, s, sq = quant_act_i8(x2, layout=0)
         with torch.cuda.device(x.device):
             L.check(L.lib().tb200_gemv_b1(q.data_ptr(), q.stride(0), s.data_ptr(), sq.data_ptr(), M, K, pw1.data_ptr(), pw1.stride(0), N,

@@ -52,7 +52,11 @@ def test_gemv_b1_matches_oracle(cuda, M, N, K, mode):
     scale = torch.rand(N, generator=g) / K ** 0.5
     bias = torch.randn(N, generator=g) * 0.3
     p1 = ops.quantize_pack_b1(W.to(cuda))
-    out = ops.binary_matmul(x.to(cuda), p1, K, scale.to(cuda), bias.to(cuda), 100.0, mode == "binary01", out_dtype=torch.float32)
+    out = ops.binary_matmul(x.to(cuda), p1, K, scale.to(cuda), bias.to(cuda), 100.0, mode == "binary01", out_dtype=torch.float32,
+                            force_b1=True)                     # quantiser + tb200_gemv_b1 at every M <= 8
+    if M <= 2:                                                # the one-launch form the layers use
+        fused = ops.binary_matmul(x.to(cuda), p1, K, scale.to(cuda), bias.to(cuda), 100.0, mode == "binary01", out_dtype=torch.float32)
+        assert torch.equal(fused, out)
     codes = ref_int8.codes_of(W.numpy(), mode)
     qo, so, _ = ref_int8.quant_act(x.float().numpy())
     acc_o = ref_int8.int_acc(qo, codes)                   # exact integers
