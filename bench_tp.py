@@ -224,6 +224,7 @@ def run_tp(args, metric):
         dist.broadcast(x, 0)
         lay_f = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0).enable_peer_gather(Mp)
         lay_n = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0)
+        lay_u = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0).enable_peer_gather(Mp, multicast=False)
 
         def t_of(fn, reps=5):
             fn()
@@ -249,6 +250,11 @@ def run_tp(args, metric):
             except Exception as e:
                 t_fused = t_of(lambda: lay_f(x, alias_ok=True))
                 fused_mode = f"eager ({type(e).__name__})"
+            try:
+                gr_u, _ = graphed(lambda: lay_u(x, alias_ok=True))
+                t_unicast = t_of(gr_u.replay)
+            except Exception:
+                t_unicast = t_of(lambda: lay_u(x, alias_ok=True))
             n_loc = lay_n.stop - lay_n.start
             y_loc = torch.empty(Mp, max(n_loc, 1), device=dev, dtype=torch.bfloat16)
             gr_l, _ = graphed(lambda: ops.ternary_matmul(x, lay_n.packed, lay_n.scale, lay_n.bias, 100.0, out=y_loc[:, :n_loc]) if n_loc else None)
@@ -258,11 +264,12 @@ def run_tp(args, metric):
             t_nccl = t_of(lambda: lay_n(x))
         ops_ = 2.0 * Mp * N * K
         prefill.append({"K": K, "N": N, "M": Mp, "us_fused_peer_gather": t_fused * 1e6, "tops_fused": ops_ / t_fused / 1e12,
-                        "fused_launch_mode": fused_mode, "us_local_gemm_only": t_local * 1e6, "us_nccl_all_gather_plus_relayout": t_gather * 1e6,
+                        "fused_launch_mode": fused_mode, "fused_multicast": bool(lay_f._peer_use_mc),
+                        "us_fused_unicast_tma_stores": t_unicast * 1e6, "us_local_gemm_only": t_local * 1e6, "us_nccl_all_gather_plus_relayout": t_gather * 1e6,
                         "us_local_gemm_then_nccl": t_nccl * 1e6, "tops_nccl": ops_ / t_nccl / 1e12,
                         "tokens_per_s_fused": Mp / t_fused,
                         "gather_bytes_received_per_rank": Mp * N * 2 * (world - 1) // world})
-        del lay_f, lay_n
+        del lay_f, lay_n, lay_u
         torch.cuda.empty_cache()
 
     # end to end: pinned host activations in, full gathered outputs back to pinned host memory, per case
@@ -294,7 +301,7 @@ def run_tp(args, metric):
             "config": dict(CONFIG_TP, parallelism=f"tp{world} (N-sharded, all-gather fused into the GEMV epilogues)"),
             "tokens_per_s": step_tokens * args.steps / (ms * 1e-3), "clocks": clocks,
             "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step, "launch_mode": mode,
-            "ms_per_step_without_barriers": ms_nobarrier,
+            "ms_per_step_without_barriers": ms_nobarrier, "multicast_stores": bool(streams[SHAPES[0]].multicast),
             "barrier_share": max(0.0, 1.0 - ms_nobarrier / (ms / args.steps)),
             "gather": "fused into the epilogues of tb200_gemv_stream_tp: stores to every rank's buffer over NVLink peer "
                       "memory + ONE symmetric-memory barrier per call (a call = one sweep case over its ring of layers)",

@@ -236,6 +236,22 @@ int tb200_gemv_stream_tp(const void* x, int x_dtype, int64_t M, int64_t K, int64
                          const float* scale, const float* bias, int64_t stride_sb, float clip_val,
                          void* const* out_peers, int n_peers, int out_dtype, int64_t ldo, int64_t stride_out,
                          int count, void* workspace, void* stream);
+/* The same through an NVSwitch MULTICAST mapping of the output buffers (e.g. torch symmetric memory, handle.multicast_ptr):
+ * `out_multicast` = multicast address of element (layer 0, token 0, first column of THIS rank's block).  Every 16 bytes of output
+ * leave the GPU once (multimem.st) and the switch writes them into every rank's buffer: egress 1x instead of n_ranks x.
+ * N_local must be a multiple of 8 (fp32 outputs: 4).  The caller issues the cross-rank barrier afterwards. */
+int tb200_gemv_stream_mc(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                         const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N_local,
+                         const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                         void* out_multicast, int out_dtype, int64_t ldo, int64_t stride_out,
+                         int count, void* workspace, void* stream);
+/* Prefill (M > 32) tensor-parallel layer through a multicast mapping: quantiser + tcgen05 GEMM whose epilogue multicasts every
+ * output tile (see tb200_linear_forward_tp for the unicast form and the argument meaning). */
+int tb200_linear_forward_mc(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+                            const uint8_t* packed, int64_t ld_packed, int64_t N_local,
+                            const float* scale, const float* bias, float clip_val,
+                            void* out_multicast, int out_dtype, int64_t ldo, void* workspace, void* stream);
+
 
 /* tb200_gemv_stream with HOST activations x_host [count, M, K] and outputs out_host [count, M, N] (dense, pinned):
  * one H2D copy, the two launches, one D2H copy, in order on `stream`.  dev_x / dev_out: device staging buffers of the

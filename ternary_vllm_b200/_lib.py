@@ -84,6 +84,9 @@ SIGNATURES = {
     "tb200_gemv_stream_workspace": (_sz, [_i64, _i64, _i32]),
     "tb200_gemv_stream": (_i32, [_vp, _i32, _i64, _i64, _i64, _i64, _vp, _i64, _i64, _i64,
                                  _vp, _vp, _i64, _f32, _vp, _i32, _i64, _i64, _i32, _vp, _vp, _vp]),
+    "tb200_gemv_stream_mc": (_i32, [_vp, _i32, _i64, _i64, _i64, _i64, _vp, _i64, _i64, _i64,
+                                    _vp, _vp, _i64, _f32, _vp, _i32, _i64, _i64, _i32, _vp, _vp]),
+    "tb200_linear_forward_mc": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32, _vp, _i32, _i64, _vp, _vp]),
     "tb200_gemv_stream_tp": (_i32, [_vp, _i32, _i64, _i64, _i64, _i64, _vp, _i64, _i64, _i64,
                                     _vp, _vp, _i64, _f32, _vp, _i32, _i32, _i64, _i64, _i32, _vp, _vp]),
     "tb200_gemv_stream_host": (_i32, [_vp, _i32, _i64, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _i64, _f32,

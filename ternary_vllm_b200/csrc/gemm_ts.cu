@@ -301,6 +301,27 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         for (int j = 0; j < CH; ++j)
                             if (n < p.N && m0 + c0 + j < p.M) p.acc_out[(m0 + c0 + j) * p.N + n] = (int)r[j] - sqv[j];
                     }
+                    if (p.mc) {
+                        // multicast gather: the staged [32 tokens][128 channels] tile leaves as 16-byte multimem stores, four per
+                        // thread (the switch writes them into every rank's buffer)
+                        asm volatile("bar.sync 1, 128;" ::: "memory");
+                        constexpr int PPR = TS_ROWS * (int)sizeof(OT) / 16;          // 16-byte pieces per token row of the tile
+                        constexpr int CPP = 16 / (int)sizeof(OT);                    // channels per piece
+                        OT* mcb = reinterpret_cast<OT*>(p.peers[0]) + layer * p.stride_out;
+#pragma unroll
+                        for (int i = 0; i < 32 * PPR / 128; ++i) {
+                            const int pc = et + 128 * i, j = pc / PPR, cp = pc - j * PPR;
+                            const int64_t tok = m0 + c0 + j, ch = (int64_t)n_tile * TS_ROWS + cp * CPP;
+                            if (tok < p.M && ch < p.N) {
+                                uint4 v;
+                                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                                             : "r"(stg + (uint32_t)(pc * 16)) : "memory");
+                                multimem_st_128(mcb + tok * p.ldo + ch, v);
+                            }
+                        }
+                        ++chunk_no;
+                        continue;
+                    }
                     fence_proxy_async();
                     asm volatile("bar.sync 1, 128;" ::: "memory");
                     if (et == 0) {

@@ -47,6 +47,7 @@ struct StreamParams {
     // shared memory and stored with ONE TMA tile store per rank into that rank's [layers, M, ldo] buffer (peer-mapped
     // NVLink addresses; tensor maps in PeerMaps, already offset to this rank's column block; TMA clips rows >= N, tokens >= M)
     int n_peers; uint32_t peer_stage_off;     // staging tiles of the aux warps, byte offset in dynamic shared memory
+    void* mc_out;                             // non-null: NVSwitch multicast address of this rank's column block -> multimem stores instead of per-rank TMA stores
     int64_t N;
     int M, Mg, nks, row_blocks, layers;
     int stages, nslots, nimg;
@@ -564,12 +565,30 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
                             asm volatile("st.shared.u16 [%0], %1;" ::"r"(stg + el * 2u), "h"(h) : "memory");
                         }
                     }
+                if (p.mc_out) {
+                    // multicast gather: the [tokens][16 rows] tile leaves as 16-byte multimem stores (one per 8 / 4 channels of a
+                    // token), replicated by the switch into every rank's buffer
+                    __syncwarp();
+                    const int ppr = (int)(SV_ROWS * esz / 16);                   // pieces per token row: 2 (16-bit) or 4 (fp32)
+                    for (int pc = lane; pc < p.M * ppr; pc += 32) {
+                        const int tok = pc / ppr, cpi = pc - tok * ppr;
+                        const int64_t row = (int64_t)cp.rb * SV_ROWS + cpi * (16 / (int)esz);
+                        if (row < p.N) {
+                            uint4 v;
+                            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                                         : "r"(stg + (uint32_t)(pc * 16)) : "memory");
+                            multimem_st_128(reinterpret_cast<uint8_t*>(p.mc_out) + (obase + (int64_t)tok * p.ldo + row) * esz, v);
+                        }
+                    }
+                    __syncwarp();
+                } else {
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) {
 #pragma unroll 1
                     for (int r = 0; r < p.n_peers; ++r) tma_store_3d(&pm.m[r], stg, cp.rb * SV_ROWS, 0, l);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
                 }
                 ++pcnt;
             }
@@ -774,6 +793,8 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     const StreamGeom gm = stream_geom(M, K);
     const bool breg = gm.ng == 1 && gm.nks == 1;
     StreamParams p = {};
+    const bool mc = peers && n_peers < 0;          // peers[0] is an NVSwitch multicast address
+    if (mc) n_peers = 1;
     const bool tp = peers && n_peers > 0;
     const size_t peer_esz = tp ? dtype_size(out_dtype) : 0;
     if (!stream_pick(gm, breg, &p.stages, &p.nslots, &p.nimg, peer_esz)) {
@@ -831,6 +852,10 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
         for (int r = n_peers; r < 8; ++r) peer_maps.m[r] = peer_maps.m[0];
         pm = &peer_maps;
         p.n_peers = n_peers;
+        if (mc) {
+            if (N % (16 / (int64_t)os)) { set_error("gemv_stream_mc: N_local must be a multiple of %d", (int)(16 / os)); return TB200_EINVAL; }
+            p.mc_out = peers[0];
+        }
         p.peer_stage_off = (uint32_t)stream_stage_off(gm, p.stages, p.nslots, p.nimg);
     }
     p.N = N; p.M = (int)M; p.Mg = gm.Mg; p.nks = gm.nks;
@@ -906,8 +931,11 @@ static int stream_umma(const void* x, int x_dtype, int64_t M, int64_t K, int64_t
     p.out = out; p.ldo = ldo; p.acc_out = acc_out;
     p.M = M; p.N = N; p.K = K; p.clip_val = fabsf(clip_val);
     p.layers = layers; p.stride_act_rows = M; p.stride_sb = stride_sb; p.stride_out = stride_out;
+    p.mc = (peers && n_peers < 0) ? 1 : 0;
+    if (p.mc) n_peers = 1;
     p.n_peers = peers ? n_peers : 0;
     for (int r = 0; r < p.n_peers; ++r) p.peers[r] = peers[r];
+    if (p.mc && N % (16 / (int64_t)dtype_size(out_dtype))) { set_error("gemv_stream_mc: N_local must be a multiple of 8 (16-bit) / 4 (fp32)"); return TB200_EINVAL; }
     p.dbg = (int)tb_knob("TB200_GEMM_DBG", 0);
     // the GEMM's prologue and launch latency overlap the quantiser (single quantiser launch directly before it)
     static const int pdl_env = (int)tb_knob("TB200_STREAM_UMMA_PDL", 1);
@@ -965,6 +993,20 @@ extern "C" int tb200_gemv_stream_tp(const void* x, int x_dtype, int64_t M, int64
         if (!out_peers[r]) { set_error("gemv_stream_tp: null peer pointer %d", r); return TB200_EINVAL; }
     return gemv_stream_entry(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N_local, scale, bias, stride_sb,
                              clip_val, out_peers[0], out_dtype, ldo, stride_out, count, nullptr, workspace, stream, out_peers, n_peers);
+}
+
+// The same through an NVSwitch MULTICAST mapping (torch symmetric memory: handle.multicast_ptr): `out_multicast` is the multicast
+// address of element (layer 0, token 0, first column of THIS rank's block); every 16 bytes of output leave the GPU ONCE and the
+// switch writes them into every rank's buffer (egress 1x instead of n_ranks x).  N_local must be a multiple of 8 (fp32: 4).
+extern "C" int tb200_gemv_stream_mc(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx, int64_t stride_x,
+                                    const uint8_t* packed, int64_t ld_packed, int64_t stride_packed, int64_t N_local,
+                                    const float* scale, const float* bias, int64_t stride_sb, float clip_val,
+                                    void* out_multicast, int out_dtype, int64_t ldo, int64_t stride_out,
+                                    int count, void* workspace, void* stream) {
+    if (!out_multicast) { set_error("gemv_stream_mc: null multicast pointer"); return TB200_EINVAL; }
+    void* peers[1] = {out_multicast};
+    return gemv_stream_entry(x, x_dtype, M, K, ldx, stride_x, packed, ld_packed, stride_packed, N_local, scale, bias, stride_sb,
+                             clip_val, out_multicast, out_dtype, ldo, stride_out, count, nullptr, workspace, stream, peers, -1);
 }
 
 // End-to-end with HOST activations / outputs for a list of layers (weights resident on the device): one H2D copy of

@@ -90,7 +90,8 @@ extern "C" int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, in
                                        void* workspace, void* stream) {
     TB_DEVICE_OR_RETURN();
     if (M == 0 || N_local == 0) return TB200_OK;
-    TB_REQUIRE(x && packed && out_peers && n_peers >= 1 && n_peers <= 8, "linear_forward_tp: bad peer list");
+    TB_REQUIRE(x && packed && out_peers && ((n_peers >= 1 && n_peers <= 8) || n_peers == -1), "linear_forward_tp: bad peer list");
+    TB_REQUIRE(n_peers != -1 || M > TB200_GEMV_MAX_M, "linear_forward_mc: the multicast form serves prefill (M > 32); use tb200_gemv_stream_mc for decode lists");
     TB_REQUIRE(K > 0 && ldx >= K && ldo >= N_local, "linear_forward_tp: bad shape");
     const int64_t kc = (K + 63) / 64;
     TB_REQUIRE(ld_packed % 16 == 0 && ld_packed >= kc * 16 && (uintptr_t)packed % 16 == 0, "linear_forward_tp: bad packed layout");
@@ -102,9 +103,13 @@ extern "C" int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, in
     LinearWs ws = carve_ws(workspace, M, K);
     int rc = tb200_quant_act_i8(x, x_dtype, M, K, ldx, ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, TB200_QLAYOUT_GEMM, stream);
     if (rc) return rc;
+    const bool mc = n_peers < 0;                   // tb200_linear_forward_mc: out_peers[0] is a multicast address
+    if (mc) n_peers = 1;
     if (M > TB200_GEMV_MAX_M) {
         TB_REQUIRE(dtype_ok(out_dtype), "linear_forward_tp: bad out dtype");
+        TB_REQUIRE(!mc || N_local % (16 / (int64_t)dtype_size(out_dtype)) == 0, "linear_forward_mc: N_local must be a multiple of 8 (16-bit) / 4 (fp32)");
         UmmaParams p = {};
+        p.mc = mc ? 1 : 0;
         p.s_x = ws.s_x; p.sum_qx = ws.sum_qx; p.scale = scale; p.bias = bias;
         p.out = out_peers[0]; p.ldo = ldo; p.acc_out = nullptr;
         p.M = M; p.N = N_local; p.K = K; p.clip_val = fabsf(clip_val);
@@ -116,4 +121,15 @@ extern "C" int tb200_linear_forward_tp(const void* x, int x_dtype, int64_t M, in
     }
     return gemv_q_impl(ws.q_x, ws.ldq, ws.s_x, ws.sum_qx, M, K, packed, ld_packed, N_local, scale, bias, clip_val,
                        out_peers[0], out_dtype, ldo, nullptr, TB200_FLAG_PDL, stream, out_peers, n_peers);
+}
+
+// Prefill tensor parallelism through an NVSwitch multicast mapping: as tb200_linear_forward_tp for M > 32, but every output tile
+// leaves the GPU once (multimem stores from the tcgen05 GEMM's epilogue) and the switch replicates it into every rank's buffer.
+extern "C" int tb200_linear_forward_mc(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+                                       const uint8_t* packed, int64_t ld_packed, int64_t N_local,
+                                       const float* scale, const float* bias, float clip_val,
+                                       void* out_multicast, int out_dtype, int64_t ldo, void* workspace, void* stream) {
+    void* peers[1] = {out_multicast};
+    return tb200_linear_forward_tp(x, x_dtype, M, K, ldx, packed, ld_packed, N_local, scale, bias, clip_val, peers, -1, out_dtype, ldo,
+                                   workspace, stream);
 }

@@ -410,6 +410,28 @@ def gemv_stream_tp(xs, packed, scale, bias, clip_val, peer_ptrs, n_peers: int, o
                                              workspace.data_ptr(), _stream(xs)), "gemv_stream_tp")
 
 
+def gemv_stream_mc(xs, packed, scale, bias, clip_val, out_multicast: int, out_dtype, ldo: int, stride_out: int, workspace=None):
+    """``gemv_stream_tp`` through an NVSwitch multicast mapping (``tb200_gemv_stream_mc``): ``out_multicast`` is the multicast
+    address of this rank's first column in the symmetric ``[R, M, ldo]`` buffers."""
+    _cuda(xs, packed, scale, bias)
+    assert packed.dim() == 3 and packed.dtype == torch.uint8 and packed.stride(2) == 1
+    R, N, _ = packed.shape
+    shared_x = xs.dim() == 2
+    assert xs.stride(-1) == 1
+    M, K = xs.shape[-2], xs.shape[-1]
+    stride_sb = scale.stride(0) if scale is not None else (bias.stride(0) if bias is not None else 0)
+    need = L.lib().tb200_gemv_stream_workspace(M, K, R)
+    if workspace is None:
+        workspace = torch.empty((need,), dtype=torch.uint8, device=xs.device)
+    assert workspace.numel() >= need
+    with torch.cuda.device(xs.device):
+        L.check(L.lib().tb200_gemv_stream_mc(xs.data_ptr(), _dt(xs), M, K, xs.stride(-2), 0 if shared_x else xs.stride(0),
+                                             packed.data_ptr(), packed.stride(1), packed.stride(0), N,
+                                             _ptr(scale), _ptr(bias), stride_sb, float(clip_val),
+                                             int(out_multicast), _DT[out_dtype], ldo, stride_out, R,
+                                             workspace.data_ptr(), _stream(xs)), "gemv_stream_mc")
+
+
 def launch_count() -> int:
     return int(L.lib().tb200_launch_count())
 

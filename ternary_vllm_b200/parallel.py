@@ -17,6 +17,7 @@ import ctypes
 
 from . import _lib as L
 from . import ops
+from ._lib import TernaryB200Error
 
 ROW_ALIGN = 16      # the decode GEMV works on 16-row tiles, the tcgen05 GEMM on 128-row tiles
 
@@ -96,7 +97,7 @@ class TPShardedLinear(nn.Module):
         return buf.view(self.world, M, self.n_shard).permute(1, 0, 2).reshape(M, self.world * self.n_shard)[:, : self.out_features]
 
     # -- fused gather over NVLink peer memory (decode shapes) -------------------------------------------
-    def enable_peer_gather(self, max_tokens: int = 32, dtype=torch.bfloat16):
+    def enable_peer_gather(self, max_tokens: int = 32, dtype=torch.bfloat16, multicast: bool = True):
         """Allocate two symmetric (peer-mapped) output buffers [max_tokens, world*n_shard] and exchange their
         addresses.  Afterwards ``forward`` for <= ``max_tokens`` tokens runs ``tb200_linear_forward_tp``: the GEMV
         epilogue (<= 32 tokens) or the tcgen05 GEMM's epilogue (prefill: TMA tile stores) writes this rank's column block
@@ -120,6 +121,8 @@ class TPShardedLinear(nn.Module):
             self._peer_bufs.append(buf)
             self._peer_hdls.append(hdl)
             self._peer_ptrs.append(ptrs)
+        self._peer_mc = [_multicast_base(h, self.rank * self.n_shard * esz) for h in self._peer_hdls]
+        self._peer_use_mc = bool(multicast and self.world > 1 and all(self._peer_mc) and (self.stop - self.start) % (16 // esz) == 0)
         self._peer_turn = 0
         return self
 
@@ -134,7 +137,15 @@ class TPShardedLinear(nn.Module):
         self._peer_turn ^= 1
         buf, hdl, ptrs = self._peer_bufs[i], self._peer_hdls[i], self._peer_ptrs[i]
         n_local = self.stop - self.start
-        if n_local > 0:
+        if n_local > 0 and self._peer_use_mc and M > L.GEMV_MAX_M:
+            # prefill: every output tile leaves this GPU once, the NVSwitch replicates it into all ranks' buffers
+            ws = ops._workspace(M, K, x2.device)
+            with torch.cuda.device(x2.device):
+                L.check(L.lib().tb200_linear_forward_mc(
+                    x2.data_ptr(), ops._dt(x2), M, K, x2.stride(0), self.packed.data_ptr(), self.packed.stride(0), n_local,
+                    ops._ptr(self.scale), ops._ptr(self.bias), float(self.maxval), self._peer_mc[i],
+                    ops._DT[self._peer_dtype], self._peer_ld, ws.data_ptr(), ops._stream(x2)), "linear_forward_mc")
+        elif n_local > 0:
             ws = ops._workspace(M, K, x2.device)
             with torch.cuda.device(x2.device):
                 L.check(L.lib().tb200_linear_forward_tp(
@@ -162,6 +173,15 @@ class TPShardedLinear(nn.Module):
         return y.reshape(*x.shape[:-1], self.out_features)
 
 
+def _multicast_base(hdl, offset_bytes: int) -> int:
+    """Multicast address of `offset_bytes` into the symmetric buffer, or 0 when the handle has no multicast mapping."""
+    try:
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+    except Exception:
+        mc = 0
+    return mc + offset_bytes if mc else 0
+
+
 class TPShardedStream(nn.Module):
     """A LIST of R independent layers of one shape (fused QKV / gate+up projections, experts, the layers of a batch
     of models), N-sharded: this rank holds rows [start, stop) of every layer.  ``forward(xs)`` runs ONE
@@ -170,7 +190,7 @@ class TPShardedStream(nn.Module):
     list, and returns the full ``[R, M, N]`` outputs on every rank.  Decode shapes only (M <= 32)."""
 
     def __init__(self, packed_shards: torch.Tensor, scale_shards, bias_shards, in_features: int, out_features: int,
-                 maxval: float, group=None, max_tokens: int = 32, dtype=torch.bfloat16):
+                 maxval: float, group=None, max_tokens: int = 32, dtype=torch.bfloat16, multicast="auto"):
         super().__init__()
         import torch.distributed._symmetric_memory as symm_mem
 
@@ -197,6 +217,13 @@ class TPShardedStream(nn.Module):
             self._hdls.append(hdl)
             self._ptrs.append((ctypes.c_void_p * self.world)(*[int(hdl.buffer_ptrs[r]) + self.rank * self.n_shard * esz
                                                                for r in _rotated(self.rank, self.world)]))
+        # NVSwitch multicast mapping of the same buffers: one store reaches every rank (egress 1x instead of world x)
+        self._mc = [_multicast_base(h, self.rank * self.n_shard * esz) for h in self._hdls]
+        want = multicast is True or (multicast == "auto" and self.world > 1)
+        self.multicast = bool(want and all(self._mc) and (self.stop - self.start) % (16 // esz) == 0)
+        if multicast is True and not self.multicast:
+            raise TernaryB200Error("multicast requested but the symmetric-memory handle has no multicast mapping "
+                                   "(or the shard width is not a multiple of 16 bytes)")
         self._turn = 0
         self._ws = None
 
@@ -213,8 +240,12 @@ class TPShardedStream(nn.Module):
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty((need,), dtype=torch.uint8, device=xs.device)
         if self.stop > self.start:
-            ops.gemv_stream_tp(xs, self.packed, self.scale, self.bias, self.maxval, self._ptrs[i], self.world, self.dtype,
-                               self.ld, self.max_tokens * self.ld, workspace=self._ws)
+            if self.multicast:
+                ops.gemv_stream_mc(xs, self.packed, self.scale, self.bias, self.maxval, self._mc[i], self.dtype,
+                                   self.ld, self.max_tokens * self.ld, workspace=self._ws)
+            else:
+                ops.gemv_stream_tp(xs, self.packed, self.scale, self.bias, self.maxval, self._ptrs[i], self.world, self.dtype,
+                                   self.ld, self.max_tokens * self.ld, workspace=self._ws)
         if barrier:
             self._hdls[i].barrier(channel=0)             # every rank's blocks of every layer have landed in every buffer
         y = self._bufs[i][:, :M, : self.out_features]

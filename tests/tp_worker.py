@@ -34,7 +34,8 @@ for (K, N) in ((4096, 11008), (11008, 4096), (1024, 1000), (256, 16 * (world - 1
     layer.scale.data.fill_(1.0 / K ** 0.5)
     tp = TPShardedLinear.from_layer(layer)
     tp_peer = TPShardedLinear.from_layer(layer).enable_peer_gather(32)
-    tp_pre = TPShardedLinear.from_layer(layer).enable_peer_gather(320)     # prefill through the tcgen05 GEMM's TMA peer stores
+    tp_pre = TPShardedLinear.from_layer(layer).enable_peer_gather(320)     # prefill: multicast stores where the box has NVLS
+    tp_pre_u = TPShardedLinear.from_layer(layer).enable_peer_gather(320, multicast=False)   # prefill: one TMA tile store per rank
     for M in (1, 8, 32, 300):
         x = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
         dist.broadcast(x, 0)
@@ -44,11 +45,12 @@ for (K, N) in ((4096, 11008), (11008, 4096), (1024, 1000), (256, 16 * (world - 1
             y2 = tp_peer(x)                                # M <= 32: fused gather (fresh tensor); M = 300: NCCL
             y3 = tp_peer(x, alias_ok=True).clone()         # second buffer, aliased form
             y4 = tp_pre(x)                                 # every M through the fused gather (M = 300: GEMM epilogue)
+            y5 = tp_pre_u(x)
         torch.cuda.synchronize()
-        good = torch.equal(want, y1) and torch.equal(want, y2) and torch.equal(want, y3) and torch.equal(want, y4)
+        good = torch.equal(want, y1) and torch.equal(want, y2) and torch.equal(want, y3) and torch.equal(want, y4) and torch.equal(want, y5)
         ok = ok and good
         say(f"K={K} N={N} M={M}: nccl {torch.equal(want, y1)} peer {torch.equal(want, y2)} peer2 {torch.equal(want, y3)} "
-            f"peer-any-M {torch.equal(want, y4)}")
+            f"peer-any-M(mc={tp_pre._peer_use_mc}) {torch.equal(want, y4)} peer-any-M(unicast) {torch.equal(want, y5)}")
 
 # list form: ONE tb200_gemv_stream_tp call + one barrier for R layers vs the unsharded tb200_gemv_stream
 for (K, N, R) in ((4096, 11008, 5), (1024, 1000, 3), (11008, 4096, 2)):
@@ -58,15 +60,18 @@ for (K, N, R) in ((4096, 11008, 5), (1024, 1000, 3), (11008, 4096, 2)):
     bias = torch.randn(R, N, generator=g, device=dev)
     a, b = shard_rows(N, world, rank)
     tps = TPShardedStream(packed[:, a:b].contiguous(), scale[:, a:b].contiguous(), bias[:, a:b].contiguous(), K, N, 100.0)
+    tps_u = TPShardedStream(packed[:, a:b].contiguous(), scale[:, a:b].contiguous(), bias[:, a:b].contiguous(), K, N, 100.0,
+                            multicast=False)
     for M in (1, 8, 32):
         xs = torch.randn(R, M, K, generator=g, device=dev, dtype=torch.bfloat16)
         want = ops.gemv_stream(xs, packed, scale, bias, 100.0)
         y1 = tps(xs)
         y2 = tps(xs, alias_ok=True).clone()
+        y3 = tps_u(xs)
         torch.cuda.synchronize()
-        good = torch.equal(want, y1) and torch.equal(want, y2)
+        good = torch.equal(want, y1) and torch.equal(want, y2) and torch.equal(want, y3)
         ok = ok and good
-        say(f"stream K={K} N={N} R={R} M={M}: {good}")
+        say(f"stream K={K} N={N} R={R} M={M}: multicast={tps.multicast} {torch.equal(want, y1) and torch.equal(want, y2)} unicast {torch.equal(want, y3)}")
 
 t = torch.tensor([1 if ok else 0], device=dev)
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
