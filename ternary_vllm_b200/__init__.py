@@ -11,7 +11,7 @@ from .modules import (  # noqa: F401
     linear_to_quantized, compute_and_set_biobjective_gradient, compute_smooth_binary_stats,
 )
 from .checkpoint import load_safetensors_packed, export_packed  # noqa: F401
-from .blocks import ChainedLinears, TernaryMLP  # noqa: F401
+from .blocks import ChainedLinears, TernaryMLP, fuse_mlp_blocks  # noqa: F401
 from .utils import quantize_moondream, clip_binary_weights, quantized_size_bits  # noqa: F401
 
 __version__ = "0.1.0"

@@ -111,3 +111,54 @@ class TernaryMLP(ChainedLinears):
     @property
     def fc2(self):
         return self.layers[1]
+
+
+# ---- wiring into an existing model (the HF Phi blocks the reference converts: quantize_moondream leaves `mlp.fc1` / `mlp.fc2`
+# as quantised layers around `mlp.activation_fn`, modeling_phi.PhiMLP / impl/tf/moondream/layers.py:32-43) ----
+_ACT_NAMES = {"NewGELUActivation": "gelu_new", "PytorchGELUTanh": "gelu_new", "GELUTanh": "gelu_new", "ReLU": "relu"}
+
+
+def _activation_name(fn):
+    """Name (key of ``_ACT_FNS``) of an activation module / callable this package can fuse, else None."""
+    if fn is None:
+        return None
+    name = type(fn).__name__
+    if name in _ACT_NAMES:
+        return _ACT_NAMES[name]
+    if isinstance(fn, nn.GELU):
+        return "gelu_new" if getattr(fn, "approximate", "none") == "tanh" else None
+    if fn is torch.relu or fn is nn.functional.relu:
+        return "relu"
+    return None
+
+
+def fuse_mlp_blocks(model: nn.Module, max_tokens: int = 2, verbose: bool = False) -> int:
+    """For every sub-module that looks like the reference's MLP block -- quantised children ``fc1`` and ``fc2`` with
+    ``fc2.in_features == fc1.out_features`` and an ``activation_fn`` / ``act`` this package knows -- route decode-shaped,
+    no-grad calls (at most ``max_tokens`` tokens) through ONE ``tb200_chain_forward`` launch; every other call keeps the
+    module's own forward.  Call it after ``quantize_moondream`` / ``load_safetensors_packed``.  Returns the number of blocks
+    fused.  The block's parameters and state dict are untouched (the fused path reads the same layers)."""
+    n = 0
+    for name, mod in list(model.named_modules()):
+        fc1, fc2 = getattr(mod, "fc1", None), getattr(mod, "fc2", None)
+        if not (isinstance(fc1, _PackedQuantLinear) and isinstance(fc2, _PackedQuantLinear)) or isinstance(mod, ChainedLinears):
+            continue
+        if fc2.in_features != fc1.out_features or getattr(mod, "_tb_fused_mlp", None) is not None:
+            continue
+        act = _activation_name(getattr(mod, "activation_fn", getattr(mod, "act", None)))
+        if act is None:
+            continue
+        fused = TernaryMLP(fc1, fc2, act)
+        fused.chain_max_tokens = max_tokens
+        object.__setattr__(mod, "_tb_fused_mlp", fused)            # not a registered child: parameters stay where they are
+        orig_forward = mod.forward
+
+        def forward(x, *args, _fused=fused, _orig=orig_forward, **kwargs):
+            if not args and not kwargs and torch.is_tensor(x) and x.is_cuda and _fused._chain_ok(x):
+                return _fused(x)
+            return _orig(x, *args, **kwargs)
+        mod.forward = forward
+        n += 1
+        if verbose:
+            print(f"fused {name}: fc1 -> {act} -> fc2 in one launch for <= {max_tokens} tokens")
+    return n

@@ -203,3 +203,45 @@ def test_mlp_module_repacks_and_falls_back(cuda):
     xt = torch.randn(2, d, device=cuda)
     mlp(xt).sum().backward()
     assert mlp.fc1.weights.grad is not None and mlp.fc2.weights.grad is not None
+
+
+def test_fuse_mlp_blocks_in_a_model(cuda):
+    """The reference's model shape: blocks with `mlp.fc1` / `mlp.activation_fn` / `mlp.fc2` (HF PhiMLP); after surgery the
+    decode call of every block is one chain launch, larger calls and training keep the module's own forward."""
+    import ternary_vllm_b200 as tb
+
+    class NewGELUActivation(torch.nn.Module):
+        def forward(self, x):
+            return torch.nn.functional.gelu(x, approximate="tanh")
+
+    class PhiMLP(torch.nn.Module):
+        def __init__(self, d, f):
+            super().__init__()
+            self.activation_fn = NewGELUActivation()
+            self.fc1 = torch.nn.Linear(d, f)
+            self.fc2 = torch.nn.Linear(f, d)
+
+        def forward(self, hidden_states):
+            return self.fc2(self.activation_fn(self.fc1(hidden_states)))
+
+    torch.manual_seed(3)
+    model = torch.nn.Sequential(PhiMLP(256, 640), PhiMLP(256, 640)).to(cuda).eval()
+    for blk in model:
+        assert tb.linear_to_quantized(blk, "ternary", "none", "none")
+    x = torch.randn(1, 256, device=cuda).bfloat16()
+    model = model.bfloat16()
+    with torch.no_grad():
+        ref = model(x)                                   # layer by layer
+        before = ops.launch_count()
+        ref = model(x)
+        per_layer = ops.launch_count() - before
+        assert tb.fuse_mlp_blocks(model) == 2 and tb.fuse_mlp_blocks(model) == 0
+        model(x)                                         # builds the plans
+        before = ops.launch_count()
+        y = model(x)
+        assert ops.launch_count() - before == 2 < per_layer          # one chain launch per block
+        err = (y.float() - ref.float()).abs().max().item()
+        assert err <= 0.03 * max(1.0, ref.float().abs().max().item())
+        xb = torch.randn(9, 256, device=cuda).bfloat16()
+        assert model(xb).shape == (9, 256)               # more tokens: the module's own forward
+    assert len(list(model.parameters())) == 8 + 4        # weights/bias/scale x 4 layers... parameters untouched by the surgery
