@@ -102,6 +102,19 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dt, int rank, const vo
     cuuint32_t bx[5] = {1, 1, 1, 1, 1}, es[5] = {1, 1, 1, 1, 1};
     for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
     for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
+    // Per-thread cache: an eager per-layer call re-encoded 3-4 maps (~1-2 us of driver time each).  A map is a pure function of
+    // the key below (address, shape, pitches, box, type, swizzle), so a hit can never be stale; 64 direct-mapped slots.
+    struct MapKey { uint64_t v[16]; };
+    struct MapSlot { MapKey key; CUtensorMap map; bool used; };
+    static thread_local MapSlot cache[64];
+    MapKey key = {};
+    key.v[0] = (uint64_t)(uintptr_t)ptr; key.v[1] = ((uint64_t)dt << 32) | ((uint64_t)rank << 8) | (uint64_t)swz;
+    for (int i = 0; i < 5; ++i) { key.v[2 + i] = d[i]; key.v[7 + i] = bx[i]; }
+    for (int i = 0; i < 4; ++i) key.v[12 + i] = st[i];
+    uint64_t h = 1469598103934665603ull;
+    for (int i = 0; i < 16; ++i) { h ^= key.v[i]; h *= 1099511628211ull; }
+    MapSlot& slot = cache[(h >> 20) & 63];
+    if (slot.used && memcmp(&slot.key, &key, sizeof(key)) == 0) { *map = slot.map; return TB200_OK; }
     CUresult r = enc(map, dt, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -109,6 +122,7 @@ int make_tensor_map(CUtensorMap* map, CUtensorMapDataType dt, int rank, const vo
                   (unsigned long long)d[0], (unsigned long long)d[1], (unsigned long long)d[2]);
         return TB200_ECUDA;
     }
+    slot.key = key; slot.map = *map; slot.used = true;
     return TB200_OK;
 }
 
