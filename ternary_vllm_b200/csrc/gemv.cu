@@ -362,16 +362,25 @@ gemv_mma_kernel(const __grid_constant__ CUtensorMap map_w, const GemvParams p) {
     const bool recycle = ntiles > stages_r;           // stages are handed back to the producer only when the ring wraps
     int s = 0; uint32_t ph = 0;
     uint4 wlo[2], whi[2], nlo[2], nhi[2];
+    // shared-memory addresses of the loop as 32-bit values the compiler cannot rematerialise: left to itself it rebuilt the
+    // ring and barrier bases from SR_CgaCtaId (S2UR + a chain of uniform-datapath instructions) on every tile
+    uint32_t a_seg0 = base + sSeg + phys0, a_seg1 = base + sSeg + phys1, a_bar = sBar;
+    asm volatile("" : "+r"(a_seg0), "+r"(a_seg1), "+r"(a_bar));
+    auto lds128 = [](uint32_t a) {
+        uint4 v;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+        return v;
+    };
     auto fetch = [&](uint4 (&lo)[2], uint4 (&hi)[2]) {
-        mbar_wait(bar_full(s), ph);
-        const uint8_t* seg = gbase + s * GV_TILE_BYTES + sSeg;
-        lo[0] = *reinterpret_cast<const uint4*>(seg + phys0);
-        hi[0] = *reinterpret_cast<const uint4*>(seg + 8 * GV_SEG + phys0);
-        lo[1] = *reinterpret_cast<const uint4*>(seg + phys1);
-        hi[1] = *reinterpret_cast<const uint4*>(seg + 8 * GV_SEG + phys1);
+        mbar_wait(a_bar + 8u * s, ph);
+        const uint32_t o = (uint32_t)s * GV_TILE_BYTES;
+        lo[0] = lds128(a_seg0 + o);
+        hi[0] = lds128(a_seg0 + o + 8 * GV_SEG);
+        lo[1] = lds128(a_seg1 + o);
+        hi[1] = lds128(a_seg1 + o + 8 * GV_SEG);
         if (recycle) {
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_empty(s));            // the tile lives in registers now
+            if (lane == 0) mbar_arrive(a_bar + 8u * (GV_MAX_STAGES + s));            // the tile lives in registers now
         }
         if (++s == stages_r) { s = 0; ph ^= 1u; }
     };

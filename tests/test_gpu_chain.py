@@ -245,3 +245,18 @@ def test_fuse_mlp_blocks_in_a_model(cuda):
         xb = torch.randn(9, 256, device=cuda).bfloat16()
         assert model(xb).shape == (9, 256)               # more tokens: the module's own forward
     assert len(list(model.parameters())) == 8 + 4        # weights/bias/scale x 4 layers... parameters untouched by the surgery
+
+
+@pytest.mark.parametrize("M", [1, 8])
+def test_chain_full_size_mlp_block(cuda, M):
+    """BASELINE-size dependent layers (the 7B-class MLP block 4096 -> 11008 -> gelu_new -> 4096, twice): every layer exactly
+    against the oracle layer fed the kernel's own stored input."""
+    dims, acts = (4096, 11008, 4096, 11008, 4096), ("gelu_new", None, "gelu_new", None)
+    gpu, cpu = build(dims, acts, seed=77 + M, cuda=cuda)
+    plan = ops.ChainPlan(gpu, dims[0], torch.bfloat16)
+    x = torch.randn(M, dims[0], generator=torch.Generator().manual_seed(100 + M)).bfloat16().to(cuda)
+    out = plan.forward(x)
+    torch.cuda.synchronize()
+    check_chain(plan, cpu, x, out, torch.bfloat16)
+    out2 = plan.forward(x)                                  # second generation (the other buffer set): same bits
+    assert torch.equal(out, out2)
