@@ -54,6 +54,7 @@ struct StreamParams {
     uint32_t img_bytes, grp_bytes;
     float clip_val;
     int one_box;
+    int contig;       // 1: a CTA takes a contiguous chunk of the global row-block list, 0: the strided list b, b + grid, ...
     int dbg;          // experiments: bit 0 skips the MMAs (memory-stream ceiling of the kernel)
 };
 
@@ -106,7 +107,14 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
     const int G = gridDim.x, b = blockIdx.x;
     const int RB = p.row_blocks;
     const int total = p.layers * RB;                       // row blocks of all layers
-    const int my_groups = total > b ? (total - b + G - 1) / G : 0;
+    // which blocks of the global list this CTA takes: a CONTIGUOUS chunk [u0, u0 + my_groups) (round 2: consecutive blocks of a
+    // CTA then belong to the same layer, so the per-layer switch -- wait for the image, 8 LDS.128 of B fragments per lane -- is
+    // paid once per ~RB blocks instead of once per block when a layer has fewer row blocks than the grid has CTAs), or the
+    // strided list b, b + G, ... of round 1 (p.contig == 0)
+    const int chunk = (total + G - 1) / G;
+    const int u0 = p.contig ? b * chunk : b, ustep = p.contig ? 1 : G;
+    const int my_groups = p.contig ? (total > u0 ? (total - u0 < chunk ? total - u0 : chunk) : 0)
+                                   : (total > b ? (total - b + G - 1) / G : 0);
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&map_w);
@@ -123,7 +131,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
         // ===================== weight tiles: independent of any previous kernel =====================
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;
-            for (int u = b; u < total; u += G) {
+            for (int gi = 0, u = u0; gi < my_groups; ++gi, u += ustep) {
                 const int l = u / RB, rb = u - l * RB;
                 for (int ks = 0; ks < p.nks; ++ks) {
                     mbar_wait_relaxed(bar_empty(s), ph ^ 1u);
@@ -145,7 +153,7 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
         if (lane == 0) {
             asm volatile("griddepcontrol.wait;" ::: "memory");
             int cur = -1, j = 0;
-            for (int u = b; u < total; u += G) {
+            for (int gi = 0, u = u0; gi < my_groups; ++gi, u += ustep) {
                 const int l = u / RB;
                 if (l == cur) continue;
                 cur = l;
@@ -199,8 +207,8 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
         const int ntiles = my_groups * nks;
         if (TEAMS == 1 && ntiles > 0) fetch(wlo, whi, 0u);
         // position in the global row-block list, advanced without divisions: u = l * RB + rb, step G = Gq * RB + Gr
-        const int Gq = G / RB, Gr = G - Gq * RB;
-        int l = b / RB, rb = b - l * RB;
+        const int Gq = ustep / RB, Gr = ustep - Gq * RB;
+        int l = u0 / RB, rb = u0 - l * RB;
         int cur = -1, ks = 0, it = 0;
         int ib = 0, ib_cur = 0; uint32_t ipar = 0;       // image buffer ring
         int sq = 0; uint32_t spar = 0;                   // partial-sum slot ring
@@ -431,12 +439,12 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
         const int g = lane >> 2, t = lane & 3;
         asm volatile("griddepcontrol.wait;" ::: "memory");
         // position of this warp's current row block and of the one it prefetches for, advanced without divisions
-        const int step = AUX * G;
+        const int step = AUX * ustep;
         const int Sq = step / RB, Sr = step - Sq * RB;
         struct Pos { int l, rb; };
         auto advance = [&](Pos& q) { q.l += Sq; q.rb += Sr; if (q.rb >= RB) { q.rb -= RB; ++q.l; } };
         Pos cp, np;
-        { const int u = b + a * G; cp.l = u / RB; cp.rb = u - cp.l * RB; }
+        { const int u = u0 + a * ustep; cp.l = u / RB; cp.rb = u - cp.l * RB; }
         np = cp;
         // scale/bias of a row block are read once per launch (cold in L2): the loads for this warp's NEXT row block are
         // issued before the current one is reduced
@@ -866,6 +874,8 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     p.one_box = one_box;
     static const int dbg_env = (int)tb_knob("TB200_STREAM_DBG", 0);
     p.dbg = dbg_env;
+    static const int contig_env = (int)tb_knob("TB200_STREAM_CONTIG", 1);
+    p.contig = contig_env;
     const int64_t total = (int64_t)p.row_blocks * layers;
     const int ctas = (int)(total < sm_count() ? total : sm_count());
     const size_t smem = stream_smem(gm, p.stages, p.nslots, p.nimg, peer_esz);
