@@ -400,9 +400,9 @@ def run_b200(args):
 
 RING_MIN = 64               # layers per ring (>= 2.2 x L2 in packed bytes for both shapes)
 # dram__bytes_read.sum + dram__bytes_write.sum of gemv_stream_kernel<1,1,2,2,0> per layer of 4096x11008, M=1:
-# (284.22 + 5.12) MB over the 25 layers of the ncu capture (profiles/r1b_gemv_stream_m1.summary.txt); the algorithmic
-# figure is 11.39 MB per layer
-TRAFFIC_BYTES_PER_LAYER = (284217344 + 5117952) / 25
+# (284.23 + 3.86) MB over the 25 layers of the ncu capture (profiles/r2_gemv_stream_m1.summary.txt, the kernel with the
+# contiguous block assignment); the algorithmic figure is 11.39 MB per layer
+TRAFFIC_BYTES_PER_LAYER = (284230656 + 3859712) / 25
 
 
 def run_e2e(args, lib, dev, rings, cases, step_bytes):
