@@ -222,7 +222,7 @@ def run_tp(args, metric):
         st0 = streams[(K, N)]
         x = xp.setdefault(K, torch.randn(Mp, K, device=dev, dtype=torch.bfloat16))
         dist.broadcast(x, 0)
-        lay_f = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0).enable_peer_gather(Mp)
+        lay_f = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0).enable_peer_gather(Mp, multicast="try")
         lay_n = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0)
         lay_u = TPShardedLinear(st0.packed[0], st0.scale[0], st0.bias[0], K, N, 100.0).enable_peer_gather(Mp, multicast=False)
 
@@ -265,6 +265,8 @@ def run_tp(args, metric):
         ops_ = 2.0 * Mp * N * K
         prefill.append({"K": K, "N": N, "M": Mp, "us_fused_peer_gather": t_fused * 1e6, "tops_fused": ops_ / t_fused / 1e12,
                         "fused_launch_mode": fused_mode, "fused_multicast": bool(lay_f._peer_use_mc),
+                        "default_form": "multicast" if (world > 4 and lay_f._peer_use_mc) else "unicast",
+                        "us_fused_default": (t_fused if (world > 4 and lay_f._peer_use_mc) else t_unicast) * 1e6,
                         "us_fused_unicast_tma_stores": t_unicast * 1e6, "us_local_gemm_only": t_local * 1e6, "us_nccl_all_gather_plus_relayout": t_gather * 1e6,
                         "us_local_gemm_then_nccl": t_nccl * 1e6, "tops_nccl": ops_ / t_nccl / 1e12,
                         "tokens_per_s_fused": Mp / t_fused,

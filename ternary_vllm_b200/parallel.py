@@ -97,7 +97,7 @@ class TPShardedLinear(nn.Module):
         return buf.view(self.world, M, self.n_shard).permute(1, 0, 2).reshape(M, self.world * self.n_shard)[:, : self.out_features]
 
     # -- fused gather over NVLink peer memory (decode shapes) -------------------------------------------
-    def enable_peer_gather(self, max_tokens: int = 32, dtype=torch.bfloat16, multicast: bool = True):
+    def enable_peer_gather(self, max_tokens: int = 32, dtype=torch.bfloat16, multicast="auto"):
         """Allocate two symmetric (peer-mapped) output buffers [max_tokens, world*n_shard] and exchange their
         addresses.  Afterwards ``forward`` for <= ``max_tokens`` tokens runs ``tb200_linear_forward_tp``: the GEMV
         epilogue (<= 32 tokens) or the tcgen05 GEMM's epilogue (prefill: TMA tile stores) writes this rank's column block
@@ -122,7 +122,8 @@ class TPShardedLinear(nn.Module):
             self._peer_hdls.append(hdl)
             self._peer_ptrs.append(ptrs)
         self._peer_mc = [_multicast_base(h, self.rank * self.n_shard * esz) for h in self._peer_hdls]
-        self._peer_use_mc = bool(multicast and self.world > 1 and all(self._peer_mc) and (self.stop - self.start) % (16 // esz) == 0)
+        want_mc = multicast is True or multicast == "try" or (multicast == "auto" and self.world > 4)        # see TPShardedStream
+        self._peer_use_mc = bool(want_mc and self.world > 1 and all(self._peer_mc) and (self.stop - self.start) % (16 // esz) == 0)
         self._peer_turn = 0
         return self
 
@@ -219,7 +220,9 @@ class TPShardedStream(nn.Module):
                                                                for r in _rotated(self.rank, self.world)]))
         # NVSwitch multicast mapping of the same buffers: one store reaches every rank (egress 1x instead of world x)
         self._mc = [_multicast_base(h, self.rank * self.n_shard * esz) for h in self._hdls]
-        want = multicast is True or (multicast == "auto" and self.world > 1)
+        # measured (bench_tp.py): the multicast form wins on 8 GPUs (egress 1x instead of 8x: 13.7 -> 16.8 TB/s) and loses on
+        # 2 / 4, where the per-rank TMA tile stores move few copies in larger pieces (prefill M=4096 on 2 GPUs: 113 vs 170 us)
+        want = multicast is True or multicast == "try" or (multicast == "auto" and self.world > 4)
         self.multicast = bool(want and all(self._mc) and (self.stop - self.start) % (16 // esz) == 0)
         if multicast is True and not self.multicast:
             raise TernaryB200Error("multicast requested but the symmetric-memory handle has no multicast mapping "

@@ -34,7 +34,7 @@ for (K, N) in ((4096, 11008), (11008, 4096), (1024, 1000), (256, 16 * (world - 1
     layer.scale.data.fill_(1.0 / K ** 0.5)
     tp = TPShardedLinear.from_layer(layer)
     tp_peer = TPShardedLinear.from_layer(layer).enable_peer_gather(32)
-    tp_pre = TPShardedLinear.from_layer(layer).enable_peer_gather(320)     # prefill: multicast stores where the box has NVLS
+    tp_pre = TPShardedLinear.from_layer(layer).enable_peer_gather(320, multicast="try")     # prefill: NVSwitch multicast stores where available
     tp_pre_u = TPShardedLinear.from_layer(layer).enable_peer_gather(320, multicast=False)   # prefill: one TMA tile store per rank
     for M in (1, 8, 32, 300):
         x = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
@@ -59,7 +59,8 @@ for (K, N, R) in ((4096, 11008, 5), (1024, 1000, 3), (11008, 4096, 2)):
     scale = torch.rand(R, N, generator=g, device=dev) / K ** 0.5
     bias = torch.randn(R, N, generator=g, device=dev)
     a, b = shard_rows(N, world, rank)
-    tps = TPShardedStream(packed[:, a:b].contiguous(), scale[:, a:b].contiguous(), bias[:, a:b].contiguous(), K, N, 100.0)
+    tps = TPShardedStream(packed[:, a:b].contiguous(), scale[:, a:b].contiguous(), bias[:, a:b].contiguous(), K, N, 100.0,
+                          multicast="try")          # multicast wherever the box has a mapping
     tps_u = TPShardedStream(packed[:, a:b].contiguous(), scale[:, a:b].contiguous(), bias[:, a:b].contiguous(), K, N, 100.0,
                             multicast=False)
     for M in (1, 8, 32):
