@@ -32,6 +32,10 @@ constexpr int SV_TILE_BYTES = 16 * 1024;
 constexpr int SV_MMA_WARPS = 8;
 // warp roles: [0, 8) MMA | 8 tile producer | 9 image producer | 10.. aux
 constexpr int sv_threads(int aux) { return (8 + 2 + aux) * 32; }
+// TEAMS == 2 with FOUR aux warps serves the tensor-parallel epilogue (its staging + peer / multicast stores do not fit the two aux
+// warps' time budget: tools/peer_cost.py, 212 -> 170 us with one local destination against 147 us without the gather).  14 warps at
+// 128 registers; a 16-warp form re-balanced with setmaxnreg (MMA warps 160, the rest 96) spilled in the aux loop and was slower.
+constexpr int sv_threads2(int teams, int aux) { return sv_threads(aux); }
 constexpr int SV_MAX_STAGES = 12;
 constexpr int SV_MAX_SLOTS = 8;
 constexpr int SV_MAX_IMG = 4;
@@ -47,6 +51,7 @@ struct StreamParams {
     // shared memory and stored with ONE TMA tile store per rank into that rank's [layers, M, ldo] buffer (peer-mapped
     // NVLink addresses; tensor maps in PeerMaps, already offset to this rank's column block; TMA clips rows >= N, tokens >= M)
     int n_peers; uint32_t peer_stage_off;     // staging tiles of the aux warps, byte offset in dynamic shared memory
+    void* peer_ptrs[8]; int direct;           // direct != 0: 16-byte st.global per piece and rank straight from the staging tile (no TMA)
     void* mc_out;                             // non-null: NVSwitch multicast address of this rank's column block -> multimem stores instead of per-rank TMA stores
     int64_t N;
     int M, Mg, nks, row_blocks, layers;
@@ -83,7 +88,7 @@ struct NoPeerMaps { int unused; };
 template <bool PEER> struct PeerArg { using type = NoPeerMaps; };
 template <> struct PeerArg<true> { using type = PeerMaps; };
 template <int NG, bool BREG, int TEAMS, int AUX, bool PEER>
-__global__ void __launch_bounds__(sv_threads(AUX), 1)
+__global__ void __launch_bounds__(sv_threads2(TEAMS, AUX), 1)
 gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ typename PeerArg<PEER>::type pm, const StreamParams p) {
     extern __shared__ uint8_t smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
@@ -127,6 +132,12 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
     asm volatile("griddepcontrol.launch_dependents;");
 
     constexpr int SV_WARP_TILES = 8, SV_WARP_IMAGE = 9, SV_WARP_AUX0 = 10;
+    constexpr bool REBAL = false;
+    if constexpr (REBAL) {
+        if (warp < SV_MMA_WARPS) asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");
+        else asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");
+        if (warp >= SV_WARP_AUX0 + AUX) return;              // two idle warps complete the fourth warpgroup
+    }
     if (warp == SV_WARP_TILES) {
         // ===================== weight tiles: independent of any previous kernel =====================
         if (lane == 0) {
@@ -483,6 +494,32 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
             if (lane == 0) for (int r = 0; r < p.n_peers; ++r) tma_prefetch_desc(&pm.m[r]);
         }
         [[maybe_unused]] int pcnt = 0;                   // staging tiles written by this warp (peer gather)
+        [[maybe_unused]] int64_t prev_off = 0; [[maybe_unused]] int prev_rb = 0;
+        // per-lane constants of the direct / multicast store of a staged tile: lane -> (token, 16-byte piece of its 16 rows)
+        const uint32_t esz_c = p.out_dtype == TB200_F32 ? 4u : 2u;
+        const int ppr_c = (int)(SV_ROWS * esz_c / 16), tok_c = lane / ppr_c, cpi_c = lane - tok_c * ppr_c;
+        const uint32_t stage0 = smem_u32(gbase) + p.peer_stage_off + (uint32_t)(a * SV_PEER_BUFS * (NG * 8 * SV_ROWS)) * esz_c;
+        auto flush_tile = [&](int buf, int64_t obase_prev, int rb_prev, bool valid) {
+            if constexpr (PEER) {
+                if (!valid) return;
+                for (int pc = lane, tok = tok_c; pc < p.M * ppr_c; pc += 32, tok += 32 / ppr_c) {
+                    const int64_t row = (int64_t)rb_prev * SV_ROWS + cpi_c * (16 / (int)esz_c);
+                    if (row < p.N) {
+                        uint4 v;
+                        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                                     : "r"(stage0 + (uint32_t)(buf * (NG * 8 * SV_ROWS)) * esz_c + (uint32_t)(pc * 16)));
+                        const int64_t off = (obase_prev + (int64_t)tok * p.ldo + row) * esz_c;
+                        if (p.mc_out) {
+                            multimem_st_128(reinterpret_cast<uint8_t*>(p.mc_out) + off, v);
+                        } else {
+#pragma unroll
+                            for (int r = 0; r < 8; ++r)
+                                if (r < p.n_peers) *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.peer_ptrs[r]) + off) = v;
+                        }
+                    }
+                }
+            }
+        };
 #pragma unroll 1
         for (int sn0 = a; sn0 < my_groups; sn0 += SV_FIFO * AUX) {
 #pragma unroll
@@ -551,44 +588,40 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
                     }
                 }
             }
-            if constexpr (PEER) {
+            if (PEER && kAblate && (p.dbg & 2)) {                  // experiment: the PEER instantiation without its stores
+                if (yv[0][0] == 123.456f) p.acc_out[0] = 1;
+            } else if constexpr (PEER) {
                 // tile [8*NG tokens][16 rows] -> staging (two buffers per aux warp) -> one TMA store per rank
                 const uint32_t esz = p.out_dtype == TB200_F32 ? 4u : 2u;
                 const uint32_t stg = smem_u32(gbase) + p.peer_stage_off + (uint32_t)((a * SV_PEER_BUFS + (pcnt & (SV_PEER_BUFS - 1))) * (NG * 8 * SV_ROWS)) * esz;
                 // the stores that last read `stg` are done (a tile store queues behind the weight tiles in flight, so
                 // several staging buffers per warp are needed to keep the warp from waiting for it)
-                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(SV_PEER_BUFS - 1) : "memory");
-                __syncwarp();
+                if (!(p.direct || p.mc_out)) {
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(SV_PEER_BUFS - 1) : "memory");
+                    __syncwarp();
+                }
+                if (kAblate && (p.dbg & 4)) { if (yv[0][0] + yv[0][1] + yv[0][2] + yv[0][3] == 123.456f) p.acc_out[0] = 1; } else
 #pragma unroll
                 for (int q = 0; q < NG; ++q)
 #pragma unroll
                     for (int e4 = 0; e4 < 4; ++e4) {
                         const uint32_t el = (uint32_t)((8 * q + 2 * t + (e4 & 1)) * SV_ROWS + g + 8 * (e4 >> 1));
                         if (p.out_dtype == TB200_F32) {
-                            asm volatile("st.shared.f32 [%0], %1;" ::"r"(stg + el * 4u), "f"(yv[q][e4]) : "memory");
+                            asm volatile("st.shared.f32 [%0], %1;" ::"r"(stg + el * 4u), "f"(yv[q][e4]));
                         } else {
                             unsigned short h;
                             if (p.out_dtype == TB200_BF16) { const __nv_bfloat16 v = __float2bfloat16_rn(yv[q][e4]); h = *reinterpret_cast<const unsigned short*>(&v); }
                             else { const __half v = __float2half_rn(yv[q][e4]); h = *reinterpret_cast<const unsigned short*>(&v); }
-                            asm volatile("st.shared.u16 [%0], %1;" ::"r"(stg + el * 2u), "h"(h) : "memory");
+                            asm volatile("st.shared.u16 [%0], %1;" ::"r"(stg + el * 2u), "h"(h));
                         }
                     }
-                if (p.mc_out) {
-                    // multicast gather: the [tokens][16 rows] tile leaves as 16-byte multimem stores (one per 8 / 4 channels of a
-                    // token), replicated by the switch into every rank's buffer
-                    __syncwarp();
-                    const int ppr = (int)(SV_ROWS * esz / 16);                   // pieces per token row: 2 (16-bit) or 4 (fp32)
-                    for (int pc = lane; pc < p.M * ppr; pc += 32) {
-                        const int tok = pc / ppr, cpi = pc - tok * ppr;
-                        const int64_t row = (int64_t)cp.rb * SV_ROWS + cpi * (16 / (int)esz);
-                        if (row < p.N) {
-                            uint4 v;
-                            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                                         : "r"(stg + (uint32_t)(pc * 16)) : "memory");
-                            multimem_st_128(reinterpret_cast<uint8_t*>(p.mc_out) + (obase + (int64_t)tok * p.ldo + row) * esz, v);
-                        }
-                    }
-                    __syncwarp();
+                if (p.direct || p.mc_out) {
+                    // 16-byte stores straight from the staging tile (per rank, or ONE multimem store that the switch replicates),
+                    // software-pipelined: the tile staged for the PREVIOUS row block leaves now, so the st.shared -> ld.shared
+                    // round trip of the current one is never waited for.  (TMA tile stores queue behind the ~128 KB of weight
+                    // tiles in flight per SM; the aux warps have no slack: tools/peer_cost.py.)
+                    if (!(kAblate && (p.dbg & 8))) flush_tile((pcnt - 1) & (SV_PEER_BUFS - 1), prev_off, prev_rb, pcnt > 0);
+                    prev_off = obase; prev_rb = cp.rb;
                 } else {
                 fence_proxy_async();
                 __syncwarp();
@@ -602,6 +635,9 @@ gemv_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_const
             }
             advance(cp);
           }
+        }
+        if constexpr (PEER) {
+            if (p.direct || p.mc_out) { __syncwarp(); flush_tile((pcnt - 1) & (SV_PEER_BUFS - 1), prev_off, prev_rb, pcnt > 0); }
         }
         if (PEER && lane == 0) {
             // all tile stores of this warp have completed; grid completion orders them before the caller's barrier kernel
@@ -738,7 +774,8 @@ static size_t stream_stage_off(const StreamGeom& gm, int stages, int nslots, int
 static size_t stream_stage_bytes(const StreamGeom& gm, bool peers, int aux, size_t esz) { return peers ? (size_t)aux * SV_PEER_BUFS * gm.ng * 8 * SV_ROWS * esz : 0; }
 static size_t stream_smem(const StreamGeom& gm, int stages, int nslots, int nimg, size_t peer_esz = 0) {
     static const int teams = (int)tb_knob("TB200_STREAM_TEAMS", 2);
-    const int aux = (gm.ng == 1 && teams != 2) ? 4 : 2;         // as dispatched in gemv_stream_impl
+    static const int aux4 = (int)tb_knob("TB200_STREAM_AUX4", -1);
+    const int aux = (gm.ng == 1 && (teams != 2 || aux4 > 0 || (aux4 < 0 && peer_esz > 0))) ? 4 : 2;         // as dispatched in gemv_stream_impl (staging: an upper bound is fine)
     return 1024 + stream_stage_off(gm, stages, nslots, nimg) + stream_stage_bytes(gm, peer_esz > 0, aux, peer_esz) + 64;
 }
 // ring depth first (bytes in flight), then a second image buffer, then more slots
@@ -773,7 +810,7 @@ static int launch_stream_v(const CUtensorMap& map, const typename PeerArg<PEER>:
     TB_CUDA(ensure_dynamic_smem(kern, optin, smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas, 1, 1);
-    cfg.blockDim = dim3(sv_threads(AUX), 1, 1);
+    cfg.blockDim = dim3(sv_threads2(TEAMS, AUX), 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
@@ -860,6 +897,9 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
         for (int r = n_peers; r < 8; ++r) peer_maps.m[r] = peer_maps.m[0];
         pm = &peer_maps;
         p.n_peers = n_peers;
+        for (int r = 0; r < n_peers; ++r) p.peer_ptrs[r] = peers[r];
+        static const int direct_env = (int)tb_knob("TB200_STREAM_PEER_DIRECT", 1);
+        p.direct = (direct_env && N % (16 / (int64_t)os) == 0) ? 1 : 0;     // whole 16-byte pieces only (else TMA clips the ragged edge)
         if (mc) {
             if (N % (16 / (int64_t)os)) { set_error("gemv_stream_mc: N_local must be a multiple of %d", (int)(16 / os)); return TB200_EINVAL; }
             p.mc_out = peers[0];
@@ -882,6 +922,8 @@ int gemv_stream_impl(const void* x, int x_dtype, int64_t M, int64_t K, int64_t l
     switch (gm.ng) {
         case 1: {
             static const int teams = (int)tb_knob("TB200_STREAM_TEAMS", 2);
+            static const int aux4 = (int)tb_knob("TB200_STREAM_AUX4", -1);     // -1: four aux warps for the tensor-parallel epilogue only
+            if (teams == 2 && breg && (aux4 > 0 || (aux4 < 0 && pm))) return launch_stream<1, true, 2, 4>(map, pm, p, smem, ctas, true, s);
             if (teams == 2)
                 return breg ? launch_stream<1, true, 2, 2>(map, pm, p, smem, ctas, true, s) : launch_stream<1, false, 2, 2>(map, pm, p, smem, ctas, true, s);
             return breg ? launch_stream<1, true, 1, 4>(map, pm, p, smem, ctas, true, s) : launch_stream<1, false, 1, 4>(map, pm, p, smem, ctas, true, s);
