@@ -316,6 +316,22 @@ int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64_t K, int64
                          void* out, int out_dtype, int64_t ldo,
                          void* workspace, void* stream);
 
+/* Allocation-free variant of tb200_linear_forward.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments and results as tb200_linear_forward minus `workspace`: the activation quantiser's scratch
+ * lives in a file-scope device array of TB200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  Limit: returns TB200_EINVAL when
+ * tb200_linear_workspace(M, K) > TB200_STATIC_SCRATCH_BYTES (8 MiB: e.g. 1024 tokens at K = 4096, 729 at K = 11008);
+ * M <= 8 never touches the scratch.  All calls on a GPU share the array and it keeps the last call's contents (nothing in
+ * it needs to start at zero: each call rewrites what it reads): calls that OVERLAP on one GPU -- two streams, or two
+ * graphs replayed concurrently -- race; serialise them or give the others tb200_linear_forward with their own workspace. */
+#define TB200_STATIC_SCRATCH_BYTES (8u << 20)
+size_t tb200_linear_static_scratch_bytes(void);
+int tb200_linear_forward_static(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+                                const uint8_t* packed, int64_t ld_packed, int64_t N,
+                                const float* scale, const float* bias, float clip_val,
+                                void* out, int out_dtype, int64_t ldo, void* stream);
+
 /* Tensor-parallel decode layer (M <= 32) with the all-gather fused into the epilogue: this rank's
  * [M, N_local] output block is stored into EVERY rank's [M, ldo] buffer through peer-mapped (NVLink)
  * pointers; out_peers[r] addresses element (0, first column of this rank's block) of rank r's buffer

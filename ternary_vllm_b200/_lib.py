@@ -99,6 +99,9 @@ SIGNATURES = {
     "tb200_linear_workspace": (_sz, [_i64, _i64]),
     "tb200_linear_forward": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
                                     _vp, _i32, _i64, _vp, _vp]),
+    "tb200_linear_static_scratch_bytes": (_sz, []),
+    "tb200_linear_forward_static": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
+                                           _vp, _i32, _i64, _vp]),
     "tb200_linear_forward_tp": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
                                        _vp, _i32, _i32, _i64, _vp, _vp]),
     "tb200_linear_forward_host": (_i32, [_vp, _i32, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,

@@ -133,3 +133,52 @@ extern "C" int tb200_linear_forward_mc(const void* x, int x_dtype, int64_t M, in
     return tb200_linear_forward_tp(x, x_dtype, M, K, ldx, packed, ld_packed, N_local, scale, bias, clip_val, peers, -1, out_dtype, ldo,
                                    workspace, stream);
 }
+
+// ---- allocation-free whole-layer call (no counterpart in the reference) ----
+// Callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) have no
+// workspace to hand to tb200_linear_forward.  This variant keeps the scratch of the activation quantiser (int8 rows,
+// per-token scales and sums, read by the GEMV / tcgen05 GEMM that follows) in a file-scope device array: every GPU that
+// loads the library holds TB200_STATIC_SCRATCH_BYTES until exit.  All calls share the array, on every stream: calls
+// that overlap on one GPU race.  Nothing in it has to start at zero -- the quantiser writes every byte the matmul kernels
+// read before they read it (the caller-provided workspace of tb200_linear_forward is uninitialised memory as well).
+static __device__ __align__(256) unsigned char g_static_scratch[TB200_STATIC_SCRATCH_BYTES];
+
+namespace tb200 {
+// g_static_scratch is, in host code, a host-side stand-in for the symbol, not a device address: the device address is
+// asked for once per device, with that device current.
+constexpr int STATIC_SCRATCH_MAX_DEVICES = 64;
+static std::atomic<void*> g_static_scratch_ptr[STATIC_SCRATCH_MAX_DEVICES];
+
+static int static_scratch(void** ptr) {
+    int dev = -1;
+    TB_CUDA(cudaGetDevice(&dev));
+    TB_REQUIRE(dev >= 0 && dev < STATIC_SCRATCH_MAX_DEVICES, "linear_forward_static: device ordinal %d out of range", dev);
+    void* p = g_static_scratch_ptr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        TB_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));       // of the CURRENT device's copy of the array
+        TB_REQUIRE(p && (uintptr_t)p % 256 == 0, "linear_forward_static: cudaGetSymbolAddress returned a bad address");
+        g_static_scratch_ptr[dev].store(p, std::memory_order_release);   // racing first calls store the same value
+    }
+    *ptr = p;
+    return TB200_OK;
+}
+}  // namespace tb200
+
+extern "C" size_t tb200_linear_static_scratch_bytes(void) { return (size_t)TB200_STATIC_SCRATCH_BYTES; }
+
+extern "C" int tb200_linear_forward_static(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
+                                           const uint8_t* packed, int64_t ld_packed, int64_t N,
+                                           const float* scale, const float* bias, float clip_val,
+                                           void* out, int out_dtype, int64_t ldo, void* stream) {
+    TB_DEVICE_OR_RETURN();
+    TB_REQUIRE(M >= 0 && K >= 0, "linear_forward_static: bad shape");
+    const size_t need = tb200_linear_workspace(M, K);
+    TB_REQUIRE(need <= (size_t)TB200_STATIC_SCRATCH_BYTES,
+               "linear_forward_static: M=%lld tokens x K=%lld needs %zu bytes of scratch, the static array holds %zu "
+               "(TB200_STATIC_SCRATCH_BYTES); split the tokens or call tb200_linear_forward with a workspace",
+               (long long)M, (long long)K, need, (size_t)TB200_STATIC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    int rc = static_scratch(&scratch);
+    if (rc) return rc;
+    return tb200_linear_forward(x, x_dtype, M, K, ldx, packed, ld_packed, N, scale, bias, clip_val, out, out_dtype, ldo, scratch, stream);
+}
