@@ -416,23 +416,40 @@ def run_e2e(args, lib, dev, rings, cases, step_bytes):
     hy = {c: torch.empty(R[c], c[2], c[1], dtype=torch.bfloat16).pin_memory() for c in cases}
     dx = {c: torch.empty(R[c], c[2], c[0], dtype=torch.bfloat16, device=dev) for c in cases}
     dy = {c: torch.empty(R[c], c[2], c[1], dtype=torch.bfloat16, device=dev) for c in cases}
-    ws = {c: torch.empty(lib.tb200_gemv_stream_workspace(c[2], c[0], R[c]), dtype=torch.uint8, device=dev) for c in cases}
     h2d = sum(hx[c].numel() * 2 for c in cases)
     d2h = sum(hy[c].numel() * 2 for c in cases)
 
-    # independent sweep cases go to three streams round-robin, so that one case's H2D copy, another's kernels and a
-    # third's D2H copy overlap (PCIe is full duplex; the copies are 124 MB per step against 0.8 ms of kernels)
-    side = [torch.cuda.Stream(dev) for _ in range(3)]
+    # Scheduling of the copies (PCIe is full duplex; the copies are 124 MB per step against 0.8 ms of kernels, so the step is
+    # bound by the 80 MB of device -> host traffic): a case whose output exceeds E2E_PIECE_BYTES goes through the call in
+    # several pieces of consecutive layers (the API takes any `count`), so that one piece's D2H copy overlaps the next
+    # piece's kernels, and the jobs are issued in flow-shop (Johnson) order -- short uploads first, short downloads last --
+    # round-robin over four streams.
+    piece = int(os.environ.get("TB200_E2E_PIECE_BYTES", 12 << 20))
+    jobs = []
+    for c in cases:
+        K, N, M = c
+        out_bytes = R[c] * M * N * 2
+        npieces = max(1, min(R[c], -(-out_bytes // piece))) if piece > 0 else 1
+        per = -(-R[c] // npieces)
+        for l0 in range(0, R[c], per):
+            cnt = min(per, R[c] - l0)
+            jobs.append({"c": c, "l0": l0, "cnt": cnt, "a": cnt * M * K * 2, "b": cnt * M * N * 2,
+                         "ws": torch.empty(lib.tb200_gemv_stream_workspace(M, K, cnt), dtype=torch.uint8, device=dev)})
+    first = sorted((j for j in jobs if j["a"] < j["b"]), key=lambda j: j["a"])
+    last = sorted((j for j in jobs if j["a"] >= j["b"]), key=lambda j: -j["b"])
+    jobs = first + last
+    side = [torch.cuda.Stream(dev) for _ in range(4)]
+    for i, j in enumerate(jobs):
+        K, N, M = j["c"]
+        ring, l0 = rings[(K, N)], j["l0"]
+        j["args"] = (hx[j["c"]][l0].data_ptr(), L.TB200_BF16, M, K, ring.packed[l0].data_ptr(), ring.packed.stride(1),
+                     ring.packed.stride(0), N, ring.scale[l0].data_ptr(), ring.bias[l0].data_ptr(), N, 100.0,
+                     hy[j["c"]][l0].data_ptr(), L.TB200_BF16, j["cnt"], dx[j["c"]][l0].data_ptr(), dy[j["c"]][l0].data_ptr(),
+                     j["ws"].data_ptr(), side[i % len(side)].cuda_stream)
 
     def step():
-        for i, c in enumerate(cases):
-            s = side[i % 3].cuda_stream
-            K, N, M = c
-            ring = rings[(K, N)]
-            rc = lib.tb200_gemv_stream_host(hx[c].data_ptr(), L.TB200_BF16, M, K, ring.packed.data_ptr(), ring.packed.stride(1),
-                                            ring.packed.stride(0), N, ring.scale.data_ptr(), ring.bias.data_ptr(), N, 100.0,
-                                            hy[c].data_ptr(), L.TB200_BF16, R[c], dx[c].data_ptr(), dy[c].data_ptr(),
-                                            ws[c].data_ptr(), s)
+        for j in jobs:
+            rc = lib.tb200_gemv_stream_host(*j["args"])
             if rc:
                 L.check(rc, "gemv_stream_host")
         for st in side:
@@ -456,10 +473,26 @@ def run_e2e(args, lib, dev, rings, cases, step_bytes):
         step()
     torch.cuda.synchronize()
     ms = (time.perf_counter() - t0) * 1e3          # host clock around synchronous steps: every step ends with the result on the host
-    return {"value": step_bytes * steps / (ms * 1e-3) / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d,
+    # what the PCIe link alone takes for the step's copies (same buffers, no kernels; uploads and downloads on two streams)
+    def copies():
+        with torch.cuda.stream(side[0]):
+            for c in cases:
+                dx[c].copy_(hx[c], non_blocking=True)
+        with torch.cuda.stream(side[1]):
+            for c in cases:
+                hy[c].copy_(dy[c], non_blocking=True)
+        side[0].synchronize(); side[1].synchronize()
+    copies()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        copies()
+    copies_ms = (time.perf_counter() - t0) * 1e3 / 5
+    return {"value": step_bytes * steps / (ms * 1e-3) / 1e9, "unit": "GB/s", "h2d_bytes_per_step": h2d, "copies_only_ms_per_step": copies_ms,
             "d2h_bytes_per_step": d2h, "steps": steps, "ms_per_step": ms / steps,
+            "calls_per_step": len(jobs),
             "api": "tb200_gemv_stream_host per sweep case (pinned host x -> device, quantiser + persistent GEMV over the "
-                   "ring, device -> pinned host y), cases round-robin on three streams, all synchronised at the end of every step"}
+                   "ring, device -> pinned host y); cases with more than 12 MB of output go in pieces of consecutive layers, "
+                   "calls in flow-shop order round-robin on four streams, all synchronised at the end of every step"}
 
 
 VIT_SHAPES = [(1024, 3072), (1024, 1024), (1024, 4096), (4096, 1024)]     # configs[3]: ViT-L/14 QKV, proj, fc1, fc2; M = 32 x 257
