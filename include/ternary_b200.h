@@ -158,6 +158,9 @@ int tb200_binary_init(const void* W, int dtype, int64_t N, int64_t K, int per_ro
 #define TB200_QLAYOUT_NATURAL 0
 #define TB200_QLAYOUT_GEMM    1
 #define TB200_QLAYOUT_GEMV    2
+#define TB200_QLAYOUT_GEMM_SPLIT 3 /* library-internal operand order of the 32-token tcgen05 kernel of decode lists: inside every
+                                     256-element block, element 16j + 4b + f (f = 2-bit field of packed byte b of word j) sits at
+                                     128 (f & 1) + 8 j + 4 (f >> 1) + b; needs ldq % 256 == 0 (zero-filled beyond K) */
 int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K, int64_t ldx,
                        int8_t* q_x, int64_t ldq, float* s_x, int32_t* sum_qx, int layout,
                        void* stream);

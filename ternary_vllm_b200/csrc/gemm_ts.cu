@@ -31,18 +31,37 @@ constexpr int TS_EXP_SETS = 2;       // expander warp sets (4 warps each) taking
 constexpr int TS_THREADS = 256 + 128 * TS_EXP_SETS;   // warps: 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue, 8.. expanders
 constexpr int TS_P_BYTES = TS_ROWS * (TS_BK / 4);   // 8 KB packed weights per stage (64 bytes per row)
 constexpr int TS_A_COLS = TS_BK / 4; // 64 columns per A tile
+// experiment switches per warp role (TB200_GEMM_DBG bits in the experiment library; -DTS_DBG_x=1 keeps one role's test in a
+// release build: the presence of these branches changes the compiler's schedule of the role's loop)
+#ifndef TS_DBG_PROD
+#define TS_DBG_PROD kAblate
+#endif
+#ifndef TS_DBG_MMA
+#define TS_DBG_MMA kAblate
+#endif
+#ifndef TS_DBG_EPI
+#define TS_DBG_EPI kAblate
+#endif
+#ifndef TS_DBG_EXP
+#define TS_DBG_EXP kAblate
+#endif
+constexpr bool kDbgProd = TS_DBG_PROD, kDbgMma = TS_DBG_MMA, kDbgEpi = TS_DBG_EPI, kDbgExp = TS_DBG_EXP;
 
-template <int BT, int OSZ = 4> struct TsCfg {
+template <int BT, int OSZ = 4, int NF = 1> struct TsCfg {
     static constexpr int B_BYTES = BT * TS_BK;
     static constexpr int STAGE_BYTES = B_BYTES + TS_P_BYTES;
     static constexpr int STAGES = BT >= 192 ? 3 : BT >= 128 ? 4 : BT >= 64 ? 6 : BT >= 32 ? 12 : 8;   // 160 -> 4 stages of 48 KB
     // skinny token tiles: TWO warps issue the MMAs of alternate k-blocks into their own accumulator (the issuing warp's
     // instruction chain, not the tensor pipe, bounds 32-token tiles); the epilogue adds the two partial sums
     static constexpr int DUAL = BT <= 32 ? 2 : 1;
-    static constexpr int D_COLS = 2 * BT * DUAL;
+    // NF == 2 ("field-split", 32-token tiles of decode lists, activations in TB200_QLAYOUT_GEMM_SPLIT order): the expanders mask
+    // the odd 2-bit fields IN PLACE (w & 0x0c0c0c0c: value 4c) instead of shifting them down -- 5 instead of 7 alu-pipe
+    // instructions per packed word, and that pipe bounds skinny token tiles -- so even and odd fields go to separate
+    // accumulators (lo, hi) and the epilogue forms lo + (hi >> 2), exactly.
+    static constexpr int D_COLS = 2 * BT * DUAL * NF;
     // A tiles in TMEM: the expand -> MMA -> retire -> reuse loop of a slot is ~2000 clocks long, so skinny token tiles
     // (which finish a k-block's MMAs quickly and have TMEM columns to spare) keep six of them in flight
-    static constexpr int NSA = BT <= 32 ? 6 : BT <= 64 ? 4 : 2;
+    static constexpr int NSA = NF == 2 ? 4 : BT <= 32 ? 6 : BT <= 64 ? 4 : 2;
     static constexpr int NEED = D_COLS + NSA * TS_A_COLS;
     static constexpr int TMEM_COLS = NEED <= 32 ? 32 : NEED <= 64 ? 64 : NEED <= 128 ? 128 : NEED <= 256 ? 256 : 512;
     static_assert(NEED <= 512, "TMEM budget");
@@ -55,11 +74,12 @@ template <int BT, int OSZ = 4> struct TsCfg {
 // CL = thread-block cluster size: the CL CTAs of a cluster work on CL adjacent weight tiles and the SAME
 // token tile; each loads 1/CL of the activation tile and TMA-multicasts it to all of them, which divides
 // the L2 -> SM operand traffic that bounds the single-CTA kernel (profiles/README.md, ablation table).
-template <typename OT, int BT, int CL>
+template <typename OT, int BT, int CL, int NF = 1>
 __global__ void __launch_bounds__(TS_THREADS, 1)
 umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_pw,
                const __grid_constant__ CUtensorMap map_out, const __grid_constant__ PeerMaps pm, const UmmaParams p) {
-    using Cfg = TsCfg<BT, (int)sizeof(OT)>;
+    using Cfg = TsCfg<BT, (int)sizeof(OT), NF>;
+    static_assert(NF == 1 || (CL == 1 && BT == 32), "field-split accumulators: 32-token single-CTA form only");
     constexpr int NS = Cfg::STAGES;
     constexpr int TS_NSA = Cfg::NSA;
     static_assert(NS > TS_NSA, "a stage's done barrier must not wrap before its A slot is reused");
@@ -93,6 +113,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
     const int tiles_per_layer = p.m_tiles * n_groups;       // super-tiles: CL weight tiles x one token tile
     const int total_tiles = tiles_per_layer * p.layers;
     constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1u);
+    const int t_begin = cluster_id, t_end = total_tiles, t_step = num_clusters;     // tiles of this CTA (cluster): round-robin
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&map_act);
@@ -124,10 +145,42 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
+        // CL == 1: the WHOLE warp runs the loop and one elected lane issues (as the MMA warps do): the loop is warp-uniform, so
+        // barrier addresses and tile coordinates stay in uniform registers.  In the single-thread form every TMA operand went
+        // through an R2UR broadcast loop and the thread's ~3 TMAs per k-block were co-critical for skinny token tiles
+        // (a k-block is ~600 clocks there; tools/stream_probe.py: 207 -> 190 us on 64 x 4096 -> 11008 at 32 tokens).
+        if (CL == 1) {
             int s = 0; uint32_t ph = 0;
             if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");     // the quantised activations are complete
-            for (int t = cluster_id; t < total_tiles; t += num_clusters) {
+            for (int t = t_begin; t < t_end; t += t_step) {
+                const int layer = t / tiles_per_layer, tl = t - layer * tiles_per_layer;
+                const int n_tile = tl / p.m_tiles, m_tile = tl - n_tile * p.m_tiles;
+                if (!(kDbgProd && (p.dbg & 8))) {
+                    for (int kb = 0; kb < p.k_blocks; ++kb) {
+                        mbar_wait_uniform(bar_done(s), ph ^ 1u);
+                        mbar_arrive_expect_tx_warp(bar_pfull(s), TS_P_BYTES);
+                        tma_load_3d_warp(sP + s * TS_P_BYTES, &map_pw, bar_pfull(s), kb * (TS_BK / 4), n_tile * TS_ROWS, layer);
+                        mbar_arrive_expect_tx_warp(bar_ready(s), Cfg::B_BYTES);
+#pragma unroll
+                        for (int j = 0; j < TS_KS; ++j)
+                            tma_load_3d_warp(sB + s * Cfg::B_BYTES + j * (BT * 128), &map_act, bar_ready(s),
+                                             kb * TS_BK + j * 128, m_tile * BT, layer);
+                        if (++s == NS) { s = 0; ph ^= 1u; }
+                    }
+                } else {                                  // experiment: no activation traffic
+                    for (int kb = 0; kb < p.k_blocks; ++kb) {
+                        mbar_wait_uniform(bar_done(s), ph ^ 1u);
+                        mbar_arrive_expect_tx_warp(bar_pfull(s), TS_P_BYTES);
+                        tma_load_3d_warp(sP + s * TS_P_BYTES, &map_pw, bar_pfull(s), kb * (TS_BK / 4), n_tile * TS_ROWS, layer);
+                        mbar_arrive_warp(bar_ready(s));
+                        if (++s == NS) { s = 0; ph ^= 1u; }
+                    }
+                }
+            }
+        } else if (lane == 0) {
+            int s = 0; uint32_t ph = 0;
+            if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");     // the quantised activations are complete
+            for (int t = t_begin; t < t_end; t += t_step) {
                 const int layer = t / tiles_per_layer, tl = t - layer * tiles_per_layer;
                 const int n_group = tl / p.m_tiles, m_tile = tl - n_group * p.m_tiles;
                 const int n_tile = n_group * CL + (int)cta_rank;
@@ -135,7 +188,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     mbar_wait(bar_done(s), ph ^ 1u);
                     mbar_arrive_expect_tx(bar_pfull(s), TS_P_BYTES);
                     tma_load_3d(sP + s * TS_P_BYTES, &map_pw, bar_pfull(s), kb * (TS_BK / 4), n_tile * TS_ROWS, layer);
-                    if (kAblate && (p.dbg & 8)) { mbar_arrive(bar_ready(s)); if (++s == NS) { s = 0; ph ^= 1u; } continue; }   // experiment: no activation traffic
+                    if (kDbgProd && (p.dbg & 8)) { mbar_arrive(bar_ready(s)); if (++s == NS) { s = 0; ph ^= 1u; } continue; }   // experiment: no activation traffic
                     mbar_arrive_expect_tx(bar_ready(s), Cfg::B_BYTES);
 #pragma unroll
                     for (int j = 0; j < TS_KS; ++j) {
@@ -158,27 +211,27 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         if (CL == 1) {
             constexpr uint32_t idesc = umma_idesc_i8(TS_ROWS, BT);
             int s = 0; uint32_t ph = 0; int a = 0; int it = 0;
-            for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
+            for (int t = t_begin; t < t_end; t += t_step, ++it) {
                 const int buf = it & 1;
                 mbar_wait_uniform(bar_tempty(buf), (((uint32_t)it >> 1) & 1u) ^ 1u);
                 tc_fence_after();
                 constexpr int ND = Cfg::DUAL;
                 const int me = ND == 2 ? (warp == 3 ? 1 : 0) : 0;             // which alternate k-blocks / accumulator
-                const uint32_t d_tmem = tmem_base + (uint32_t)((buf * ND + me) * BT);
+                const uint32_t d_tmem = tmem_base + (uint32_t)((buf * ND + me) * NF * BT);     // NF == 2: lo | hi
                 int mine_done = 0;
                 for (int kb = 0; kb < p.k_blocks; ++kb) {
                     if (ND == 1 || (kb & 1) == me) {
                         mbar_wait_uniform(bar_ready(s), ph);
                         tc_fence_after();
                         const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
-                        if (!(kAblate && (p.dbg & 4))) {
+                        if (!(kDbgMma && (p.dbg & 4))) {
 #pragma unroll
                             for (int j = 0; j < TS_KS; ++j) {
                                 const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
 #pragma unroll
                                 for (int k = 0; k < 4; ++k)
-                                    umma_i8_ts_warp(d_tmem, a_tmem + (uint32_t)(j * 32 + k * 8), bdesc + 2u * k, idesc,
-                                                    (mine_done | j | k) ? 1u : 0u);
+                                    umma_i8_ts_warp(d_tmem + (uint32_t)(NF == 2 ? j * BT : 0), a_tmem + (uint32_t)(j * 32 + k * 8), bdesc + 2u * k, idesc,
+                                                    (mine_done | (NF == 2 ? 0 : j) | k) ? 1u : 0u);
                             }
                         }
                         mine_done = 1;
@@ -195,7 +248,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         } else if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_i8(TS_ROWS, BT);
             int s = 0; uint32_t ph = 0; int a = 0; int it = 0;
-            for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
+            for (int t = t_begin; t < t_end; t += t_step, ++it) {
                 const int buf = it & 1;
                 mbar_wait(bar_tempty(buf), (((uint32_t)it >> 1) & 1u) ^ 1u);
                 tc_fence_after();
@@ -204,7 +257,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     mbar_wait(bar_ready(s), ph);
                     tc_fence_after();
                     const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
-                    if (!(kAblate && (p.dbg & 4))) {
+                    if (!(kDbgMma && (p.dbg & 4))) {
 #pragma unroll
                         for (int j = 0; j < TS_KS; ++j) {
                             const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
@@ -232,7 +285,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
             tma_prefetch_desc(&map_out);
             for (int r = 0; r < p.n_peers; ++r) tma_prefetch_desc(&pm.m[r]);
         }
-        for (int t = cluster_id; t < total_tiles; t += num_clusters, ++it) {
+        for (int t = t_begin; t < t_end; t += t_step, ++it) {
             const int buf = it & 1;
             const int layer = t / tiles_per_layer, tl = t - layer * tiles_per_layer;
             const int n_group = tl / p.m_tiles, m_tile = tl - n_group * p.m_tiles;
@@ -251,21 +304,38 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
             asm volatile("bar.sync 1, 128;" ::: "memory");
             const float sc = (n < p.N && p.scale) ? p.scale[layer * p.stride_sb + n] : 1.0f;
             const float bi = (n < p.N && p.bias) ? p.bias[layer * p.stride_sb + n] : 0.0f;
-            mbar_wait(bar_tfull(buf), ((uint32_t)it >> 1) & 1u);
+            // skinny token tiles are bound by the expanders' instruction stream on the same schedulers: poll with a back-off
+            if (BT <= 64 && !(kDbgEpi && (p.dbg & 32))) mbar_wait_relaxed(bar_tfull(buf), ((uint32_t)it >> 1) & 1u);
+            else mbar_wait(bar_tfull(buf), ((uint32_t)it >> 1) & 1u);
             tc_fence_after();
             constexpr int CH = BT >= 32 ? 32 : 16;
             const uint32_t sx_s = sSX + (uint32_t)(buf * BT) * 4u;                 // shared-space addresses: explicit
             const uint32_t sq_s = sSX + (uint32_t)(2 * BT + buf * BT) * 4u;       // ld.shared keeps them off the generic path
 #pragma unroll 1
-            for (int c0 = 0; c0 < ((kAblate && (p.dbg & 1)) ? 0 : BT); c0 += CH) {
+            for (int c0 = 0; c0 < ((kDbgEpi && (p.dbg & 1)) ? 0 : BT); c0 += CH) {
                 // per-token scale and code offset of the chunk first (registers), so that the 32 output
                 // chains below are independent of each other and of the global stores
                 float sxv[CH]; int sqv[CH];
                 uint32_t r[32];
                 constexpr int ND = (CL == 1) ? Cfg::DUAL : 1;
                 constexpr bool SPLIT_LD = (CH == 32 && ND == 1);      // TMEM load issued first, waited for after the barrier below
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * ND * BT + c0);
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * ND * NF * BT + c0);
                 if (SPLIT_LD) tmem_ld32_issue(taddr, r);
+                if constexpr (NF == 2) {          // lo + (hi >> 2), both issuers' partial sums; before sxv / sqv take their registers
+                    uint32_t rh[32], r2[32];
+                    tmem_ld32(taddr, r);
+                    tmem_ld32(taddr + (uint32_t)BT, rh);
+                    if (ND == 2 && p.k_blocks > 1) {
+                        tmem_ld32(taddr + (uint32_t)(2 * BT), r2);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) r[j] += r2[j];
+                        tmem_ld32(taddr + (uint32_t)(3 * BT), r2);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) rh[j] += r2[j];
+                    }
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) r[j] += (uint32_t)((int)rh[j] >> 2);      // hi is a multiple of 4
+                }
 #pragma unroll
                 for (int j = 0; j < CH; j += 4) {
                     asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
@@ -273,8 +343,8 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                     asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];"
                                  : "=r"(sqv[j]), "=r"(sqv[j + 1]), "=r"(sqv[j + 2]), "=r"(sqv[j + 3]) : "r"(sq_s + (c0 + j) * 4));
                 }
-                if (!SPLIT_LD) { if (CH == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r); }
-                if (ND == 2 && p.k_blocks > 1) {
+                if (!SPLIT_LD && NF == 1) { if (CH == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r); }
+                if (NF == 1 && ND == 2 && p.k_blocks > 1) {
                     uint32_t r2[32];
                     if (CH == 32) tmem_ld32(taddr + (uint32_t)BT, r2); else tmem_ld16(taddr + (uint32_t)BT, r2);
 #pragma unroll
@@ -338,7 +408,7 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                 } else if (SPLIT_LD ? (tmem_ld32_wait(r), n < p.N) : (n < p.N)) {     // the wait is warp-wide: before the row test
                     OT* orow = out + m0 * p.ldo + n + (int64_t)c0 * p.ldo;
                     int valid = (int)((p.M - m0 - c0) < CH ? (p.M - m0 - c0) : CH);            // tokens of the chunk in range
-                    if (kAblate && (p.dbg & 256)) valid = (sc == 12345.678f) ? valid : 0;
+                    if (kDbgEpi && (p.dbg & 256)) valid = (sc == 12345.678f) ? valid : 0;
 #pragma unroll
                     for (int j = 0; j < CH; ++j) {
                         const int a = (int)r[j] - sqv[j];
@@ -371,54 +441,73 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
         const int q = warp & 3;                       // TMEM lane quarter; thread = weight row q*32 + lane
         const int row = q * 32 + lane;
         const int set = (warp - 8) >> 2;              // this warp set expands k-blocks set, set+SETS, ...
-        int s = 0; uint32_t ph = 0;                   // ring position of the current k-block
-        int s2 = 0; uint32_t ph2 = 0;                 // ring position of the k-block TS_NSA earlier (A-slot reuse)
-        int a = 0, turn = 0; long long kbc = 0;
-        for (int t = cluster_id; t < total_tiles; t += num_clusters) {
-            for (int kb = 0; kb < p.k_blocks; ++kb, ++kbc) {
-                const bool mine = turn == set;
-                if (++turn == TS_EXP_SETS) turn = 0;
-                if (mine) {
-                    mbar_wait(bar_pfull(s), ph);
-                    // SWIZZLE_64B: 16-byte chunk index ^= address bits [7:8] = (row >> 1) & 3 at a 64-byte row pitch
-                    const uint8_t* P = gP + s * TS_P_BYTES + row * 64;
-                    const int sw = (row >> 1) & 3;
-                    uint32_t w[16];
+        // This set's k-blocks are kbc = set, set + SETS, ... of the CTA's whole k-block sequence (tiles back to back): the ring
+        // positions are stepped by SETS per OWN k-block (walking every k-block and skipping the other set's cost ~20 alu-pipe
+        // instructions per k-block and warp, 16 % of the pipe that bounds skinny token tiles).
+        const long long my_tiles = t_begin < t_end ? (t_end - t_begin + t_step - 1) / t_step : 0;
+        const long long total_kb = my_tiles * p.k_blocks;
+        static_assert(NS >= TS_EXP_SETS && TS_NSA >= TS_EXP_SETS, "ring steps assume at most one wrap");
+        int s = set; uint32_t ph = 0;                 // ring position of the current k-block (kbc % NS)
+        int a = set % TS_NSA;                         // A slot (kbc % TS_NSA)
+        // ring position of the k-block TS_NSA earlier (A-slot reuse), valid from the first own kbc >= TS_NSA
+        int s2 = ((set - TS_NSA) % TS_EXP_SETS + TS_EXP_SETS) % TS_EXP_SETS; uint32_t ph2 = 0;
+        for (long long kbc = set; kbc < total_kb; kbc += TS_EXP_SETS) {
+            mbar_wait(bar_pfull(s), ph);
+            // SWIZZLE_64B: 16-byte chunk index ^= address bits [7:8] = (row >> 1) & 3 at a 64-byte row pitch
+            const uint8_t* P = gP + s * TS_P_BYTES + row * 64;
+            const int sw = (row >> 1) & 3;
+            uint32_t w[16];
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const uint4 v = *reinterpret_cast<const uint4*>(P + ((c ^ sw) << 4));
-                        w[4 * c] = v.x; w[4 * c + 1] = v.y; w[4 * c + 2] = v.z; w[4 * c + 3] = v.w;
-                    }
-                    uint32_t r0[32], r1[32];
-                    if (!(kAblate && (p.dbg & 2))) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            r0[4 * j + 0] = w[j] & 0x03030303u;
-                            r0[4 * j + 1] = (w[j] >> 2) & 0x03030303u;
-                            r0[4 * j + 2] = (w[j] >> 4) & 0x03030303u;
-                            r0[4 * j + 3] = (w[j] >> 6) & 0x03030303u;
-                            r1[4 * j + 0] = w[8 + j] & 0x03030303u;
-                            r1[4 * j + 1] = (w[8 + j] >> 2) & 0x03030303u;
-                            r1[4 * j + 2] = (w[8 + j] >> 4) & 0x03030303u;
-                            r1[4 * j + 3] = (w[8 + j] >> 6) & 0x03030303u;
-                        }
-                    }
-                    if (kbc >= TS_NSA) mbar_wait(bar_done(s2), ph2);   // the MMAs that read this A slot have retired
-                    tc_fence_after();
-                    if (!(kAblate && (p.dbg & 2))) {
-                        const uint32_t ta = tmem_a0 + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * TS_A_COLS);
-                        tmem_st32(ta, r0);
-                        tmem_st32(ta + 32u, r1);
-                        tmem_wait_st();
-                    }
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_ready(s));
-                }
-                if (++s == NS) { s = 0; ph ^= 1u; }
-                if (kbc >= TS_NSA) { if (++s2 == NS) { s2 = 0; ph2 ^= 1u; } }
-                if (++a == TS_NSA) a = 0;
+            for (int c = 0; c < 4; ++c) {
+                const uint4 v = *reinterpret_cast<const uint4*>(P + ((c ^ sw) << 4));
+                w[4 * c] = v.x; w[4 * c + 1] = v.y; w[4 * c + 2] = v.z; w[4 * c + 3] = v.w;
             }
+            uint32_t r0[32], r1[32];
+            if (NF == 2 && !(kDbgExp && (p.dbg & 2))) {
+                // columns 0..31: even fields (values c) -> accumulator lo; columns 32..63: odd fields in place (values 4c) -> hi
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const uint32_t w4 = w[j] >> 4;
+                    r0[2 * j + 0] = w[j] & 0x03030303u;
+                    r0[2 * j + 1] = w4 & 0x03030303u;
+                    r1[2 * j + 0] = w[j] & 0x0c0c0c0cu;
+                    r1[2 * j + 1] = w4 & 0x0c0c0c0cu;
+                }
+            } else if (!(kDbgExp && (p.dbg & 2))) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    r0[4 * j + 0] = w[j] & 0x03030303u;
+                    r0[4 * j + 1] = (w[j] >> 2) & 0x03030303u;
+                    r0[4 * j + 2] = (w[j] >> 4) & 0x03030303u;
+                    r0[4 * j + 3] = (w[j] >> 6) & 0x03030303u;
+                    r1[4 * j + 0] = w[8 + j] & 0x03030303u;
+                    r1[4 * j + 1] = (w[8 + j] >> 2) & 0x03030303u;
+                    r1[4 * j + 2] = (w[8 + j] >> 4) & 0x03030303u;
+                    r1[4 * j + 3] = (w[8 + j] >> 6) & 0x03030303u;
+                }
+            }
+            // pin the 64 expanded words HERE: without it the compiler sinks the whole expansion below the wait for the A slot
+            // (to shorten the live ranges), and the slot ring stops hiding the 112 alu-pipe instructions behind that wait
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                asm volatile("" : "+r"(r0[j]), "+r"(r0[j + 1]), "+r"(r0[j + 2]), "+r"(r0[j + 3]), "+r"(r0[j + 4]), "+r"(r0[j + 5]), "+r"(r0[j + 6]), "+r"(r0[j + 7]));
+                asm volatile("" : "+r"(r1[j]), "+r"(r1[j + 1]), "+r"(r1[j + 2]), "+r"(r1[j + 3]), "+r"(r1[j + 4]), "+r"(r1[j + 5]), "+r"(r1[j + 6]), "+r"(r1[j + 7]));
+            }
+            const bool reuse = kbc >= TS_NSA;
+            if (reuse) mbar_wait(bar_done(s2), ph2);   // the MMAs that read this A slot have retired
+            tc_fence_after();
+            if (!(kDbgExp && (p.dbg & 2))) {
+                const uint32_t ta = tmem_a0 + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * TS_A_COLS);
+                tmem_st32(ta, r0);
+                tmem_st32(ta + 32u, r1);
+                tmem_wait_st();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_ready(s));
+            s += TS_EXP_SETS; if (s >= NS) { s -= NS; ph ^= 1u; }
+            if (reuse) { s2 += TS_EXP_SETS; if (s2 >= NS) { s2 -= NS; ph2 ^= 1u; } }
+            a += TS_EXP_SETS; if (a >= TS_NSA) a -= TS_NSA;
         }
     }
 
@@ -434,10 +523,10 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
     }
 }
 
-template <typename OT, int BT, int CL>
+template <typename OT, int BT, int CL, int NF = 1>
 static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed, UmmaParams p, cudaStream_t s,
                      int64_t stride_q_rows, int64_t stride_packed) {
-    using Cfg = TsCfg<BT, (int)sizeof(OT)>;
+    using Cfg = TsCfg<BT, (int)sizeof(OT), NF>;
     static_assert(BT % (8 * CL) == 0, "token-tile slices must be whole 8-row swizzle atoms");
     CUtensorMap map_act, map_pw;
     const uint64_t L = (uint64_t)p.layers;
@@ -472,7 +561,7 @@ static int launch_ts(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int6
         }
         for (int r = p.n_peers; r < 8; ++r) peer_maps.m[r] = map_out;
     }
-    auto kern = umma_ts_kernel<OT, BT, CL>;
+    auto kern = umma_ts_kernel<OT, BT, CL, NF>;
     static SmemOptIn optin;
     TB_CUDA(ensure_dynamic_smem(kern, optin, Cfg::SMEM_BYTES));
     p.m_tiles = (int)((p.M + BT - 1) / BT);
@@ -514,7 +603,14 @@ static int ts_cluster_size() {
 template <typename OT>
 static int ts_dispatch_bt(const int8_t* q_x, int64_t ldq, const uint8_t* packed, int64_t ld_packed,
                           const UmmaParams& p, cudaStream_t s, int64_t sq, int64_t sp) {
-    if (p.M <= 32) return launch_ts<OT, 32, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+    if (p.M <= 32) {
+        // measured and dropped for these tiles: one multicast copy of the activation tile per cluster of 2 / 4 CTAs (the lock-step of
+        // the ring across the cluster costs 40 %), and activations resident in shared memory for a whole layer (no gain once the
+        // producer warp issued its TMAs from uniform code: the re-reads from L2 are not the bound)
+        if (p.qlayout == TB200_QLAYOUT_GEMM_SPLIT) return launch_ts<OT, 32, 1, 2>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+        return launch_ts<OT, 32, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
+    }
+    if (p.qlayout == TB200_QLAYOUT_GEMM_SPLIT) { set_error("gemm_ts: the field-split activation layout serves at most 32 tokens"); return TB200_EINVAL; }
     if (p.M <= 64) return launch_ts<OT, 64, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
     if (p.M <= 128) return launch_ts<OT, 128, 1>(q_x, ldq, packed, ld_packed, p, s, sq, sp);
     const int n_tiles = (int)((p.N + TS_ROWS - 1) / TS_ROWS);

@@ -951,7 +951,7 @@ extern "C" size_t tb200_gemv_stream_workspace(int64_t M, int64_t K, int count) {
     const StreamGeom gm = stream_geom(M, K);
     const size_t image = (size_t)gm.blob_stride * (size_t)count + 256;
     const int64_t rows = M * count;
-    const size_t umma = (size_t)(ru(rows * ru(K, 16), 256) + 2 * ru(rows * 4, 256) + 256);
+    const size_t umma = (size_t)(ru(rows * ru(K, 256), 256) + 2 * ru(rows * 4, 256) + 256);     // field-split operand order: 256-element blocks
     return image > umma ? image : umma;
 }
 
@@ -962,23 +962,26 @@ static int stream_umma(const void* x, int x_dtype, int64_t M, int64_t K, int64_t
                        void* out, int out_dtype, int64_t ldo, int64_t stride_out,
                        int32_t* acc_out, int layers, void* workspace, cudaStream_t s,
                        void* const* peers = nullptr, int n_peers = 0) {
-    const int64_t ldq = ru(K, 16), rows = M * layers;
+    // <= 32 tokens: the field-split form of the tcgen05 kernel (in-place masks of the odd 2-bit fields, gemm_ts.cu TsCfg NF == 2)
+    const int qlayout = M <= 32 ? TB200_QLAYOUT_GEMM_SPLIT : TB200_QLAYOUT_GEMM;
+    const int64_t ldq = qlayout == TB200_QLAYOUT_GEMM_SPLIT ? ru(K, 256) : ru(K, 16), rows = M * layers;
     char* w = (char*)workspace;
     int8_t* q_x = (int8_t*)w;      w += ru(rows * ldq, 256);
     float* s_x = (float*)w;        w += ru(rows * 4, 256);
     int32_t* sum_qx = (int32_t*)w;
     const size_t xs = dtype_size(x_dtype);
     if (layers == 1 || stride_x == M * ldx) {
-        int rc = tb200_quant_act_i8(x, x_dtype, rows, K, ldx, q_x, ldq, s_x, sum_qx, TB200_QLAYOUT_GEMM, s);
+        int rc = tb200_quant_act_i8(x, x_dtype, rows, K, ldx, q_x, ldq, s_x, sum_qx, qlayout, s);
         if (rc) return rc;
     } else {
         for (int l = 0; l < layers; ++l) {
             int rc = tb200_quant_act_i8((const char*)x + (size_t)l * stride_x * xs, x_dtype, M, K, ldx, q_x + (int64_t)l * M * ldq, ldq,
-                                        s_x + (int64_t)l * M, sum_qx + (int64_t)l * M, TB200_QLAYOUT_GEMM, s);
+                                        s_x + (int64_t)l * M, sum_qx + (int64_t)l * M, qlayout, s);
             if (rc) return rc;
         }
     }
     UmmaParams p = {};
+    p.qlayout = qlayout;
     p.s_x = s_x; p.sum_qx = sum_qx; p.scale = scale; p.bias = bias;
     p.out = out; p.ldo = ldo; p.acc_out = acc_out;
     p.M = M; p.N = N; p.K = K; p.clip_val = fabsf(clip_val);

@@ -68,6 +68,12 @@ __device__ __forceinline__ void store16q(int8_t* qr, int64_t g, const float (&v)
                ((uint32_t)(qv[e0 + 2 * st] & 0xff) << 16) | ((uint32_t)(qv[e0 + 3 * st] & 0xff) << 24);
     }
     int64_t pos = g;
+    if (layout == 3) {      // field-split order: even fields in the first 128 bytes of every 256-element block, odd fields in the second
+        int8_t* blk = qr + 256 * (g >> 4) + 8 * (g & 15);
+        *reinterpret_cast<uint2*>(blk) = make_uint2(w[0], w[2]);
+        *reinterpret_cast<uint2*>(blk + 128) = make_uint2(w[1], w[3]);
+        return;
+    }
     if (layout == 2) {
         const int64_t c = g >> 2, j = g & 3;
         pos = ((c >> 5) * 4 + j) * 32 + (c & 31);
@@ -332,6 +338,12 @@ quant_act_fast_kernel(const T* __restrict__ x, int64_t M, int64_t ldx, int8_t* _
         }
         const int g = lane + 32 * u;
         int pos = g;
+        if (LAYOUT == 3) {
+            int8_t* blk = qr + 256 * (g >> 4) + 8 * (g & 15);
+            *reinterpret_cast<uint2*>(blk) = make_uint2(w[0], w[2]);
+            *reinterpret_cast<uint2*>(blk + 128) = make_uint2(w[1], w[3]);
+            continue;
+        }
         if (LAYOUT == 2) {
             const int c = g >> 2, j = g & 3;
             pos = ((c >> 5) * 4 + j) * 32 + (c & 31);
@@ -350,7 +362,8 @@ static void launch_quant_fast(const T* x, int64_t M, int64_t ldx, int8_t* q, flo
     const unsigned grid = (unsigned)((M + QW - 1) / QW);
     if (layout == 0) quant_act_fast_kernel<T, GC, 0><<<grid, QW * 32, 0, st>>>(x, M, ldx, q, s_x, sum_qx);
     else if (layout == 1) quant_act_fast_kernel<T, GC, 1><<<grid, QW * 32, 0, st>>>(x, M, ldx, q, s_x, sum_qx);
-    else quant_act_fast_kernel<T, GC, 2><<<grid, QW * 32, 0, st>>>(x, M, ldx, q, s_x, sum_qx);
+    else if (layout == 2) quant_act_fast_kernel<T, GC, 2><<<grid, QW * 32, 0, st>>>(x, M, ldx, q, s_x, sum_qx);
+    else quant_act_fast_kernel<T, GC, 3><<<grid, QW * 32, 0, st>>>(x, M, ldx, q, s_x, sum_qx);
 }
 
 }  // namespace tb200
@@ -367,7 +380,8 @@ extern "C" int tb200_quant_act_i8(const void* x, int dtype, int64_t M, int64_t K
     TB_REQUIRE(ldq >= K && ldq % 16 == 0, "quant_act_i8: ldq=%lld must be >= K and a multiple of 16", (long long)ldq);
     TB_REQUIRE((uintptr_t)q_x % 16 == 0, "quant_act_i8: q_x must be 16-byte aligned");
     TB_REQUIRE(dtype_ok(dtype), "quant_act_i8: bad dtype %d", dtype);
-    TB_REQUIRE(layout >= 0 && layout <= 2, "quant_act_i8: bad layout %d", layout);
+    TB_REQUIRE(layout >= 0 && layout <= 3, "quant_act_i8: bad layout %d", layout);
+    TB_REQUIRE(layout != 3 || ldq % 256 == 0, "quant_act_i8: layout 3 needs ldq %% 256 == 0");
     TB_REQUIRE(layout != 2 || ldq % 4096 == 0, "quant_act_i8: layout 2 needs ldq = 4096*ceil(K/4096)");
     const size_t es = dtype_size(dtype);
     const bool vec_ok = ((uintptr_t)x % 16 == 0) && ((ldx * es) % 16 == 0);

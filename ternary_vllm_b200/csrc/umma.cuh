@@ -138,6 +138,7 @@ struct UmmaParams {
     void* peers[8]; int n_peers;      // tensor-parallel gather: store every element into each rank's buffer (see gemv.cu)
     int mc;           // n_peers == 1 and peers[0] is an NVSwitch multicast address: ONE multimem store per 16 bytes reaches every rank
     int pdl;          // launched with programmatic stream serialisation: the activation quantiser may still be running
+    int qlayout;      // 0 / TB200_QLAYOUT_GEMM: activations in layout 1; TB200_QLAYOUT_GEMM_SPLIT (M <= 32, ldq % 256 == 0): field-split kernel
     int dbg;          // TB200_GEMM_DBG experiments: 1 skip the epilogue body, 2 skip the expansion, 4 skip the MMAs
 };
 

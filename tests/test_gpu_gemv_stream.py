@@ -62,6 +62,33 @@ def test_stream_matches_single_layer_kernel(cuda, M):
         assert torch.equal(out[r], ops.gemv(xd, packed[r], sd[r], bd[r], 100.0)), f"layer {r}"
 
 
+@pytest.mark.parametrize("odtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("M", [9, 20, 32])
+@pytest.mark.parametrize("R,N,K", [(22, 1800, 4096), (30, 1300, 3000), (40, 1024, 2560), (21, 1920, 3840)])
+def test_stream_long_list_resident_activations(cuda, M, R, N, K, odtype):
+    """9..32 tokens over a list with several weight tiles per SM and K <= 4096: the tcgen05 kernel keeps a layer's
+    activations resident in shared memory and walks contiguous runs of tiles (gemm_ts.cu, TsCfg RES; K = 3840 has an odd
+    number of k-blocks and stays on the ring form).  Same bits as the layer-by-layer calls (ring form: too few tiles for
+    the resident one), integer accumulators of layer 0 against the oracle, every layer against the oracle's outputs."""
+    Ws, x, scale, bias = make_layers(R, N, K, M, seed=M + R + N + K)
+    packed = torch.stack([ops.quantize_pack(W.to(cuda), "ternary") for W in Ws])
+    xd, sd, bd = x.to(cuda), scale.to(cuda), bias.to(cuda)
+    out, acc = ops.gemv_stream(xd, packed, sd, bd, 100.0, out_dtype=odtype, debug=True)
+    out2 = ops.gemv_stream(xd, packed, sd, bd, 100.0, out_dtype=odtype)          # a second call: same bits
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2)
+    tol = {torch.bfloat16: 2.0 ** -7, torch.float32: 2e-6}[odtype]
+    for r in range(R):
+        if M > 16:      # tb200_linear_forward runs the same tcgen05 kernel (ring form) above 16 tokens
+            assert torch.equal(out[r], ops.ternary_matmul(xd[r], packed[r], sd[r], bd[r], 100.0, out_dtype=odtype)), f"layer {r}"
+        if M <= 16 or r in (0, R // 2, R - 1):
+            acc_o, want = oracle_out(Ws[r], x[r], scale[r], bias[r], 100.0, odtype)
+            if r == 0:
+                assert np.array_equal(acc.cpu().numpy().astype(np.int64), acc_o), "integer accumulators differ"
+            got = out[r].float().cpu().numpy()
+            assert np.all(np.abs(got - want) <= np.abs(want) * tol + 1e-6), f"layer {r}"
+
+
 @pytest.mark.parametrize("odtype", [torch.float32, torch.float16, torch.bfloat16])
 def test_stream_dtypes_no_scale_bias(cuda, odtype):
     R, N, K, M = 2, 200, 1024, 3
