@@ -61,7 +61,9 @@ template <int BT, int OSZ = 4, int NF = 1> struct TsCfg {
     static constexpr int D_COLS = 2 * BT * DUAL * NF;
     // A tiles in TMEM: the expand -> MMA -> retire -> reuse loop of a slot is ~2000 clocks long, so skinny token tiles
     // (which finish a k-block's MMAs quickly and have TMEM columns to spare) keep six of them in flight
-    static constexpr int NSA = NF == 2 ? 4 : BT <= 32 ? 6 : BT <= 64 ? 4 : 2;
+    // (160-token tiles leave room for a third slot: 24.6 -> 21.5 us on the ViT projection M=8224 K=1024 N=1024; a third slot for
+    // 128-token tiles and 128-token tiles for large M were measured and change nothing / lose 15 %)
+    static constexpr int NSA = NF == 2 ? 4 : BT <= 32 ? 6 : BT <= 64 ? 4 : BT == 160 ? 3 : 2;
     static constexpr int NEED = D_COLS + NSA * TS_A_COLS;
     static constexpr int TMEM_COLS = NEED <= 32 ? 32 : NEED <= 64 ? 64 : NEED <= 128 ? 128 : NEED <= 256 ? 256 : 512;
     static_assert(NEED <= 512, "TMEM budget");
@@ -224,18 +226,13 @@ umma_ts_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constan
                         mbar_wait_uniform(bar_ready(s), ph);
                         tc_fence_after();
                         const uint32_t a_tmem = tmem_a0 + (uint32_t)(a * TS_A_COLS);
-                        if (!(kDbgMma && (p.dbg & 4))) {
-#pragma unroll
-                            for (int j = 0; j < TS_KS; ++j) {
-                                const uint64_t bdesc = umma_desc_sw128(sB + s * Cfg::B_BYTES + j * (BT * 128));
-#pragma unroll
-                                for (int k = 0; k < 4; ++k)
-                                    umma_i8_ts_warp(d_tmem + (uint32_t)(NF == 2 ? j * BT : 0), a_tmem + (uint32_t)(j * 32 + k * 8), bdesc + 2u * k, idesc,
-                                                    (mine_done | (NF == 2 ? 0 : j) | k) ? 1u : 0u);
-                            }
-                        }
+                        static_assert(TS_KS == 2, "umma_i8_ts_kblock_warp issues two sub-tiles");
+                        if (!(kDbgMma && (p.dbg & 4)))
+                            umma_i8_ts_kblock_warp<NF == 2>(d_tmem, d_tmem + (uint32_t)(NF == 2 ? BT : 0), a_tmem,
+                                                            umma_desc_sw128(sB + s * Cfg::B_BYTES), umma_desc_sw128(sB + s * Cfg::B_BYTES + BT * 128),
+                                                            idesc, (uint32_t)mine_done, bar_done(s));
+                        else umma_commit_warp(bar_done(s));
                         mine_done = 1;
-                        umma_commit_warp(bar_done(s));
                         if (kb + ND >= p.k_blocks) umma_commit_warp(bar_tfull(buf));   // my last k-block of the tile
                     }
                     if (++s == NS) { s = 0; ph ^= 1u; }

@@ -102,6 +102,36 @@ __device__ __forceinline__ void umma_i8_ts_warp(uint32_t tmem_d, uint32_t tmem_a
         "@q tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
         ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
 }
+// One k-block of the TS kernel (256 int8 of K = two 128-byte activation sub-tiles x four K=32 slices) issued under ONE election,
+// followed by the commit that frees the stage: 8 MMAs + commit = 10 issued instructions instead of 8 x (setp + elect + mma) + elect
+// + commit with their operand moves.  A columns a .. a + 63; sub-tile 0 accumulates into d0, sub-tile 1 into d1 (the same
+// accumulator, or the "hi" one of the field-split form, whose first MMA then also takes the `accum` flag).
+template <bool SPLIT>
+__device__ __forceinline__ void umma_i8_ts_kblock_warp(uint32_t d0, uint32_t d1, uint32_t a, uint64_t bdesc0, uint64_t bdesc1,
+                                                       uint32_t idesc, uint32_t accum, uint32_t bar_done) {
+    asm volatile(
+        "{\n\t.reg .pred p, p1, q, t;\n\t"
+        ".reg .b32 a1, a2, a3, a4, a5, a6, a7;\n\t"
+        ".reg .b64 b01, b02, b03, b11, b12, b13;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "setp.eq.b32 t, %6, %6;\n\t"
+        "setp.ne.or.b32 p1, %8, 0, p;\n\t"
+        "add.u32 a1, %1, 8;\n\tadd.u32 a2, %1, 16;\n\tadd.u32 a3, %1, 24;\n\tadd.u32 a4, %1, 32;\n\t"
+        "add.u32 a5, %1, 40;\n\tadd.u32 a6, %1, 48;\n\tadd.u32 a7, %1, 56;\n\t"
+        "add.u64 b01, %2, 2;\n\tadd.u64 b02, %2, 4;\n\tadd.u64 b03, %2, 6;\n\t"
+        "add.u64 b11, %3, 2;\n\tadd.u64 b12, %3, 4;\n\tadd.u64 b13, %3, 6;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %5, p;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%0], [a1], b01, %5, t;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%0], [a2], b02, %5, t;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%0], [a3], b03, %5, t;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%4], [a4], %3, %5, p1;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%4], [a5], b11, %5, t;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%4], [a6], b12, %5, t;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%4], [a7], b13, %5, t;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%7];\n\t}"
+        ::"r"(d0), "r"(a), "l"(bdesc0), "l"(bdesc1), "r"(d1), "r"(idesc), "r"(accum), "r"(bar_done), "r"(SPLIT ? 0u : 1u) : "memory");
+}
 __device__ __forceinline__ void umma_commit_warp(uint32_t bar) {
     asm volatile(
         "{\n\t.reg .pred q;\n\t"
