@@ -8,7 +8,8 @@ N=1 workload = BASELINE.json configs[1], the decode GEMV sweep: ternary Linear 4
 ring of >= 64 distinct layers whose packed weights exceed L2 (so every layer is streamed from HBM),
 one tb200_gemv_stream call per case (activation quantiser launch + ONE persistent GEMV launch for
 the whole ring; tcgen05 grouped kernel above 8 tokens).  `value` = algorithmic bytes of the step /
-device time (GB/s), the step replayed as one CUDA graph; `e2e` = the same sweep through the
+device time (GB/s), the step replayed as one CUDA graph whose six independent cases sit on three branches
+(`step_schedule`; the one-stream figure is reported beside it); `e2e` = the same sweep through the
 host-buffer C-ABI call (tb200_gemv_stream_host: H2D of all activations of the ring, the two
 launches, D2H of all outputs, per case).  Every case also reports the same ring as a CHAIN of
 per-layer calls (`cases[i].chain`: tb200_gemv with programmatic dependent launch / tb200_linear_forward),
@@ -288,6 +289,29 @@ def run_b200(args):
         for c in cases:
             launch_case(c)
 
+    # The six cases are independent problems: captured on three branches of the graph, one case's quantiser launch and the ramp of
+    # its persistent kernel run in the tail of the previous case's kernel (every kernel here is one CTA per SM, so the
+    # branches take turns on the SMs rather than share them).  TB200_BENCH_FORK=0 captures them back to back on one stream.
+    fork = int(os.environ.get("TB200_BENCH_FORK", "3"))      # measured: 1 branch 4.78, 2: 4.85, 3: 4.96, 4: 4.97, 6: 4.94 TB/s
+    side_streams = [torch.cuda.Stream(dev) for _ in range(max(0, fork - 1))]
+
+    def launch_step_forked():
+        main = torch.cuda.current_stream(dev)
+        branches = [main] + side_streams
+        ev = torch.cuda.Event()
+        ev.record(main)
+        for b in side_streams:
+            b.wait_event(ev)
+        # longest cases first on alternating branches
+        order = sorted(cases, key=lambda c: -algorithmic_bytes(*c) * rings[c[:2]].R)
+        for i, c in enumerate(order):
+            with torch.cuda.stream(branches[i % len(branches)]):
+                launch_case(c)
+        for b in side_streams:
+            e = torch.cuda.Event()
+            e.record(b)
+            main.wait_event(e)
+
     step_bytes = sum(algorithmic_bytes(*c) * rings[c[:2]].R for c in cases)
     step_tokens = sum(c[2] * rings[c[:2]].R for c in cases)
 
@@ -312,13 +336,15 @@ def run_b200(args):
 
     # ---- one step = all six cases, captured as one CUDA graph ----
     stream = torch.cuda.Stream(dev)
+    step_fn = launch_step_forked if fork > 1 else launch_step
     with torch.cuda.stream(stream):
         launch_step()
         stream.synchronize()
+        t_serial, _, _ = timed_graph(launch_step, stream, max(3, min(args.steps, 20)))      # reported beside the forked step
         n0 = ops.launch_count()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph, stream=stream):
-            launch_step()
+            step_fn()
         launches_per_step = ops.launch_count() - n0
         for _ in range(max(3, args.warmup)):
             graph.replay()
@@ -390,6 +416,9 @@ def run_b200(args):
         "dtype": "int8 (u8 codes x s8 activations, s32 accumulate)", "data": "synthetic",
         "config": CONFIG_N1, "tokens_per_s": step_tokens * args.steps / (ms * 1e-3),
         "frac_hbm_measured": value / pk["hbm_gbs"], "clocks": clocks,
+        "step_schedule": {"branches": max(1, fork), "note": "the six independent cases captured on this many branches of one CUDA graph "
+                          "(longest first, alternating): a case's quantiser and the ramp of its persistent kernel overlap the tail of "
+                          "the previous case's kernel", "value_one_stream": step_bytes / t_serial / 1e9, "ms_per_step_one_stream": t_serial * 1e3},
         "e2e": e2e, "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
         "cases": per_case, "roofline": roofline, "mlp_chain": None if args.no_extra else run_mlp(dev, pk),
         "prep": None if args.no_extra else run_prep(dev, pk), "binary_1bit": None if args.no_extra else run_binary_1bit(dev, pk), "gemm": gemm, "vit_l14": None if args.no_gemm else run_vit(dev),

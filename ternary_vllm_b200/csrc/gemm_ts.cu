@@ -61,8 +61,8 @@ template <int BT, int OSZ = 4, int NF = 1> struct TsCfg {
     static constexpr int D_COLS = 2 * BT * DUAL * NF;
     // A tiles in TMEM: the expand -> MMA -> retire -> reuse loop of a slot is ~2000 clocks long, so skinny token tiles
     // (which finish a k-block's MMAs quickly and have TMEM columns to spare) keep six of them in flight
-    // (160-token tiles leave room for a third slot: 24.6 -> 21.5 us on the ViT projection M=8224 K=1024 N=1024; a third slot for
-    // 128-token tiles and 128-token tiles for large M were measured and change nothing / lose 15 %)
+    // (160-token tiles leave room for a third slot: 24.6 -> 21.5 us on the ViT projection M=8224 K=1024 N=1024 in the experiment
+    // build, no change in the release build; a third slot for 128-token tiles changes nothing, 128-token tiles for large M lose 15 %)
     static constexpr int NSA = NF == 2 ? 4 : BT <= 32 ? 6 : BT <= 64 ? 4 : BT == 160 ? 3 : 2;
     static constexpr int NEED = D_COLS + NSA * TS_A_COLS;
     static constexpr int TMEM_COLS = NEED <= 32 ? 32 : NEED <= 64 ? 64 : NEED <= 128 ? 128 : NEED <= 256 ? 256 : 512;
