@@ -40,6 +40,19 @@ def kperm_index(K_padded: int) -> np.ndarray:
     return g * 16 + 4 * (r % 4) + r // 4
 
 
+def split_layout_index(K_padded: int) -> np.ndarray:
+    """tb200_quant_act_i8 layout 3 (TB200_QLAYOUT_GEMM_SPLIT, operand order of the field-split 32-token tcgen05 kernel):
+    inside every 256-element block, element 16 j + 4 b + f (f = 2-bit field of packed byte b of packed word j) sits at
+    position 128 (f & 1) + 8 j + 4 (f >> 1) + b.  Returns idx with: position p holds element idx[p]."""
+    assert K_padded % 256 == 0
+    k = np.arange(256)
+    j, b, f = k // 16, (k % 16) // 4, k % 4
+    pos = 128 * (f & 1) + 8 * j + 4 * (f >> 1) + b
+    inv = np.empty(256, dtype=np.int64)
+    inv[pos] = k
+    return (np.arange(K_padded // 256)[:, None] * 256 + inv[None, :]).reshape(-1)
+
+
 def gemv_layout_index(K: int) -> np.ndarray:
     """tb200_quant_act_i8 layout 2 (the decode GEMV's shared-memory image): byte position p of the
     row holds element gemv_layout_index[p] of the zero-padded activation row (ldq = 4096*ceil(K/4096)).

@@ -180,12 +180,13 @@ def binary_init(weight: torch.Tensor, per_row: bool, positive_only: bool = False
 # ------------------------------------------------------------------ activations
 def quant_act_i8(x: torch.Tensor, kperm: bool = False, layout: int | None = None):
     """x [M,K] -> (q_x int8 [M, ldq], s_x f32 [M], sum_qx i32 [M]).  layout 0 natural, 1 tcgen05
-    GEMM operand order (``kperm=True``), 2 decode-GEMV image; ldq = K rounded up to 16 (4096 for 2)."""
+    GEMM operand order (``kperm=True``), 2 decode-GEMV image, 3 the field-split order of the 32-token list kernel;
+    ldq = K rounded up to 16 (4096 for layout 2, 256 for layout 3)."""
     _cuda(x)
     assert x.dim() == 2 and x.stride(1) == 1
     M, K = x.shape
     layout = int(kperm) if layout is None else layout
-    ldq = (K + 4095) // 4096 * 4096 if layout == 2 else (K + 15) // 16 * 16
+    ldq = (K + 4095) // 4096 * 4096 if layout == 2 else (K + 255) // 256 * 256 if layout == 3 else (K + 15) // 16 * 16
     q = torch.empty((M, ldq), dtype=torch.int8, device=x.device)
     s = torch.empty((M,), dtype=torch.float32, device=x.device)
     sq = torch.empty((M,), dtype=torch.int32, device=x.device)
@@ -549,7 +550,7 @@ def _quant_act_op(x: torch.Tensor, layout: int) -> tuple[torch.Tensor, torch.Ten
 @_quant_act_op.register_fake
 def _(x, layout):
     M, K = x.shape
-    ldq = (K + 4095) // 4096 * 4096 if layout == 2 else (K + 15) // 16 * 16
+    ldq = (K + 4095) // 4096 * 4096 if layout == 2 else (K + 255) // 256 * 256 if layout == 3 else (K + 15) // 16 * 16
     return (x.new_empty((M, ldq), dtype=torch.int8), x.new_empty((M,), dtype=torch.float32),
             x.new_empty((M,), dtype=torch.int32))
 

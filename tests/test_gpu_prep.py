@@ -134,7 +134,7 @@ def test_ternary_init_vs_oracle(cuda, N, K, dtype):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("layout", [0, 1, 2])
+@pytest.mark.parametrize("layout", [0, 1, 2, 3])
 @pytest.mark.parametrize("M,K", [(1, 64), (5, 77), (3, 4096), (40, 1000), (2, 11008),
                                  # >= 4 rows per SM: the warp-per-row kernels (specialised for K = 1024 / 2048 / 4096, generic otherwise)
                                  (700, 4096), (650, 1024), (600, 2048), (640, 512), (610, 3000)])
@@ -154,6 +154,9 @@ def test_quant_act_bit_exact(cuda, dtype, layout, M, K):
     elif layout == 2:
         assert ldq == (K + 4095) // 4096 * 4096
         qpad = qpad[:, ref_int8.gemv_layout_index(K)]
+    elif layout == 3:
+        assert ldq == (K + 255) // 256 * 256
+        qpad = qpad[:, ref_int8.split_layout_index(ldq)]
     assert np.array_equal(q.cpu().numpy(), qpad)
 
 
