@@ -329,7 +329,6 @@ int tb200_linear_forward(const void* x, int x_dtype, int64_t M, int64_t K, int64
  * it needs to start at zero: each call rewrites what it reads): calls that OVERLAP on one GPU -- two streams, or two
  * graphs replayed concurrently -- race; serialise them or give the others tb200_linear_forward with their own workspace. */
 #define TB200_STATIC_SCRATCH_BYTES (8u << 20)
-size_t tb200_linear_static_scratch_bytes(void);
 int tb200_linear_forward_static(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
                                 const uint8_t* packed, int64_t ld_packed, int64_t N,
                                 const float* scale, const float* bias, float clip_val,

@@ -18,6 +18,7 @@ Q_TERNARY, Q_SIGN, Q_STEP = 0, 1, 2
 FMT_A, FMT_B, FMT_C = 0, 1, 2
 GEMV_MAX_M = 32
 GEMV_FUSED_M = 8          # TB200_GEMV_FUSED_M: tokens per pass of the decode GEMVs
+STATIC_SCRATCH_BYTES = 8 << 20    # TB200_STATIC_SCRATCH_BYTES (tb200_linear_forward_static)
 FLAG_PDL = 1
 ACT_NONE, ACT_GELU_TANH, ACT_RELU = 0, 1, 2
 CHAIN_MAX_M, CHAIN_MAX_LAYERS = 8, 128
@@ -99,7 +100,6 @@ SIGNATURES = {
     "tb200_linear_workspace": (_sz, [_i64, _i64]),
     "tb200_linear_forward": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
                                     _vp, _i32, _i64, _vp, _vp]),
-    "tb200_linear_static_scratch_bytes": (_sz, []),
     "tb200_linear_forward_static": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,
                                            _vp, _i32, _i64, _vp]),
     "tb200_linear_forward_tp": (_i32, [_vp, _i32, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _f32,

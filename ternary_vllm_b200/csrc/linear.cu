@@ -164,8 +164,6 @@ static int static_scratch(void** ptr) {
 }
 }  // namespace tb200
 
-extern "C" size_t tb200_linear_static_scratch_bytes(void) { return (size_t)TB200_STATIC_SCRATCH_BYTES; }
-
 extern "C" int tb200_linear_forward_static(const void* x, int x_dtype, int64_t M, int64_t K, int64_t ldx,
                                            const uint8_t* packed, int64_t ld_packed, int64_t N,
                                            const float* scale, const float* bias, float clip_val,

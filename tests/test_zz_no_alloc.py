@@ -50,7 +50,6 @@ def _with_workspace(x, packed, sc, bi, clip, N, stream):
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("M,K,N", [(1, 1024, 512), (8, 4096, 1000), (12, 1024, 300), (32, 2048, 640), (300, 1024, 384), (729, 4304, 256)])
 def test_static_scratch_matches_workspace_call(cuda, M, K, N, dtype):
-    assert L.lib().tb200_linear_static_scratch_bytes() == 8 << 20
     stream = torch.cuda.current_stream(cuda)
     tol = {torch.bfloat16: 2.0 ** -7, torch.float32: 2e-6}[dtype]
     for call in range(2):                       # two calls in a row, different inputs: the shared array holds call 0's rows
@@ -109,7 +108,7 @@ def test_static_scratch_under_graph_capture(cuda):
 
 def test_static_scratch_rejects_oversize(cuda):
     lib = L.lib()
-    cap = lib.tb200_linear_static_scratch_bytes()
+    cap = L.STATIC_SCRATCH_BYTES
     M, K = 4096, 4096
     assert lib.tb200_linear_workspace(M, K) > cap
     rc = lib.tb200_linear_forward_static(None, L.TB200_BF16, M, K, K, None, 1024, 16, None, None, 100.0, None, L.TB200_BF16, 16, None)
