@@ -10,10 +10,16 @@
 //     its rows (4 conflict-free LDS.128 per thread), turns the 16 words into 64 registers of u8 codes
 //     (3 shifts + 4 ANDs per word) and writes them with two tcgen05.st.32x32b.x32 into one of two A
 //     slots in tensor memory (64 columns each): the expanded weights never touch shared memory;
-//   * ONE thread issues 8 x tcgen05.mma.cta_group::1.kind::i8 (A from TMEM, B from shared memory) after
+//   * the MMA warp issues 8 x tcgen05.mma.cta_group::1.kind::i8 (A from TMEM, B from shared memory) after
 //     ONE mbarrier wait (ready[s] = activation bytes landed + A slot written) and signals ONE
-//     tcgen05.commit (done[s] frees the shared-memory stage and the A slot).  The issuing thread's loop
-//     latency, not the tensor pipe, bounded the first versions (profiles/README.md, ablation table);
+//     tcgen05.commit (done[s] frees the shared-memory stage and the A slot) -- all nine under ONE election
+//     in one asm block (umma_i8_ts_kblock_warp): the issuing loop's latency, not the tensor pipe, bounded the
+//     first versions (profiles/README.md, ablation table) and still sets how soon an A slot is free again;
+//   * the TMA producer, like the MMA issuer, is a whole warp running warp-uniform code with one elected lane
+//     issuing: a single producer THREAD moved every TMA operand through an R2UR broadcast loop, which was
+//     co-critical for 32-token tiles (three TMAs per ~600-clock k-block);
+//   * 32-token tiles of decode lists use the field-split form (TsCfg NF == 2): odd 2-bit fields masked in
+//     place (value 4c) into their own accumulators, activations in TB200_QLAYOUT_GEMM_SPLIT order;
 //   * accumulators are double-buffered in TMEM (2 x BT columns); the epilogue warps read them with
 //     tcgen05.ld, apply -sum_qx, s_x*scale, bias, clip, and hand 32-token x 128-channel chunks to TMA
 //     stores through a double-buffered shared-memory staging tile (2-byte scattered stores cost 60 us).
